@@ -1,0 +1,137 @@
+"""Thin object wrapper over the C ABI (include/lr_api.h).
+
+`Context` owns one `lr_ctx` (one CUDA device).  All compute goes through
+liblr_b200.so; a missing library or missing GPU raises -- there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import numpy as np
+
+from . import _capi as K
+from .scene import Scene
+
+
+def _ptr(a):
+    """numpy array or torch tensor -> (void*, is_device)."""
+    if isinstance(a, np.ndarray):
+        return C.c_void_p(a.ctypes.data), 0
+    # torch tensor (duck-typed to keep torch optional at import time)
+    if hasattr(a, "data_ptr"):
+        return C.c_void_p(a.data_ptr()), 1 if a.is_cuda else 0
+    raise TypeError("expected a numpy array or a torch tensor")
+
+
+class Context:
+    def __init__(self, device: int = 0, lib_path: str | None = None):
+        self.lib = K.load_library(lib_path)
+        self.ctx = C.c_void_p()
+        st = self.lib.lr_create(int(device), C.byref(self.ctx))
+        if st != K.LR_OK:
+            K.check(self.lib, None, st, "lr_create")
+        self.device = device
+        self.scene: Scene | None = None
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.lr_destroy(self.ctx); self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, st, what):
+        K.check(self.lib, self.ctx, st, what)
+
+    # -- scene ---------------------------------------------------------------
+    def upload(self, scene: Scene):
+        pod = scene.pod()
+        self._chk(self.lib.lr_scene_upload(self.ctx, C.byref(pod)), "lr_scene_upload")
+        self.scene = scene
+        return self
+
+    def set_stream(self, cuda_stream_ptr: int):
+        self._chk(self.lib.lr_set_stream(self.ctx, C.c_void_p(cuda_stream_ptr)), "lr_set_stream")
+
+    # -- forward ---------------------------------------------------------------
+    def render(self, seed: int = 0, spp: int | None = None, out=None):
+        sc = self.scene; W, H = sc.film_size; spp = spp or sc.spp
+        if out is None:
+            out = np.empty((H, W, sc.out_channels), dtype=np.float32)
+        p, dev = _ptr(out)
+        self._chk(self.lib.lr_render(self.ctx, seed & 0xffffffff, spp, p, dev), "lr_render")
+        return out
+
+    def film_clear(self):
+        self._chk(self.lib.lr_film_clear(self.ctx), "lr_film_clear")
+
+    def render_lanes(self, seed, spp, begin, end):
+        self._chk(self.lib.lr_render_lanes(self.ctx, seed & 0xffffffff, spp, begin, end), "lr_render_lanes")
+
+    def film_channels(self):
+        return self.lib.lr_film_channels(self.ctx)
+
+    def film_read(self, out=None):
+        W, H = self.scene.film_size
+        if out is None:
+            out = np.empty((H, W, self.film_channels()), dtype=np.float32)
+        p, dev = _ptr(out); self._chk(self.lib.lr_film_read(self.ctx, p, dev), "lr_film_read"); return out
+
+    def film_write(self, block):
+        p, dev = _ptr(block); self._chk(self.lib.lr_film_write(self.ctx, p, dev), "lr_film_write")
+
+    def film_develop(self, out=None):
+        sc = self.scene; W, H = sc.film_size
+        if out is None:
+            out = np.empty((H, W, sc.out_channels), dtype=np.float32)
+        p, dev = _ptr(out); self._chk(self.lib.lr_film_develop(self.ctx, p, dev), "lr_film_develop"); return out
+
+    def film_device_ptr(self):
+        return self.lib.lr_film_device_ptr(self.ctx)
+
+    def sample_lanes(self, seed, spp, begin, end, out=None):
+        if out is None:
+            out = np.empty((end - begin, 4), dtype=np.float32)
+        p, dev = _ptr(out)
+        self._chk(self.lib.lr_sample_lanes(self.ctx, seed & 0xffffffff, spp, begin, end, p, dev), "lr_sample_lanes")
+        return out
+
+    # -- adjoint -----------------------------------------------------------------
+    def render_backward(self, grad_in, seed: int = 0, spp: int | None = None, begin: int = 0, end: int = 0):
+        spp = spp or self.scene.spp
+        p, dev = _ptr(grad_in)
+        self._chk(self.lib.lr_render_backward(self.ctx, seed & 0xffffffff, spp, p, dev, begin, end), "lr_render_backward")
+
+    def grid_update(self, grid: int, data):
+        p, dev = _ptr(data); self._chk(self.lib.lr_grid_update(self.ctx, grid, p, dev), "lr_grid_update")
+
+    def grid_grad_zero(self, grid: int):
+        self._chk(self.lib.lr_grid_grad_zero(self.ctx, grid), "lr_grid_grad_zero")
+
+    def grid_grad_read(self, grid: int, out=None):
+        n = self.lib.lr_grid_size(self.ctx, grid)
+        if out is None:
+            out = np.empty(n, dtype=np.float32)
+        p, dev = _ptr(out); self._chk(self.lib.lr_grid_grad_read(self.ctx, grid, p, dev), "lr_grid_grad_read"); return out
+
+    def grid_grad_device_ptr(self, grid: int):
+        return self.lib.lr_grid_grad_device_ptr(self.ctx, grid)
+
+    def grid_size(self, grid: int):
+        return self.lib.lr_grid_size(self.ctx, grid)
+
+    # -- probes / control ------------------------------------------------------------
+    def ray_intersect(self, rays: np.ndarray):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        hits = np.empty((rays.shape[0], 4), dtype=np.float32)
+        self._chk(self.lib.lr_ray_intersect(self.ctx, C.c_void_p(rays.ctypes.data), rays.shape[0], C.c_void_p(hits.ctypes.data)), "lr_ray_intersect")
+        return hits
+
+    def cancel(self):
+        self.lib.lr_cancel(self.ctx)
+
+    def stats(self) -> dict:
+        s = K.lr_stats(); self._chk(self.lib.lr_stats_get(self.ctx, C.byref(s)), "lr_stats_get")
+        return {k: getattr(s, k) for k, _ in K.lr_stats._fields_}

@@ -1,0 +1,325 @@
+// lr_backend_api.inl -- scene upload and the render / adjoint entry points (included by lr_backend.cu)
+
+extern "C" {
+
+int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
+    if (!c || !s) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_scene_upload: NULL argument");
+    if (s->api_version != LR_API_VERSION) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_scene_upload: api_version %u != %u", s->api_version, LR_API_VERSION);
+    if (s->n_bsdfs > LR_MAX_BSDFS || s->n_media > LR_MAX_MEDIA || s->n_grids > LR_MAX_GRIDS || s->n_emitters > LR_MAX_EMITTERS)
+        LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: too many bsdfs/media/grids/emitters");
+    if (s->integrator.kind > LR_INTEGRATOR_PRBVOLPATH) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: unknown integrator kind %u", s->integrator.kind);
+    LR_CUDA(c, cudaSetDevice(c->device));
+    c->free_scene();
+    DScene &sc = c->sc; memset(&sc, 0, sizeof sc);
+    sc.sensor = s->sensor; sc.integ = s->integrator;
+    mat_copy(sc.cam_to_world, s->sensor.to_world); mat_copy(sc.sample_to_camera, s->sensor.sample_to_camera);
+    sc.max_depth = s->integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) s->integrator.max_depth;
+    sc.rr_depth = s->integrator.rr_depth; sc.hide_emitters = s->integrator.hide_emitters;
+    if (s->sensor.rfilter == LR_RFILTER_GAUSSIAN) gaussian_coeffs(s->sensor.rfilter_stddev, s->sensor.rfilter_radius, sc.gauss_coeff);
+    if (s->sensor.rfilter_radius > 2.5f) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: reconstruction filter radius > 2.5 px is outside the hot path");
+    LR_CUDA(c, c->scratch.alloc(256));
+
+    // ---- meshes: concatenate triangles (gid order), upload per-mesh attribute arrays ----
+    std::vector<DTri> tris; std::vector<DMesh> meshes(s->n_meshes);
+    V3 lo = mk3(INFINITY), hi = mk3(-INFINITY);
+    for (uint32_t i = 0; i < s->n_meshes; ++i) {
+        const lr_mesh &m = s->meshes[i]; DMesh &d = meshes[i]; memset(&d, 0, sizeof d);
+        if (m.bsdf < 0 || (uint32_t) m.bsdf >= s->n_bsdfs) LR_FAIL(c, LR_ERR_INVALID_ARG, "mesh %u: bsdf index out of range", i);
+        DevBuf *bp = c->newbuf(), *bi = c->newbuf();
+        if (int r = upload(c, bp, m.positions, (size_t) m.n_vertices * 3)) return r;
+        if (int r = upload(c, bi, m.indices, (size_t) m.n_faces * 3)) return r;
+        d.pos = bp->as<float>(); d.idx = bi->as<uint32_t>();
+        if (m.normals) { DevBuf *b = c->newbuf(); if (int r = upload(c, b, m.normals, (size_t) m.n_vertices * 3)) return r; d.nrm = b->as<float>(); }
+        if (m.texcoords) { DevBuf *b = c->newbuf(); if (int r = upload(c, b, m.texcoords, (size_t) m.n_vertices * 2)) return r; d.uv = b->as<float>(); }
+        d.bsdf = m.bsdf; d.interior = m.interior_medium; d.exterior = m.exterior_medium; d.emitter = m.emitter;
+        d.tri_offset = (uint32_t) tris.size(); d.n_faces = m.n_faces;
+        d.flags = (m.interior_medium >= 0 || m.exterior_medium >= 0) ? 1u : 0u;
+        bool is_null = s->bsdfs[m.bsdf].kind == LR_BSDF_NULL; if (is_null) sc.any_null_bsdf = 1;
+        std::vector<float> cdf(m.n_faces); float area = 0.f;
+        for (uint32_t f = 0; f < m.n_faces; ++f) {
+            const uint32_t *ix = m.indices + 3 * (size_t) f;
+            for (int k = 0; k < 3; ++k) if (ix[k] >= m.n_vertices) LR_FAIL(c, LR_ERR_INVALID_ARG, "mesh %u: vertex index out of range", i);
+            const float *a = m.positions + 3 * (size_t) ix[0], *b = m.positions + 3 * (size_t) ix[1], *cc = m.positions + 3 * (size_t) ix[2];
+            DTri t; uint32_t gid = (uint32_t) tris.size();
+            t.v0 = make_float4(a[0], a[1], a[2], 0.f); t.v1 = make_float4(b[0], b[1], b[2], 0.f); t.v2 = make_float4(cc[0], cc[1], cc[2], 0.f);
+            memcpy(&t.v0.w, &gid, 4); memcpy(&t.v1.w, &i, 4); uint32_t fl = is_null ? 1u : 0u; memcpy(&t.v2.w, &fl, 4);
+            tris.push_back(t);
+            for (const float *p : {a, b, cc}) { lo.x = std::min(lo.x, p[0]); lo.y = std::min(lo.y, p[1]); lo.z = std::min(lo.z, p[2]);
+                                                hi.x = std::max(hi.x, p[0]); hi.y = std::max(hi.y, p[1]); hi.z = std::max(hi.z, p[2]); }
+            // 0.5 * |e1 x e2| with the device's operation order is not needed bit-exactly: set-up only
+            float e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {cc[0] - a[0], cc[1] - a[1], cc[2] - a[2]};
+            float cx = e1[1] * e2[2] - e1[2] * e2[1], cy = e1[2] * e2[0] - e1[0] * e2[2], cz = e1[0] * e2[1] - e1[1] * e2[0];
+            area += 0.5f * sqrtf(cx * cx + cy * cy + cz * cz); cdf[f] = area;
+        }
+        d.area = area;
+        DevBuf *bc = c->newbuf(); if (int r = upload(c, bc, cdf.data(), cdf.size())) return r; d.area_cdf = bc->as<float>();
+    }
+    if (!tris.empty()) {                                       // scene bounding sphere (bbox.h:343-346)
+        sc.bs_center = mk3((lo.x + hi.x) * 0.5f, (lo.y + hi.y) * 0.5f, (lo.z + hi.z) * 0.5f);
+        float dx = sc.bs_center.x - hi.x, dy = sc.bs_center.y - hi.y, dz = sc.bs_center.z - hi.z;
+        sc.bs_radius = sqrtf(fmaf(dz, dz, fmaf(dy, dy, dx * dx)));
+    }
+    { DevBuf *b = c->newbuf(); if (int r = upload(c, b, meshes.data(), meshes.size())) return r; sc.meshes = b->as<DMesh>(); sc.n_meshes = s->n_meshes; }
+    { DevBuf *b = c->newbuf(); if (int r = upload(c, b, s->bsdfs, s->n_bsdfs)) return r; sc.bsdfs = b->as<lr_bsdf>(); }
+    if (int r = build_lbvh(c, tris, lo, hi)) return r;
+
+    // ---- grids ----
+    c->h_grids.resize(s->n_grids); c->grid_floats.resize(s->n_grids);
+    for (uint32_t i = 0; i < s->n_grids; ++i) {
+        const lr_grid &g = s->grids[i]; DGrid &d = c->h_grids[i]; memset(&d, 0, sizeof d);
+        if (g.channels != 1 && g.channels != 3) LR_FAIL(c, LR_ERR_UNSUPPORTED, "grid %u: channels must be 1 or 3", i);
+        size_t n = (size_t) g.res[0] * g.res[1] * g.res[2] * g.channels; c->grid_floats[i] = n;
+        DevBuf *b = c->newbuf(); if (int r = upload(c, b, g.data, n)) return r;
+        d.data = b->as<float>(); d.rx = g.res[0]; d.ry = g.res[1]; d.rz = g.res[2]; d.ch = g.channels;
+        mat_copy(d.to_local, g.to_local); d.bmin = mk3(g.bbox_min[0], g.bbox_min[1], g.bbox_min[2]); d.bmax = mk3(g.bbox_max[0], g.bbox_max[1], g.bbox_max[2]);
+        d.filter = g.filter; d.wrap = g.wrap; d.differentiable = g.differentiable;
+        d.cell = s->integrator.majorant_cell ? (int) s->integrator.majorant_cell : 8;
+        d.mx = (d.rx + d.cell - 1) / d.cell; d.my = (d.ry + d.cell - 1) / d.cell; d.mz = (d.rz + d.cell - 1) / d.cell;
+        DevBuf *bm = c->newbuf(); LR_CUDA(c, bm->alloc((size_t) d.mx * d.my * d.mz * 4)); d.maj = bm->as<float>();
+        if (g.differentiable) { DevBuf *bg = c->newbuf(); LR_CUDA(c, bg->alloc(n * 4)); LR_CUDA(c, cudaMemsetAsync(bg->p, 0, n * 4, c->stream)); d.grad = bg->as<float>(); }
+    }
+    c->h_media.resize(s->n_media);
+    for (uint32_t i = 0; i < s->n_media; ++i) {
+        c->h_media[i].m = s->media[i]; c->h_media[i].max_density = 0.f;
+        const lr_medium &m = s->media[i];
+        if (m.kind == LR_MEDIUM_HETEROGENEOUS && (m.sigma_t_grid < 0 || (uint32_t) m.sigma_t_grid >= s->n_grids))
+            LR_FAIL(c, LR_ERR_INVALID_ARG, "medium %u: heterogeneous medium needs a sigma_t grid", i);
+        if (m.kind == LR_MEDIUM_HETEROGENEOUS) sc.prb_handle_null = 1; else sc.prb_nee_homogeneous = 1;
+    }
+    c->d_grids = c->newbuf(); LR_CUDA(c, c->d_grids->alloc(std::max<size_t>(s->n_grids, 1) * sizeof(DGrid)));
+    c->d_media = c->newbuf(); LR_CUDA(c, c->d_media->alloc(std::max<size_t>(s->n_media, 1) * sizeof(DMedium)));
+    sc.grids = c->d_grids->as<DGrid>(); sc.media = c->d_media->as<DMedium>();
+    if (s->n_media) LR_CUDA(c, cudaMemcpyAsync(c->d_media->p, c->h_media.data(), s->n_media * sizeof(DMedium), cudaMemcpyHostToDevice, c->stream));
+    for (uint32_t i = 0; i < s->n_grids; ++i) {
+        if (int r = refresh_grid_derived(c, i)) return r;
+        if (s->grids[i].max_value >= 0.f) {                     // `max_value` override (grid.cpp:303-306)
+            c->h_grids[i].maxv = s->grids[i].max_value;
+            for (auto &m : c->h_media) if (m.m.kind == LR_MEDIUM_HETEROGENEOUS && m.m.sigma_t_grid == (int) i) m.max_density = m.m.scale * s->grids[i].max_value;
+            LR_CUDA(c, cudaMemcpyAsync(c->d_grids->p, c->h_grids.data(), c->h_grids.size() * sizeof(DGrid), cudaMemcpyHostToDevice, c->stream));
+            LR_CUDA(c, cudaMemcpyAsync(c->d_media->p, c->h_media.data(), c->h_media.size() * sizeof(DMedium), cudaMemcpyHostToDevice, c->stream));
+        }
+    }
+
+    // ---- emitters ----
+    std::vector<DEmitter> ems(s->n_emitters); sc.env = -1; sc.n_emitters = s->n_emitters;
+    for (uint32_t i = 0; i < s->n_emitters; ++i) {
+        DEmitter &d = ems[i]; memset(&d, 0, sizeof d); d.e = s->emitters[i]; d.e.pixels = nullptr;
+        if (d.e.kind != LR_EMITTER_AREA) sc.env = (int) i;
+        if (d.e.kind == LR_EMITTER_AREA && !d.e.is_rectangle && (d.e.mesh < 0 || (uint32_t) d.e.mesh >= s->n_meshes))
+            LR_FAIL(c, LR_ERR_INVALID_ARG, "emitter %u: area light without a mesh", i);
+        if (d.e.kind == LR_EMITTER_ENVMAP) {
+            if (!s->emitters[i].pixels || d.e.width < 2 || d.e.height < 2) LR_FAIL(c, LR_ERR_INVALID_ARG, "emitter %u: envmap needs pixels", i);
+            std::vector<float> px, warp; build_envmap(s->emitters[i], px, warp, d);
+            DevBuf *bp = c->newbuf(), *bw = c->newbuf();
+            if (int r = upload(c, bp, px.data(), px.size())) return r; if (int r = upload(c, bw, warp.data(), warp.size())) return r;
+            d.pixels = bp->as<float>(); d.warp_data = bw->as<float>();
+            mat_copy(d.to_world, d.e.to_world); invert4(d.e.to_world, d.to_local.m);
+        }
+    }
+    { DevBuf *b = c->newbuf(); if (int r = upload(c, b, ems.data(), ems.size())) return r; sc.emitters = b->as<DEmitter>(); }
+
+    // ---- film ----
+    c->W = s->sensor.film_width; c->H = s->sensor.film_height; c->film_channels = s->sensor.has_alpha ? 5 : 4;
+    LR_CUDA(c, c->film.alloc((size_t) c->W * c->H * c->film_channels * 4));
+    LR_CUDA(c, cudaMemsetAsync(c->film.p, 0, c->film.bytes, c->stream));
+    LR_CUDA(c, c->weight_img.alloc((size_t) c->W * c->H * 4));
+    LR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->has_scene = true; memset(&c->st, 0, sizeof c->st);
+    return LR_OK;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// launches
+// ---------------------------------------------------------------------------------------------
+struct PassPlan { uint32_t spp_per_pass, n_passes; uint64_t n_lanes; };
+// pass splitting when W*H*spp exceeds 2^32-1 lanes (src/render/integrator.cpp:275-293)
+static PassPlan plan_passes(const lr_ctx *c, uint32_t spp) {
+    PassPlan p; p.spp_per_pass = spp; p.n_passes = 1;
+    uint64_t wf = (uint64_t) c->W * c->H * spp, limit = 0xffffffffull;
+    if (wf > limit) { p.spp_per_pass = spp / (uint32_t) ((wf + limit - 1) / limit); p.n_passes = spp / p.spp_per_pass; }
+    p.n_lanes = (uint64_t) c->W * c->H * p.spp_per_pass;
+    return p;
+}
+
+template <typename K> static int grid_for(lr_ctx *c, K kernel, int block, int &grid) {
+    int per_sm = 0; LR_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0));
+    grid = std::max(per_sm, 1) * c->n_sm; return LR_OK;           // persistent: a whole number of CTAs per SM
+}
+
+template <int KIND, int C, bool TO_FILM> static int launch_render_t(lr_ctx *c, const RenderArgs &a) {
+    int grid; if (int r = grid_for(c, k_render<KIND, C, TO_FILM>, 128, grid)) return r;
+    uint64_t warps_needed = (a.lane_end - a.lane_begin + 31) / 32;
+    grid = (int) std::min<uint64_t>((uint64_t) grid, (warps_needed + 3) / 4); if (grid < 1) grid = 1;
+    k_render<KIND, C, TO_FILM><<<grid, 128, 0, c->stream>>>(c->sc, a);
+    LR_CUDA(c, cudaGetLastError()); return LR_OK;
+}
+template <int C, bool TO_FILM> static int launch_render_k(lr_ctx *c, const RenderArgs &a) {
+    switch (c->sc.integ.kind) {
+        case LR_INTEGRATOR_PATH: return launch_render_t<LR_INTEGRATOR_PATH, C, TO_FILM>(c, a);
+        case LR_INTEGRATOR_VOLPATH: return launch_render_t<LR_INTEGRATOR_VOLPATH, C, TO_FILM>(c, a);
+        default: return launch_render_t<LR_INTEGRATOR_PRBVOLPATH, C, TO_FILM>(c, a);
+    }
+}
+
+static int begin_call(lr_ctx *c, const char *what) {
+    if (!c) { g_last_error = std::string(what) + ": NULL context"; return LR_ERR_INVALID_ARG; }
+    if (!c->has_scene) LR_FAIL(c, LR_ERR_NO_SCENE, "%s: no scene uploaded", what);
+    LR_CUDA(c, cudaSetDevice(c->device));
+    *c->cancel_host = 0;
+    LR_CUDA(c, cudaMemsetAsync(c->work_counter.p, 0, 8, c->stream));
+    LR_CUDA(c, cudaMemsetAsync(c->stats.p, 0, 32, c->stream));
+    LR_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    return LR_OK;
+}
+static int end_call(lr_ctx *c, uint64_t launches, bool tracking) {
+    LR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    unsigned long long h[4]; LR_CUDA(c, cudaMemcpyAsync(h, c->stats.p, 32, cudaMemcpyDeviceToHost, c->stream));
+    LR_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f; LR_CUDA(c, cudaEventElapsedTime(&ms, c->ev0, c->ev1));
+    c->st.samples = h[0]; c->st.rays = h[1]; c->st.collisions = h[2]; c->st.real_scatters = h[3];
+    c->st.launches = launches; c->st.device_ms = ms;
+    if (tracking) { c->st.tracking_ms = ms; c->st.tracking_launches = 1; }
+    if (*c->cancel_host) LR_FAIL(c, LR_ERR_CANCELLED, "render cancelled");
+    return LR_OK;
+}
+
+static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t begin, uint64_t end, float *lanes_out) {
+    PassPlan p = plan_passes(c, spp);
+    if (end == 0 && begin == 0) end = p.n_lanes;
+    if (begin > end || end > p.n_lanes) LR_FAIL(c, LR_ERR_INVALID_ARG, "lane range [%llu,%llu) outside [0,%llu)", (unsigned long long) begin, (unsigned long long) end, (unsigned long long) p.n_lanes);
+    RenderArgs a{}; a.tris_gid = c->tris_gid->as<DTri>(); a.film = c->film.as<float>(); a.lanes_out = lanes_out;
+    a.lane_begin = begin; a.lane_end = end; a.seed = seed; a.spp_per_pass = p.spp_per_pass; a.n_passes = p.n_passes; a.total_spp = spp;
+    a.work_counter = c->work_counter.as<unsigned long long>(); a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev;
+    if (begin == end) return LR_OK;
+    if (lanes_out) return c->film_channels == 5 ? launch_render_k<5, false>(c, a) : launch_render_k<4, false>(c, a);
+    return c->film_channels == 5 ? launch_render_k<5, true>(c, a) : launch_render_k<4, true>(c, a);
+}
+
+static int copy_out(lr_ctx *c, void *dst, const void *src_dev, size_t bytes, int dst_is_device) {
+    LR_CUDA(c, cudaMemcpyAsync(dst, src_dev, bytes, dst_is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, c->stream));
+    LR_CUDA(c, cudaStreamSynchronize(c->stream)); return LR_OK;
+}
+
+extern "C" {
+
+int lr_film_clear(lr_ctx *c) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    LR_CUDA(c, cudaSetDevice(c->device)); LR_CUDA(c, cudaMemsetAsync(c->film.p, 0, c->film.bytes, c->stream)); return LR_OK;
+}
+int lr_film_channels(const lr_ctx *c) { return c ? c->film_channels : 0; }
+void *lr_film_device_ptr(lr_ctx *c) { return c ? c->film.p : nullptr; }
+
+int lr_render_lanes(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t lane_begin, uint64_t lane_end) {
+    if (int r = begin_call(c, "lr_render_lanes")) return r;
+    if (spp == 0) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render_lanes: spp must be > 0");
+    if (int r = render_lanes_impl(c, seed, spp, lane_begin, lane_end, nullptr)) return r;
+    return end_call(c, 1, true);
+}
+
+int lr_film_develop(lr_ctx *c, float *out, int out_is_device) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    LR_CUDA(c, cudaSetDevice(c->device));
+    uint32_t npix = c->W * c->H; int C = c->film_channels; size_t bytes = (size_t) npix * (C - 1) * 4;
+    float *dst = out;
+    if (!out_is_device) { if (c->scratch.bytes < bytes) LR_CUDA(c, c->scratch.alloc(bytes)); dst = c->scratch.as<float>(); }
+    k_develop<<<(npix + 255) / 256, 256, 0, c->stream>>>(c->film.as<float>(), dst, npix, C);
+    LR_CUDA(c, cudaGetLastError());
+    if (!out_is_device) return copy_out(c, out, dst, bytes, 0);
+    LR_CUDA(c, cudaStreamSynchronize(c->stream)); return LR_OK;
+}
+
+int lr_render(lr_ctx *c, uint32_t seed, uint32_t spp, float *out, int out_is_device) {
+    if (int r = begin_call(c, "lr_render")) return r;
+    if (spp == 0 || !out) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render: spp must be > 0 and out non-NULL");
+    LR_CUDA(c, cudaMemsetAsync(c->film.p, 0, c->film.bytes, c->stream));
+    if (int r = render_lanes_impl(c, seed, spp, 0, 0, nullptr)) return r;
+    if (int r = end_call(c, 2, true)) return r;
+    return lr_film_develop(c, out, out_is_device);
+}
+
+int lr_film_read(lr_ctx *c, float *block, int is_device) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    LR_CUDA(c, cudaSetDevice(c->device)); return copy_out(c, block, c->film.p, c->film.bytes, is_device);
+}
+int lr_film_write(lr_ctx *c, const float *block, int is_device) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    LR_CUDA(c, cudaSetDevice(c->device));
+    LR_CUDA(c, cudaMemcpyAsync(c->film.p, block, c->film.bytes, is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    LR_CUDA(c, cudaStreamSynchronize(c->stream)); return LR_OK;
+}
+
+int lr_sample_lanes(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t lane_begin, uint64_t lane_end, float *out, int out_is_device) {
+    if (int r = begin_call(c, "lr_sample_lanes")) return r;
+    if (spp == 0 || !out || lane_end <= lane_begin) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_sample_lanes: bad arguments");
+    PassPlan p = plan_passes(c, spp); size_t bytes = (size_t) (lane_end - lane_begin) * p.n_passes * 16;
+    float *dst = out; DevBuf tmp;
+    if (!out_is_device) { LR_CUDA(c, tmp.alloc(bytes)); dst = tmp.as<float>(); }
+    if (int r = render_lanes_impl(c, seed, spp, lane_begin, lane_end, dst)) return r;
+    if (int r = end_call(c, 1, true)) return r;
+    if (!out_is_device) return copy_out(c, out, dst, bytes, 0);
+    return LR_OK;
+}
+
+int lr_render_backward(lr_ctx *c, uint32_t seed, uint32_t spp, const float *grad_in, int grad_is_device, uint64_t lane_begin, uint64_t lane_end) {
+    if (int r = begin_call(c, "lr_render_backward")) return r;
+    if (c->sc.integ.kind != LR_INTEGRATOR_PRBVOLPATH) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_render_backward: integrator is not prbvolpath");
+    if (spp == 0 || !grad_in) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render_backward: bad arguments");
+    PassPlan p = plan_passes(c, spp);
+    if (p.n_passes != 1) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_render_backward: W*H*spp exceeds 2^32 (the reference raises as well, common.py:359-364)");
+    if (lane_begin == 0 && lane_end == 0) lane_end = p.n_lanes;
+    if (lane_begin > lane_end || lane_end > p.n_lanes) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render_backward: lane range out of bounds");
+    uint32_t gc = c->film_channels - 1; size_t gbytes = (size_t) c->W * c->H * gc * 4;
+    const float *g = grad_in; DevBuf tmp;
+    if (!grad_is_device) { LR_CUDA(c, tmp.alloc(gbytes)); LR_CUDA(c, cudaMemcpyAsync(tmp.p, grad_in, gbytes, cudaMemcpyHostToDevice, c->stream)); g = tmp.as<float>(); }
+    LR_CUDA(c, cudaMemsetAsync(c->weight_img.p, 0, c->weight_img.bytes, c->stream));
+    k_weight_image<<<c->n_sm * 8, 256, 0, c->stream>>>(c->sc, c->weight_img.as<float>(), p.n_lanes, seed, spp);
+    LR_CUDA(c, cudaGetLastError());
+    RenderArgs a{}; a.tris_gid = c->tris_gid->as<DTri>(); a.lane_begin = lane_begin; a.lane_end = lane_end; a.seed = seed;
+    a.spp_per_pass = spp; a.n_passes = 1; a.total_spp = spp; a.work_counter = c->work_counter.as<unsigned long long>();
+    a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev; a.grad_in = g; a.weight_img = c->weight_img.as<float>(); a.grad_channels = gc;
+    if (lane_end > lane_begin) {
+        int grid; if (int r = grid_for(c, k_backward, 128, grid)) return r;
+        k_backward<<<grid, 128, 0, c->stream>>>(c->sc, a);
+        LR_CUDA(c, cudaGetLastError());
+    }
+    return end_call(c, 2, true);
+}
+
+int lr_grid_update(lr_ctx *c, uint32_t grid, const float *data, int is_device) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    if (grid >= c->h_grids.size() || !data) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_grid_update: bad grid index");
+    LR_CUDA(c, cudaSetDevice(c->device));
+    LR_CUDA(c, cudaMemcpyAsync((void *) c->h_grids[grid].data, data, c->grid_floats[grid] * 4, is_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+    if (int r = refresh_grid_derived(c, grid)) return r;
+    LR_CUDA(c, cudaStreamSynchronize(c->stream)); return LR_OK;
+}
+int lr_grid_grad_zero(lr_ctx *c, uint32_t grid) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    if (grid >= c->h_grids.size() || !c->h_grids[grid].grad) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_grid_grad_zero: grid %u is not differentiable", grid);
+    LR_CUDA(c, cudaSetDevice(c->device)); LR_CUDA(c, cudaMemsetAsync(c->h_grids[grid].grad, 0, c->grid_floats[grid] * 4, c->stream)); return LR_OK;
+}
+int lr_grid_grad_read(lr_ctx *c, uint32_t grid, float *out, int is_device) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    if (grid >= c->h_grids.size() || !c->h_grids[grid].grad || !out) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_grid_grad_read: grid %u is not differentiable", grid);
+    LR_CUDA(c, cudaSetDevice(c->device)); return copy_out(c, out, c->h_grids[grid].grad, c->grid_floats[grid] * 4, is_device);
+}
+void *lr_grid_grad_device_ptr(lr_ctx *c, uint32_t grid) { return (c && c->has_scene && grid < c->h_grids.size()) ? c->h_grids[grid].grad : nullptr; }
+size_t lr_grid_size(const lr_ctx *c, uint32_t grid) { return (c && grid < c->grid_floats.size()) ? c->grid_floats[grid] : 0; }
+
+int lr_ray_intersect(lr_ctx *c, const float *rays, uint64_t n, float *hits) {
+    if (!c || !c->has_scene) return LR_ERR_NO_SCENE;
+    if (!rays || !hits) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_ray_intersect: NULL buffers");
+    if (n == 0) return LR_OK;
+    LR_CUDA(c, cudaSetDevice(c->device));
+    DevBuf dr, dh; LR_CUDA(c, dr.alloc(n * 32)); LR_CUDA(c, dh.alloc(n * 16));
+    LR_CUDA(c, cudaMemcpyAsync(dr.p, rays, n * 32, cudaMemcpyHostToDevice, c->stream));
+    k_ray_probe<<<(unsigned) ((n + 127) / 128), 128, 0, c->stream>>>(c->sc, dr.as<float>(), n, dh.as<float>());
+    LR_CUDA(c, cudaGetLastError());
+    return copy_out(c, hits, dh.p, n * 16, 0);
+}
+
+int lr_stats_get(lr_ctx *c, lr_stats *out) { if (!c || !out) return LR_ERR_INVALID_ARG; *out = c->st; return LR_OK; }
+
+} // extern "C"

@@ -1,0 +1,383 @@
+"""Scene description -> POD `lr_scene` (the host half of the drop-in boundary).
+
+Mirrors the subset of `mi.load_dict` (src/core/parser.cpp + plugin constructors)
+that the hot path needs: plugin names, property names and defaults follow the
+reference plugins cited next to each builder.  The result owns every numpy
+buffer the POD points into.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import numpy as np
+
+from . import _capi as K
+from . import shapes as S
+from .transforms import ScalarTransform4f, parse_fov, perspective_projection
+from .volume_io import read_vol
+
+
+def _rgb(v, default=None):
+    if v is None:
+        v = default
+    if isinstance(v, dict):
+        t = v.get("type", "rgb")
+        if t in ("rgb", "srgb", "uniform"):
+            v = v["value"]
+        else:
+            raise NotImplementedError(f"texture/spectrum type '{t}' is outside the hot path (constant rgb only)")
+    a = np.asarray(v, dtype=np.float32).reshape(-1)
+    if a.size == 1:
+        a = np.repeat(a, 3)
+    if a.size != 3:
+        raise ValueError("expected a float or an RGB triple")
+    return a
+
+
+def _flt(v, default=None):
+    if v is None:
+        v = default
+    if isinstance(v, dict):
+        v = v["value"]
+    return float(np.asarray(v).reshape(-1)[0])
+
+
+def _f16(m):
+    return (C.c_float * 16)(*np.asarray(m, dtype=np.float32).reshape(-1))
+
+
+def _f3(v):
+    return (C.c_float * 3)(*np.asarray(v, dtype=np.float32).reshape(-1)[:3])
+
+
+def _xf(d, key="to_world"):
+    t = d.get(key)
+    if t is None:
+        return ScalarTransform4f()
+    if isinstance(t, ScalarTransform4f):
+        return t
+    return ScalarTransform4f(np.asarray(t, dtype=np.float64))
+
+
+_IOR = {"vacuum": 1.0, "air": 1.000277, "water": 1.3330, "bk7": 1.5046, "diamond": 2.419, "glass": 1.5046}
+
+
+def _ior(v, default):
+    if v is None:
+        v = default
+    if isinstance(v, str):
+        return _IOR[v.lower()]
+    return float(v)
+
+
+class Scene:
+    """Flattened scene + the context handle of the backend it was uploaded to."""
+
+    def __init__(self, d: dict, base_dir: str = "."):
+        if d.get("type", "scene") != "scene":
+            raise ValueError("load_dict(): top-level dictionary must be of type 'scene'")
+        self.base_dir = base_dir
+        self._keep = []                       # numpy buffers referenced by the POD
+        self.meshes, self.bsdfs, self.media, self.grids, self.emitters = [], [], [], [], []
+        self._bsdf_ids, self._medium_ids = {}, {}
+        self.grid_arrays = []                 # numpy views of grid data, index-aligned with self.grids
+        self.param_keys = {}                  # 'shape.interior_medium.sigma_t.data' -> grid index
+        self.sensor = None; self.integrator = None
+        self.spp = 4
+        self._named = {k: v for k, v in d.items() if isinstance(v, dict)}
+        # first pass: named BSDFs / media so that {'type':'ref','id':...} resolves
+        for name, v in self._named.items():
+            t = v.get("type")
+            if t in ("diffuse", "roughdielectric", "principled", "null", "dielectric"):
+                self._bsdf_ids[name] = self._add_bsdf(v)
+            elif t in ("homogeneous", "heterogeneous"):
+                self._medium_ids[name] = self._add_medium(v, name)
+        for name, v in self._named.items():
+            t = v.get("type")
+            if t in ("rectangle", "cube", "obj", "sphere", "mesh"):
+                self._add_shape(v, name)
+            elif t in ("constant", "envmap"):
+                self._add_env(v)
+            elif t == "perspective":
+                self._sensor_dict = v
+            elif t in ("path", "volpath", "prbvolpath"):
+                self._integrator_dict = v
+        if not hasattr(self, "_sensor_dict"):
+            raise ValueError("scene has no 'perspective' sensor")
+        self._build_sensor(self._sensor_dict)
+        self._build_integrator(getattr(self, "_integrator_dict", {"type": "path"}))
+        self._ctx = None
+
+    # ---- BSDFs ------------------------------------------------------------
+    def _resolve_bsdf(self, v):
+        if v is None:
+            return self._add_bsdf({"type": "diffuse"})        # Shape default BSDF (src/render/shape.cpp)
+        if v.get("type") == "ref":
+            return self._bsdf_ids[v["id"]]
+        return self._add_bsdf(v)
+
+    def _add_bsdf(self, v):
+        b = K.lr_bsdf(); t = v["type"]
+        b.sample_visible = 1; b.eta = 1.0
+        b.reflectance = _f3([1, 1, 1]); b.transmittance = _f3([1, 1, 1])
+        if t == "diffuse":                                     # diffuse.cpp: reflectance default 0.5
+            b.kind = K.BSDF_DIFFUSE; b.reflectance = _f3(_rgb(v.get("reflectance"), 0.5))
+        elif t == "null":
+            b.kind = K.BSDF_NULL
+        elif t in ("dielectric", "roughdielectric"):           # roughdielectric.cpp:165-220
+            b.kind = K.BSDF_DIELECTRIC if t == "dielectric" else K.BSDF_ROUGHDIELECTRIC
+            int_ior = _ior(v.get("int_ior"), "bk7"); ext_ior = _ior(v.get("ext_ior"), "air")
+            if int_ior < 0 or ext_ior < 0 or int_ior == ext_ior:
+                raise RuntimeError("The interior and exterior indices of refraction must be positive and differ!")
+            b.eta = int_ior / ext_ior
+            b.reflectance = _f3(_rgb(v.get("specular_reflectance"), 1.0))
+            b.transmittance = _f3(_rgb(v.get("specular_transmittance"), 1.0))
+            if t == "roughdielectric":
+                distr = str(v.get("distribution", "beckmann")).lower()
+                if distr not in ("beckmann", "ggx"):
+                    raise RuntimeError(f'Specified an invalid distribution "{distr}", must be "beckmann" or "ggx"!')
+                b.mf_kind = K.MF_BECKMANN if distr == "beckmann" else K.MF_GGX
+                b.sample_visible = 1 if v.get("sample_visible", True) else 0
+                if "alpha_u" in v or "alpha_v" in v:
+                    b.alpha_u = _flt(v["alpha_u"]); b.alpha_v = _flt(v["alpha_v"])
+                else:
+                    b.alpha_u = b.alpha_v = _flt(v.get("alpha"), 0.1)
+        elif t == "principled":                                # principled.cpp:190-238
+            b.kind = K.BSDF_PRINCIPLED
+            b.reflectance = _f3(_rgb(v.get("base_color"), 0.5)); b.roughness = _flt(v.get("roughness"), 0.5)
+            flags = 0
+            def opt(name, bit, default=0.0):
+                nonlocal flags
+                val = _flt(v.get(name), default)
+                if name in v and not (isinstance(v[name], (int, float)) and float(v[name]) == 0.0):   # get_flag()
+                    flags |= bit
+                return val
+            b.anisotropic = opt("anisotropic", K.PR_HAS_ANISOTROPIC); b.spec_trans = opt("spec_trans", K.PR_HAS_SPEC_TRANS)
+            b.sheen = opt("sheen", K.PR_HAS_SHEEN); b.sheen_tint = opt("sheen_tint", K.PR_HAS_SHEEN_TINT)
+            b.flatness = opt("flatness", K.PR_HAS_FLATNESS); b.spec_tint = opt("spec_tint", K.PR_HAS_SPEC_TINT)
+            b.metallic = opt("metallic", K.PR_HAS_METALLIC); b.clearcoat = opt("clearcoat", K.PR_HAS_CLEARCOAT)
+            b.clearcoat_gloss = _flt(v.get("clearcoat_gloss"), 0.0)
+            b.main_spec_srate = _flt(v.get("main_specular_sampling_rate"), 1.0)
+            b.clearcoat_srate = _flt(v.get("clearcoat_sampling_rate"), 1.0)
+            b.diff_refl_srate = _flt(v.get("diffuse_reflectance_sampling_rate"), 1.0)
+            has_st = bool(flags & K.PR_HAS_SPEC_TRANS)
+            if "eta" in v and "specular" in v:
+                raise RuntimeError('Specified an invalid index of refraction property, either use "eta" or "specular" !')
+            if "eta" in v:
+                flags |= K.PR_ETA_SPECULAR; eta = np.float32(v["eta"])
+                if has_st and eta == 1:
+                    eta = np.float32(1.001)
+                b.eta = float(eta)
+            else:
+                spec = np.float32(v.get("specular", 0.5))
+                if has_st and spec == 0:
+                    spec = np.float32(1e-3)
+                b.specular = float(spec)
+                b.eta = float(np.float32(2.0) * (np.float32(1.0) / (np.float32(1.0) - np.sqrt(np.float32(0.08) * spec))) - np.float32(1.0))
+            b.flags = flags
+        else:
+            raise NotImplementedError(f"BSDF plugin '{t}' is outside the hot path")
+        self.bsdfs.append(b)
+        return len(self.bsdfs) - 1
+
+    # ---- volumes / media ----------------------------------------------------
+    def _add_grid(self, v, differentiable=False):
+        """gridvolume (src/volumes/grid.cpp:164-307): data [z][y][x][c]."""
+        if "filename" in v:
+            data = read_vol(os.path.join(self.base_dir, v["filename"]))
+        else:
+            data = np.asarray(v.get("grid", v.get("data")), dtype=np.float32)
+        if data.ndim == 3:
+            data = data[..., None]
+        data = np.ascontiguousarray(data, dtype=np.float32)
+        g = K.lr_grid(); rz, ry, rx, ch = data.shape
+        if ch not in (1, 3):
+            raise RuntimeError("gridvolume: only 1 or 3 channels are supported on this path")
+        g.res = (C.c_uint32 * 3)(rx, ry, rz); g.channels = ch
+        to_world = _xf(v); to_local = to_world.inverse()
+        g.to_local = _f16(to_local.matrix)
+        corners = np.array([[x, y, z] for x in (0, 1) for y in (0, 1) for z in (0, 1)], dtype=np.float64)
+        wc = to_world.transform_affine(corners).astype(np.float32)
+        g.bbox_min = _f3(wc.min(0)); g.bbox_max = _f3(wc.max(0))
+        ft = str(v.get("filter_type", "trilinear")).lower(); wm = str(v.get("wrap_mode", "clamp")).lower()
+        g.filter = {"nearest": K.FILTER_NEAREST, "trilinear": K.FILTER_TRILINEAR}[ft]
+        g.wrap = {"repeat": K.WRAP_REPEAT, "mirror": K.WRAP_MIRROR, "clamp": K.WRAP_CLAMP}[wm]
+        g.max_value = float(v["max_value"]) if "max_value" in v else -1.0
+        g.differentiable = 1 if differentiable else 0
+        g.data = data.ctypes.data_as(K.c_float_p)
+        self._keep.append(data); self.grids.append(g); self.grid_arrays.append(data)
+        return len(self.grids) - 1
+
+    def _add_medium(self, v, name="medium"):
+        """homogeneous.cpp:137-181 / heterogeneous.cpp:155-201 / medium.cpp:16-32."""
+        m = K.lr_medium(); t = v["type"]
+        m.kind = K.MEDIUM_HOMOGENEOUS if t == "homogeneous" else K.MEDIUM_HETEROGENEOUS
+        m.scale = _flt(v.get("scale"), 1.0)
+        m.sample_emitters = 1 if v.get("sample_emitters", True) else 0
+        m.has_spectral_extinction = 1 if v.get("has_spectral_extinction", True) else 0
+        ph = v.get("phase", {"type": "isotropic"})
+        if ph["type"] == "isotropic":
+            m.phase = K.PHASE_ISOTROPIC
+        elif ph["type"] == "hg":
+            m.phase = K.PHASE_HG; m.phase_g = _flt(ph.get("g"), 0.8)
+            if not (-1 < m.phase_g < 1):
+                raise RuntimeError("The asymmetry parameter must lie in the interval (-1, 1)!")
+        else:
+            raise NotImplementedError(f"phase function '{ph['type']}' is outside the hot path")
+        m.sigma_t_grid = -1; m.albedo_grid = -1
+        m.sigma_t_const = _f3([1, 1, 1]); m.albedo_const = _f3([0.75] * 3)
+        for key, dst_grid, dst_const, default in (("sigma_t", "sigma_t_grid", "sigma_t_const", 1.0),
+                                                  ("albedo", "albedo_grid", "albedo_const", 0.75)):
+            val = v.get(key, default)
+            if isinstance(val, dict) and val.get("type") == "gridvolume":
+                if t == "homogeneous":
+                    raise RuntimeError("homogeneous medium: grid volumes are not supported, use 'heterogeneous'")
+                gi = self._add_grid(val, differentiable=(key == "sigma_t"))
+                setattr(m, dst_grid, gi)
+                self.param_keys[f"{name}.{key}.data"] = gi
+            elif isinstance(val, dict) and val.get("type") == "constvolume":
+                setattr(m, dst_const, _f3(_rgb(val.get("value"), default)))
+            else:
+                setattr(m, dst_const, _f3(_rgb(val, default)))
+        if t == "heterogeneous" and m.sigma_t_grid < 0:
+            # constant sigma_t inside a heterogeneous medium: 1-voxel... represent with a 2^3 grid
+            c = _rgb(v.get("sigma_t", 1.0))
+            gi = self._add_grid({"grid": np.full((2, 2, 2, 3), 1.0, dtype=np.float32) * c})
+            m.sigma_t_grid = gi
+        self.media.append(m)
+        return len(self.media) - 1
+
+    def _resolve_medium(self, v, name):
+        if v is None:
+            return -1
+        if v.get("type") == "ref":
+            return self._medium_ids[v["id"]]
+        return self._add_medium(v, name)
+
+    # ---- shapes ---------------------------------------------------------------
+    def _add_shape(self, v, name):
+        t = v["type"]; to_world = _xf(v)
+        if t == "rectangle":
+            md = S.rectangle(to_world)
+        elif t == "cube":
+            md = S.cube(to_world)
+        elif t == "sphere":
+            md = S.icosphere(to_world, int(v.get("subdivisions", 5)), v.get("center", (0, 0, 0)), float(v.get("radius", 1.0)))
+        elif t == "obj":
+            md = S.load_obj(os.path.join(self.base_dir, v["filename"]), to_world, bool(v.get("face_normals", False)))
+        else:  # 'mesh': raw arrays
+            md = S.MeshData(to_world.transform_affine(np.asarray(v["positions"], dtype=np.float64)), v["indices"],
+                            None if v.get("normals") is None else S._xf_normals(to_world, v["normals"]), v.get("texcoords"))
+        m = K.lr_mesh()
+        m.positions = md.positions.ctypes.data_as(K.c_float_p); m.indices = md.indices.ctypes.data_as(K.c_uint32_p)
+        m.normals = md.normals.ctypes.data_as(K.c_float_p) if md.normals is not None else None
+        m.texcoords = md.texcoords.ctypes.data_as(K.c_float_p) if md.texcoords is not None else None
+        m.n_vertices = md.positions.shape[0]; m.n_faces = md.indices.shape[0]
+        m.bsdf = self._resolve_bsdf(v.get("bsdf"))
+        m.interior_medium = self._resolve_medium(v.get("interior"), f"{name}.interior_medium")
+        m.exterior_medium = self._resolve_medium(v.get("exterior"), f"{name}.exterior_medium")
+        m.emitter = -1; m.flip_normals = 0
+        self._keep.append(md)
+        mesh_id = len(self.meshes)
+        em = v.get("emitter")
+        if em is not None:
+            if em["type"] != "area":
+                raise NotImplementedError("only 'area' emitters can be attached to shapes")
+            e = K.lr_emitter(); e.kind = K.EMITTER_AREA; e.mesh = mesh_id
+            e.radiance = _f3(_rgb(em.get("radiance"), 1.0)); e.scale = 1.0
+            if t == "rectangle":
+                o, eu, ev, n, inv_area = S.rectangle_emitter_params(to_world)
+                e.is_rectangle = 1; e.rect_origin = _f3(o); e.rect_edge_u = _f3(eu); e.rect_edge_v = _f3(ev)
+                e.rect_normal = _f3(n); e.inv_area = inv_area
+            m.emitter = len(self.emitters); self.emitters.append(e)
+        self.meshes.append(m)
+
+    def _add_env(self, v):
+        e = K.lr_emitter(); e.mesh = -1; e.scale = 1.0
+        if v["type"] == "constant":
+            e.kind = K.EMITTER_CONSTANT; e.radiance = _f3(_rgb(v.get("radiance"), 1.0))
+        else:                                                   # envmap.cpp:113-232
+            e.kind = K.EMITTER_ENVMAP
+            if "filename" in v:
+                from .image_io import read_image_rgb
+                px = read_image_rgb(os.path.join(self.base_dir, v["filename"]))
+            else:
+                px = np.asarray(v["bitmap"], dtype=np.float32)
+            px = np.ascontiguousarray(px[..., :3], dtype=np.float32)
+            e.height, e.width = px.shape[0], px.shape[1]
+            e.pixels = px.ctypes.data_as(K.c_float_p); self._keep.append(px)
+            e.scale = _flt(v.get("scale"), 1.0)
+            e.to_world = _f16(_xf(v).matrix)
+        self.emitters.append(e)
+
+    # ---- sensor / film / sampler / integrator ---------------------------------
+    def _build_sensor(self, v):
+        """perspective.cpp + hdrfilm.cpp + independent.cpp property names."""
+        s = K.lr_sensor(); film = v.get("film", {})
+        W = int(film.get("width", 768)); H = int(film.get("height", 576))
+        to_world = _xf(v)
+        if to_world.has_scale():
+            raise RuntimeError("Scale factors in the camera-to-world transformation are not allowed!")
+        near = float(v.get("near_clip", 1e-2)); far = float(v.get("far_clip", 1e4))
+        fov_x = parse_fov(float(v.get("fov", 45.0)) if "fov" in v else 39.5977527, str(v.get("fov_axis", "x")), W / H)
+        c2s = perspective_projection((W, H), (W, H), (0, 0), fov_x, near, far)
+        s.to_world = _f16(to_world.matrix); s.sample_to_camera = _f16(c2s.inverse().matrix)
+        s.near_clip = near; s.far_clip = far; s.film_width = W; s.film_height = H
+        rf = film.get("rfilter", {"type": "gaussian"}); rt = rf.get("type", "gaussian")
+        if rt == "box":
+            s.rfilter = K.RFILTER_BOX; s.rfilter_radius = 0.5
+        elif rt == "tent":
+            s.rfilter = K.RFILTER_TENT; s.rfilter_radius = float(rf.get("radius", 1.0))
+        elif rt == "gaussian":
+            s.rfilter = K.RFILTER_GAUSSIAN; s.rfilter_stddev = float(rf.get("stddev", 0.5)); s.rfilter_radius = 4 * s.rfilter_stddev
+        else:
+            raise NotImplementedError(f"rfilter '{rt}' is outside the hot path")
+        pf = str(film.get("pixel_format", "rgb")).lower()
+        if pf not in ("rgb", "rgba"):
+            raise NotImplementedError("hdrfilm pixel_format must be rgb or rgba on this path")
+        s.has_alpha = 1 if pf == "rgba" else 0
+        s.medium = self._resolve_medium(v.get("medium"), "sensor.medium")
+        smp = v.get("sampler", {"type": "independent"})
+        if smp.get("type", "independent") != "independent":
+            raise NotImplementedError("only the 'independent' sampler is on the hot path")
+        self.spp = int(smp.get("sample_count", 4)); self.base_seed = int(smp.get("seed", 0))
+        self.sensor = s
+
+    def _build_integrator(self, v):
+        i = K.lr_integrator()
+        i.kind = {"path": K.INTEGRATOR_PATH, "volpath": K.INTEGRATOR_VOLPATH, "prbvolpath": K.INTEGRATOR_PRBVOLPATH}[v["type"]]
+        md = int(v.get("max_depth", 6 if v["type"] == "prbvolpath" else -1))
+        if md < 0 and md != -1:
+            raise RuntimeError('"max_depth" must be set to -1 (infinite) or a value >= 0')
+        i.max_depth = md; i.rr_depth = int(v.get("rr_depth", 5))
+        if i.rr_depth <= 0:
+            raise RuntimeError('"rr_depth" must be set to a value greater than zero!')
+        i.hide_emitters = 1 if v.get("hide_emitters", False) else 0
+        i.tracking = {"reference": K.TRACKING_REFERENCE, "dda": K.TRACKING_DDA}[str(v.get("tracking", "reference")).lower()]
+        i.base_seed = self.base_seed; i.majorant_cell = int(v.get("majorant_cell", 0))
+        self.integrator = i
+
+    # ---- POD ---------------------------------------------------------------------
+    def pod(self) -> K.lr_scene:
+        sc = K.lr_scene(); sc.api_version = 1
+        def arr(T, lst):
+            a = (T * max(len(lst), 1))(*lst); self._keep.append(a); return a
+        sc.n_meshes, sc.n_bsdfs, sc.n_media = len(self.meshes), len(self.bsdfs), len(self.media)
+        sc.n_grids, sc.n_emitters = len(self.grids), len(self.emitters)
+        sc.meshes = arr(K.lr_mesh, self.meshes); sc.bsdfs = arr(K.lr_bsdf, self.bsdfs); sc.media = arr(K.lr_medium, self.media)
+        sc.grids = arr(K.lr_grid, self.grids); sc.emitters = arr(K.lr_emitter, self.emitters)
+        sc.sensor = self.sensor; sc.integrator = self.integrator
+        return sc
+
+    @property
+    def film_size(self):
+        return int(self.sensor.film_width), int(self.sensor.film_height)
+
+    @property
+    def out_channels(self):
+        return 4 if self.sensor.has_alpha else 3
+
+
+def load_dict(d: dict, base_dir: str = ".") -> Scene:
+    """`mi.load_dict` for the hot-path plugin subset."""
+    return Scene(d, base_dir)

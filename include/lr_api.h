@@ -126,7 +126,11 @@ typedef struct lr_bsdf {
     float roughness, anisotropic, metallic, spec_trans, specular, spec_tint;
     float sheen, sheen_tint, flatness, clearcoat, clearcoat_gloss;
     float diff_refl_srate, main_spec_srate, clearcoat_srate;
-    float reserved[4];
+    /* `reflectance` texture: 0 = constant, 1 = checkerboard (src/textures/checkerboard.cpp:70-89):
+       color0 = reflectance, color1 = tex_color1, uv' = tex_to_uv (2x3 affine, row-major) * (u, v, 1) */
+    uint32_t tex_kind;
+    float tex_color1[3];
+    float tex_to_uv[6];
 } lr_bsdf;
 
 #define LR_PR_HAS_ANISOTROPIC (1u << 0)

@@ -47,7 +47,7 @@ class lr_bsdf(C.Structure):
                 ("specular", C.c_float), ("spec_tint", C.c_float), ("sheen", C.c_float), ("sheen_tint", C.c_float),
                 ("flatness", C.c_float), ("clearcoat", C.c_float), ("clearcoat_gloss", C.c_float),
                 ("diff_refl_srate", C.c_float), ("main_spec_srate", C.c_float), ("clearcoat_srate", C.c_float),
-                ("reserved", C.c_float * 4)]
+                ("tex_kind", C.c_uint32), ("tex_color1", C.c_float * 3), ("tex_to_uv", C.c_float * 6)]
 
 
 class lr_grid(C.Structure):

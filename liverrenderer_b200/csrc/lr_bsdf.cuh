@@ -163,9 +163,17 @@ LR_DEV void calc_dist_params(float anisotropic, float roughness, bool has_aniso,
 struct PrParams { float anisotropic, roughness, spec_trans, metallic, clearcoat, flatness, sheen, brdf, bsdf; };
 
 struct BSDF {
-    const lr_bsdf &b;
-    LR_DEV explicit BSDF(const lr_bsdf &b_) : b(b_) {}
-    LR_DEV V3 refl() const { return mk3(b.reflectance[0], b.reflectance[1], b.reflectance[2]); }
+    const lr_bsdf &b; V2 uv;
+    LR_DEV BSDF(const lr_bsdf &b_, V2 uv_) : b(b_), uv(uv_) {}
+    LR_DEV V3 refl() const {
+        if (b.tex_kind == 1) {                      // checkerboard (src/textures/checkerboard.cpp:70-89)
+            float u = fmaf(b.tex_to_uv[0], uv.x, fmaf(b.tex_to_uv[1], uv.y, b.tex_to_uv[2])),
+                  v = fmaf(b.tex_to_uv[3], uv.x, fmaf(b.tex_to_uv[4], uv.y, b.tex_to_uv[5]));
+            bool mx = u - floorf(u) > .5f, my = v - floorf(v) > .5f;
+            if (mx != my) return mk3(b.tex_color1[0], b.tex_color1[1], b.tex_color1[2]);
+        }
+        return mk3(b.reflectance[0], b.reflectance[1], b.reflectance[2]);
+    }
     LR_DEV V3 trans() const { return mk3(b.transmittance[0], b.transmittance[1], b.transmittance[2]); }
     LR_DEV bool has(uint32_t f) const { return (b.flags & f) != 0; }
     LR_DEV uint32_t flags() const {

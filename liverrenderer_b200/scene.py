@@ -121,7 +121,15 @@ class Scene:
         b.sample_visible = 1; b.eta = 1.0
         b.reflectance = _f3([1, 1, 1]); b.transmittance = _f3([1, 1, 1])
         if t == "diffuse":                                     # diffuse.cpp: reflectance default 0.5
-            b.kind = K.BSDF_DIFFUSE; b.reflectance = _f3(_rgb(v.get("reflectance"), 0.5))
+            b.kind = K.BSDF_DIFFUSE
+            r = v.get("reflectance")
+            if isinstance(r, dict) and r.get("type") == "checkerboard":     # src/textures/checkerboard.cpp
+                b.tex_kind = 1
+                b.reflectance = _f3(_rgb(r.get("color0"), 0.4)); b.tex_color1 = _f3(_rgb(r.get("color1"), 0.2))
+                m = _xf(r, "to_uv").matrix
+                b.tex_to_uv = (C.c_float * 6)(m[0, 0], m[0, 1], m[0, 3], m[1, 0], m[1, 1], m[1, 3])
+            else:
+                b.reflectance = _f3(_rgb(r, 0.5))
         elif t == "null":
             b.kind = K.BSDF_NULL
         elif t in ("dielectric", "roughdielectric"):           # roughdielectric.cpp:165-220

@@ -196,9 +196,17 @@ inline V3 lerp3(V3 a, V3 b, float t) { return {lerp(a.x, b.x, t), lerp(a.y, b.y,
 
 /* ---- BSDF dispatch --------------------------------------------------------- */
 struct BSDF {
-    const lr_bsdf &b;
-    explicit BSDF(const lr_bsdf &b_) : b(b_) {}
-    V3 refl() const { return {b.reflectance[0], b.reflectance[1], b.reflectance[2]}; }
+    const lr_bsdf &b; V2 uv;
+    explicit BSDF(const lr_bsdf &b_, V2 uv_ = {0.f, 0.f}) : b(b_), uv(uv_) {}
+    V3 refl() const {
+        if (b.tex_kind == 1) {                      /* checkerboard (src/textures/checkerboard.cpp:70-89) */
+            float u = fmaf(b.tex_to_uv[0], uv.x, fmaf(b.tex_to_uv[1], uv.y, b.tex_to_uv[2])),
+                  v = fmaf(b.tex_to_uv[3], uv.x, fmaf(b.tex_to_uv[4], uv.y, b.tex_to_uv[5]));
+            bool mx = u - floorf(u) > .5f, my = v - floorf(v) > .5f;
+            if (mx != my) return {b.tex_color1[0], b.tex_color1[1], b.tex_color1[2]};
+        }
+        return {b.reflectance[0], b.reflectance[1], b.reflectance[2]};
+    }
     V3 trans() const { return {b.transmittance[0], b.transmittance[1], b.transmittance[2]}; }
     bool has(uint32_t f) const { return (b.flags & f) != 0; }
 

@@ -327,7 +327,12 @@ class Scene:
         if to_world.has_scale():
             raise RuntimeError("Scale factors in the camera-to-world transformation are not allowed!")
         near = float(v.get("near_clip", 1e-2)); far = float(v.get("far_clip", 1e4))
-        fov_x = parse_fov(float(v.get("fov", 45.0)) if "fov" in v else 39.5977527, str(v.get("fov_axis", "x")), W / H)
+        if "fov" in v:
+            fov_x = parse_fov(float(v["fov"]), str(v.get("fov_axis", "x")), W / H)
+        else:                                                   # focal_length default "50mm" (src/render/sensor.cpp:160-174)
+            fl = float(str(v.get("focal_length", "50mm")).replace("mm", ""))
+            import math
+            fov_x = parse_fov(2.0 * math.degrees(math.atan(math.sqrt(36.0 * 36 + 24 * 24) / (2.0 * fl))), "diagonal", W / H)
         c2s = perspective_projection((W, H), (W, H), (0, 0), fov_x, near, far)
         s.to_world = _f16(to_world.matrix); s.sample_to_camera = _f16(c2s.inverse().matrix)
         s.near_clip = near; s.far_clip = far; s.film_width = W; s.film_height = H

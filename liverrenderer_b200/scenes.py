@@ -83,7 +83,8 @@ def _liver_sensor(res, spp, rgba=True):
 
 def _liver_env():
     return {"type": "envmap", "bitmap": cavity_envmap(), "scale": 2.5,
-            "to_world": T().rotate([0.57735, 0.57735, 0.57735], 180).scale(1).translate([-3, 3, 4])}
+            # XML order rotate -> scale -> translate (scene.xml:93-101): first listed applied first => T * S * R
+            "to_world": T().translate([-3, 3, 4]).scale(1).rotate([0.57735, 0.57735, 0.57735], 180)}
 
 
 def liver_single_mesh(res: int = 1080, spp: int = 1024, grid_res: int = 256, phase: str = "isotropic",

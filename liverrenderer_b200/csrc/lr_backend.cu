@@ -34,13 +34,14 @@ struct lr_ctx {
     std::vector<DGrid> h_grids; DevBuf *d_grids = nullptr;
     std::vector<DMedium> h_media; DevBuf *d_media = nullptr;
     std::vector<size_t> grid_floats;
+    std::vector<float> grid_fixed_max;              // `max_value` override (grid.cpp:303-306, 324), < 0: none
     int film_channels = 4; uint32_t W = 0, H = 0;
     int *cancel_host = nullptr; int *cancel_dev = nullptr;      // mapped pinned flag polled by the kernels
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     lr_stats st{};
     int blocks_per_sm[8] = {0}; int n_sm = 148;
     DevBuf *newbuf() { pool.push_back(new DevBuf()); return pool.back(); }
-    void free_scene() { for (auto *b : pool) delete b; pool.clear(); h_grids.clear(); h_media.clear(); grid_floats.clear(); has_scene = false; }
+    void free_scene() { for (auto *b : pool) delete b; pool.clear(); h_grids.clear(); h_media.clear(); grid_floats.clear(); grid_fixed_max.clear(); has_scene = false; }
 };
 
 #define LR_FAIL(ctx, code, ...) do { char _b[512]; snprintf(_b, sizeof _b, __VA_ARGS__); if (ctx) (ctx)->err = _b; g_last_error = _b; return (code); } while (0)
@@ -194,7 +195,7 @@ static int refresh_grid_derived(lr_ctx *c, uint32_t gi) {
     k_grid_max<<<std::min<size_t>((n + 255) / 256, 1184), 256, 0, c->stream>>>(g.data, n, c->scratch.as<float>());
     float mx = 0.f; LR_CUDA(c, cudaMemcpyAsync(&mx, c->scratch.p, 4, cudaMemcpyDeviceToHost, c->stream));
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
-    g.maxv = mx;
+    g.maxv = (gi < c->grid_fixed_max.size() && c->grid_fixed_max[gi] >= 0.f) ? c->grid_fixed_max[gi] : mx;
     int nc = g.mx * g.my * g.mz;
     k_majorant_grid<<<(nc + 127) / 128, 128, 0, c->stream>>>(g.data, g.rx, g.ry, g.rz, g.ch, g.cell, g.mx, g.my, g.mz, (float *) g.maj);
     LR_CUDA(c, cudaGetLastError());

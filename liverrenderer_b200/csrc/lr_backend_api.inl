@@ -64,7 +64,8 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     if (int r = build_lbvh(c, tris, lo, hi)) return r;
 
     // ---- grids ----
-    c->h_grids.resize(s->n_grids); c->grid_floats.resize(s->n_grids);
+    c->h_grids.resize(s->n_grids); c->grid_floats.resize(s->n_grids); c->grid_fixed_max.assign(s->n_grids, -1.f);
+    for (uint32_t i = 0; i < s->n_grids; ++i) c->grid_fixed_max[i] = s->grids[i].max_value;
     for (uint32_t i = 0; i < s->n_grids; ++i) {
         const lr_grid &g = s->grids[i]; DGrid &d = c->h_grids[i]; memset(&d, 0, sizeof d);
         if (g.channels != 1 && g.channels != 3) LR_FAIL(c, LR_ERR_UNSUPPORTED, "grid %u: channels must be 1 or 3", i);
@@ -92,12 +93,6 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     if (s->n_media) LR_CUDA(c, cudaMemcpyAsync(c->d_media->p, c->h_media.data(), s->n_media * sizeof(DMedium), cudaMemcpyHostToDevice, c->stream));
     for (uint32_t i = 0; i < s->n_grids; ++i) {
         if (int r = refresh_grid_derived(c, i)) return r;
-        if (s->grids[i].max_value >= 0.f) {                     // `max_value` override (grid.cpp:303-306)
-            c->h_grids[i].maxv = s->grids[i].max_value;
-            for (auto &m : c->h_media) if (m.m.kind == LR_MEDIUM_HETEROGENEOUS && m.m.sigma_t_grid == (int) i) m.max_density = m.m.scale * s->grids[i].max_value;
-            LR_CUDA(c, cudaMemcpyAsync(c->d_grids->p, c->h_grids.data(), c->h_grids.size() * sizeof(DGrid), cudaMemcpyHostToDevice, c->stream));
-            LR_CUDA(c, cudaMemcpyAsync(c->d_media->p, c->h_media.data(), c->h_media.size() * sizeof(DMedium), cudaMemcpyHostToDevice, c->stream));
-        }
     }
 
     // ---- emitters ----

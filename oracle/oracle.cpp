@@ -60,7 +60,8 @@ static void build_scene(OrcScene &o, const lr_scene *s) {
         gr.data.assign(g.data, g.data + n); memcpy(gr.res, g.res, 12); gr.ch = g.channels; memcpy(gr.to_local.m, g.to_local, 64);
         gr.bmin = V3(g.bbox_min[0], g.bbox_min[1], g.bbox_min[2]); gr.bmax = V3(g.bbox_max[0], g.bbox_max[1], g.bbox_max[2]);
         gr.filter = g.filter; gr.wrap = g.wrap; gr.differentiable = g.differentiable != 0;
-        if (g.max_value >= 0.f) gr.maxv = g.max_value; else gr.recompute_max();
+        gr.fixed_max = g.max_value >= 0.f;
+        if (gr.fixed_max) gr.maxv = g.max_value; else gr.recompute_max();
         if (gr.differentiable) gr.grad.assign(n, 0.0);
         sc.grids.push_back(std::move(gr));
     }
@@ -217,7 +218,7 @@ void orc_grid_grad_zero(void *h, uint32_t g) { auto &v = ((OrcScene *) h)->sc.gr
 void orc_grid_grad_read(void *h, uint32_t g, float *out) { auto &v = ((OrcScene *) h)->sc.grids[g].grad; for (size_t i = 0; i < v.size(); ++i) out[i] = (float) v[i]; }
 void orc_grid_update(void *h, uint32_t g, const float *data) {
     OrcScene &o = *(OrcScene *) h; Grid &gr = o.sc.grids[g];
-    std::copy(data, data + gr.data.size(), gr.data.begin()); gr.recompute_max();
+    std::copy(data, data + gr.data.size(), gr.data.begin()); if (!gr.fixed_max) gr.recompute_max();   /* max_value override survives updates (grid.cpp:314-327) */
     for (Medium &m : o.sc.media) if (m.m.kind == LR_MEDIUM_HETEROGENEOUS && m.m.sigma_t_grid == (int) g) m.max_density = m.m.scale * gr.maxv;
 }
 

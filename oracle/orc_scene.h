@@ -139,7 +139,7 @@ struct BVH {
 
 struct Grid {
     std::vector<float> data; uint32_t res[3]; uint32_t ch; M4 to_local; V3 bmin, bmax;
-    uint32_t filter, wrap; float maxv; bool differentiable;
+    uint32_t filter, wrap; float maxv; bool differentiable; bool fixed_max = false;
     std::vector<double> grad;     /* adjoint accumulator (prbvolpath) */
     int wrap_i(int p, int r) const {
         if (wrap == LR_WRAP_CLAMP) return std::min(std::max(p, 0), r - 1);

@@ -15,7 +15,11 @@ pytestmark = pytest.mark.gpu
 def _small_inverse(res=24, spp=16, grid_res=8, seed_density=0):
     rng = np.random.default_rng(12345 + seed_density)
     dens = (0.02 + 0.05 * rng.random((grid_res, grid_res, grid_res, 1))).astype(np.float32)
-    return scenes.sphere_liver_inverse(res=res, spp=spp, grid_res=grid_res, density=dens)
+    d = scenes.sphere_liver_inverse(res=res, spp=spp, grid_res=grid_res, density=dens)
+    # fixed majorant (`max_value`, src/volumes/grid.cpp:303-306): perturbing the grid then leaves the
+    # free-flight samples untouched, so finite differences see common random numbers
+    d["sphere"]["interior"]["sigma_t"]["max_value"] = 0.08
+    return d
 
 
 def test_prb_primal_per_path_matches_oracle():
@@ -63,10 +67,11 @@ def test_adjoint_lane_split_sums_to_whole():
 
 
 def test_gradient_finite_difference():
-    """d/d(eps) of loss(render(sigma_t + eps * dir)) by central differences with common random numbers
-    vs <grad, dir> from render_backward, along block directions (8^3-voxel blocks of SURVEY 8(d) scaled
-    to the 8^3 test grid: 2^3 blocks)."""
-    res, spp, gr = 24, 256, 8
+    """Directional derivative of loss(render(sigma_t + eps * dir)) by central differences with common
+    random numbers (same seed, fixed majorant) vs <grad, dir> from render_backward.  Delta tracking makes
+    the same-seed render piecewise constant in sigma_t per path (null/real decisions flip), so the FD of
+    a finite-sample render carries O(sqrt(1/(eps*N))) noise: N = 16.8M paths here."""
+    res, spp, gr = 16, 65536, 4
     d = _small_inverse(res=res, spp=spp, grid_res=gr)
     dens0 = np.array(d["sphere"]["interior"]["sigma_t"]["grid"], dtype=np.float32)
     sc = mi.load_dict(d); ctx = mi.Context(0).upload(sc)
@@ -86,20 +91,20 @@ def test_gradient_finite_difference():
     grad = ctx.grid_grad_read(0).reshape(dens0.shape).astype(np.float64)
     assert np.isfinite(grad).all() and np.abs(grad).max() > 0
 
-    # whole-grid direction + a few block directions
     dirs = [np.ones_like(dens0, dtype=np.float64)]
-    for _ in range(3):
-        z, y, x = rng.integers(0, gr // 2, size=3) * 2
-        m = np.zeros_like(dens0, dtype=np.float64); m[z:z + 2, y:y + 2, x:x + 2] = 1.0; dirs.append(m)
+    zz = np.arange(gr)[:, None, None, None] / (gr - 1.0)
+    dirs.append(np.broadcast_to(zz, dens0.shape).astype(np.float64))                 # linear ramp along z
+    dirs.append(np.broadcast_to(1.0 - zz.transpose(1, 0, 2, 3), dens0.shape).astype(np.float64))   # ramp along y
+    report = []
     for k, m in enumerate(dirs):
-        eps = 2e-3
+        eps = 1e-3
         lp, _ = loss_and_img(dens0 + eps * m); lm, _ = loss_and_img(dens0 - eps * m)
         fd = (lp - lm) / (2 * eps); an = float((grad * m).sum())
-        # The estimator is a detached-sampling PRB estimator: FD of the *same-seed* render includes the
-        # change of the discrete null/real decisions, so agreement is statistical at finite spp.
-        tol = 0.15 if k else 0.05
-        assert abs(fd - an) <= tol * max(abs(fd), abs(an)) + 1e-7, (k, fd, an)
+        report.append((k, fd, an, abs(fd - an) / max(abs(fd), abs(an))))
     ctx.grid_update(0, dens0)
+    print("FD check (dir, fd, analytic, rel):", report)
+    for k, fd, an, rel in report:
+        assert rel < 2e-2, report
 
 
 def test_traverse_update_recomputes_majorant():

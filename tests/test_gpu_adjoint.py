@@ -108,7 +108,8 @@ def test_gradient_finite_difference():
 
 
 def test_traverse_update_recomputes_majorant():
-    d = _small_inverse(res=16, spp=4); sc = mi.load_dict(d)
+    d = _small_inverse(res=16, spp=4); d["sphere"]["interior"]["sigma_t"].pop("max_value")
+    sc = mi.load_dict(d)
     params = mi.traverse(sc)
     key = [k for k in params.keys() if k.endswith("sigma_t.data")][0]
     img0 = mi.render(sc, spp=4, seed=1)

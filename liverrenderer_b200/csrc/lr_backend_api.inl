@@ -33,7 +33,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         if (m.texcoords) { DevBuf *b = c->newbuf(); if (int r = upload(c, b, m.texcoords, (size_t) m.n_vertices * 2)) return r; d.uv = b->as<float>(); }
         d.bsdf = m.bsdf; d.interior = m.interior_medium; d.exterior = m.exterior_medium; d.emitter = m.emitter;
         d.tri_offset = (uint32_t) tris.size(); d.n_faces = m.n_faces;
-        d.flags = (m.interior_medium >= 0 || m.exterior_medium >= 0) ? 1u : 0u;
+        d.flags = ((m.interior_medium >= 0 || m.exterior_medium >= 0) ? 1u : 0u) | (m.flip_normals ? 2u : 0u);
         bool is_null = s->bsdfs[m.bsdf].kind == LR_BSDF_NULL; if (is_null) sc.any_null_bsdf = 1;
         std::vector<float> cdf(m.n_faces); float area = 0.f;
         for (uint32_t f = 0; f < m.n_faces; ++f) {

@@ -31,6 +31,19 @@ LR_DEV SurfaceInteraction intersect(const DScene &sc, const DTri *tris_gid, cons
     Hit h = bvh_trace<false, false>(sc, ray);
     return compute_si(sc, ray, h, tris_gid);
 }
+LR_DEV int hit_emitter(const DScene &sc, const DTri *tris_gid, const Hit &h) {
+    return hit_valid(h) ? sc.meshes[__float_as_uint(tris_gid[h.prim].v1.w)].emitter : -1;
+}
+// Integrator::skip_area_emitters (src/render/integrator.cpp:97-123): first hit along `ray` that is not an
+// area emitter; `ray` ends up as the segment that hit was found with.
+LR_DEV Hit skip_area_emitters(const DScene &sc, const DTri *tris_gid, Ray &ray, Counters &cnt) {
+    for (;;) {
+        cnt.rays++; Hit pi = bvh_trace<false, false>(sc, ray);
+        if (hit_emitter(sc, tris_gid, pi) < 0) return pi;
+        SurfaceInteraction si = compute_si(sc, ray, pi, tris_gid);
+        ray = spawn_ray(si.p, si.n, ray.d);
+    }
+}
 LR_DEV SurfaceInteraction invalid_si() {
     SurfaceInteraction si; si.t = LR_INF; si.p = si.n = si.wi = mk3(0.f); si.sh.s = si.sh.t = si.sh.n = mk3(0.f); si.uv = mk2(0.f, 0.f); si.mesh = -1; si.prim = 0; return si;
 }
@@ -52,6 +65,10 @@ LR_DEV LaneResult sample_path(const DScene &sc, const DTri *tris_gid, Sampler &s
     bool valid_ray = !sc.hide_emitters && sc.env >= 0;
     V3 prev_p = mk3(0.f); float prev_bsdf_pdf = 1.f; bool prev_bsdf_delta = true;
     cnt.rays++; Hit pi = bvh_trace<false, false>(sc, ray);
+    if (sc.hide_emitters && hit_emitter(sc, tris_gid, pi) >= 0) {         // path.cpp:178-191 (ls.ray itself is kept)
+        SurfaceInteraction s0 = compute_si(sc, ray, pi, tris_gid);
+        Ray r2 = spawn_ray(s0.p, s0.n, ray.d); pi = skip_area_emitters(sc, tris_gid, r2, cnt);
+    }
     bool active = true;
     while (active) {
         SurfaceInteraction si = compute_si(sc, ray, pi, tris_gid);
@@ -228,7 +245,12 @@ LR_DEV LaneResult sample_volpath(const DScene &sc, const DTri *tris_gid, Sampler
         }
 
         active_surface |= escaped_medium;
-        if (active_surface && needs_intersection) si = intersect(sc, tris_gid, ray, cnt);
+        bool intersect_now = active_surface && needs_intersection;
+        if (intersect_now) si = intersect(sc, tris_gid, ray, cnt);
+        if (sc.hide_emitters && intersect_now && depth == 0u && si_valid(si) && sc.meshes[si.mesh].emitter >= 0) {   // volpath.cpp:307-323
+            Ray r2 = spawn_ray(si.p, si.n, ray.d); Hit pi = skip_area_emitters(sc, tris_gid, r2, cnt);
+            si = compute_si(sc, r2, pi, tris_gid);
+        }
         if (active_surface) {
             bool count_direct = depth == 0u || specular_chain;
             int emitter = emitter_of(sc, si);

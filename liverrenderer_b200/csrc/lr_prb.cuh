@@ -164,7 +164,12 @@ LR_DEV LaneResult sample_prb(const DScene &sc, const DTri *tris_gid, Sampler &sm
         if (act_medium_scatter) { phase.kind = sc.media[mei.medium].m.phase; phase.g = sc.media[mei.medium].m.phase_g; }
 
         active_surface |= escaped_medium;
-        if (active_surface && needs_intersection) si = intersect(sc, tris_gid, ray, cnt);
+        bool intersect_now = active_surface && needs_intersection;
+        if (intersect_now) si = intersect(sc, tris_gid, ray, cnt);
+        if (sc.hide_emitters && intersect_now && depth == 0u && si_valid(si) && sc.meshes[si.mesh].emitter >= 0) {   // prbvolpath.py:218-231
+            Ray r2 = spawn_ray(si.p, si.n, ray.d); Hit pi = skip_area_emitters(sc, tris_gid, r2, cnt);
+            si = compute_si(sc, ray, pi, tris_gid);                       // the reference recomputes with the ORIGINAL ray here
+        }
         if (active_surface) {
             bool count_direct = depth == 0u || specular_chain;
             int emitter = emitter_of(sc, si);

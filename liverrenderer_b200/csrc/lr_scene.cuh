@@ -197,6 +197,7 @@ LR_DEV SurfaceInteraction compute_si(const DScene &sc, const Ray &ray, const Hit
         V3 n = fma3(n2, b2, fma3(n1, b1, mk3(__fmul_rn(n0.x, b0), __fmul_rn(n0.y, b0), __fmul_rn(n0.z, b0))));
         si.sh.n = n * (1.f / sqrtf(sqnorm(n)));
     } else si.sh.n = si.n;
+    if (me.flags & 2u) { si.n = -si.n; si.sh.n = -si.sh.n; }         // flip_normals (mesh.cpp:1652-1655)
     si.sh.s = normalize(fma3(si.sh.n, -dot(si.sh.n, dp_du), dp_du));
     if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { V3 t_; coordinate_system(si.sh.n, si.sh.s, t_); }
     si.sh.t = cross(si.sh.n, si.sh.s);

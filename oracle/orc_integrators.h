@@ -40,6 +40,16 @@ struct Integrator {
         rr_depth = s.integ.rr_depth; hide_emitters = s.integ.hide_emitters != 0;
     }
     SurfaceInteraction intersect(const Ray &r) { cnt.rays++; return sc.ray_intersect(r); }
+    /* Integrator::skip_area_emitters (src/render/integrator.cpp:97-123): first hit along `ray` that is not an
+       area emitter; `ray` ends up as the segment that hit was found with. */
+    Hit skip_area_emitters(Ray &ray) {
+        for (;;) {
+            cnt.rays++; Hit pi = sc.ray_intersect_prelim(ray);
+            if (!(pi.valid() && sc.meshes[sc.tris[pi.prim].mesh].emitter >= 0)) return pi;
+            SurfaceInteraction si = sc.compute_si(ray, pi);
+            ray = si.spawn_ray(ray.d);
+        }
+    }
 
     /* ===================== path (src/integrators/path.cpp:95-349) ===================== */
     LaneResult sample_path(Sampler &smp, Ray ray) {
@@ -48,6 +58,10 @@ struct Integrator {
         bool valid_ray = !hide_emitters && sc.env >= 0;
         Interaction prev_si; float prev_bsdf_pdf = 1.f; bool prev_bsdf_delta = true;
         cnt.rays++; Hit pi = sc.ray_intersect_prelim(ray);
+        if (hide_emitters && pi.valid() && sc.meshes[sc.tris[pi.prim].mesh].emitter >= 0) {   /* :178-191; ls.ray itself is kept */
+            Ray r2 = sc.compute_si(ray, pi).spawn_ray(ray.d);
+            pi = skip_area_emitters(r2);
+        }
         bool active = true;
         while (active) {
             SurfaceInteraction si = sc.compute_si(ray, pi);

@@ -158,7 +158,13 @@ LaneResult sample_prb(bool primal, Sampler &smp, Ray ray, V3 dL, V3 state_in) {
         Phase phase = act_medium_scatter ? phase_of(mei.medium) : Phase{LR_PHASE_ISOTROPIC, 0.f};
 
         active_surface |= escaped_medium;
-        if (active_surface && needs_intersection) si = intersect(ray);
+        bool intersect_now = active_surface && needs_intersection;
+        if (intersect_now) si = intersect(ray);
+        if (hide_emitters && intersect_now && depth == 0u && si.is_valid() && sc.meshes[si.mesh].emitter >= 0) {
+            /* hide area emitters on the first segment (prbvolpath.py:218-231: si recomputed with the ORIGINAL ray) */
+            Ray r2 = si.spawn_ray(ray.d); Hit pi = skip_area_emitters(r2);
+            si = sc.compute_si(ray, pi);
+        }
         if (active_surface) {                                                     /* :236-252 */
             bool count_direct = depth == 0u || specular_chain;
             int emitter = sc.emitter_of(si);

@@ -219,7 +219,6 @@ struct Scene {
         si.p = fma3(p0, b0, fma3(p1, b1, p2 * b2));
         si.t = h.t; si.mesh = (int) tr.mesh; si.prim = h.prim;
         si.n = normalize(cross(p1 - p0, p2 - p0));
-        if (me.flip) si.n = -si.n;
         si.uv = {b1, b2};
         coordinate_system(si.n, si.dp_du, si.dp_dv);
         V3 dp0 = p1 - p0, dp1 = p2 - p0;
@@ -239,6 +238,7 @@ struct Scene {
             float il = 1.f / sqrtf(sqnorm(n));
             si.sh.n = n * il;
         } else si.sh.n = si.n;
+        if (me.flip) { si.n = -si.n; si.sh.n = -si.sh.n; }                 /* mesh.cpp:1652-1655 */
         /* initialize_sh_frame: Gram-Schmidt against dp_du */
         si.sh.s = normalize(fma3(si.sh.n, -dot(si.sh.n, si.dp_du), si.dp_du));
         if (si.dp_du.x == 0.f && si.dp_du.y == 0.f && si.dp_du.z == 0.f) { V3 t_; coordinate_system(si.sh.n, si.sh.s, t_); }

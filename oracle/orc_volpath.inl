@@ -154,7 +154,13 @@ LaneResult sample_volpath(Sampler &smp, Ray ray, int initial_medium) {
 
         /* ---- surfaces (:300-389) ---- */
         active_surface |= escaped_medium;
-        if (active_surface && needs_intersection) si = intersect(ray);
+        bool intersect_now = active_surface && needs_intersection;
+        if (intersect_now) si = intersect(ray);
+        if (hide_emitters && intersect_now && depth == 0u && si.is_valid() && sc.meshes[si.mesh].emitter >= 0) {
+            /* hide area emitters on the first segment (volpath.cpp:307-323: si recomputed with the skip ray) */
+            Ray r2 = si.spawn_ray(ray.d); Hit pi = skip_area_emitters(r2);
+            si = sc.compute_si(r2, pi);
+        }
         if (active_surface) {
             bool count_direct = depth == 0u || specular_chain;
             int emitter = sc.emitter_of(si);

@@ -169,3 +169,24 @@ def test_rgba_alpha_channel():
     img = mi.render(sc, spp=4)
     assert img.shape == (32, 32, 4)
     assert np.allclose(img[..., 3], 1.0)          # environment emitter => every ray valid (volpath.cpp:103)
+
+
+@pytest.mark.parametrize("integrator", ["path", "volpath", "prbvolpath"])
+def test_hide_emitters_directly_visible_pixel(integrator):
+    """src/integrators/tests/test_integrators.py:29-52: Cornell pixel (124, 36) looks at the light: max_depth=1 =>
+    exactly the radiance; hide_emitters => the light is skipped (Integrator::skip_area_emitters) => 0."""
+    spp = 16; pix = 36 * 256 + 124
+    for hide in (False, True):
+        d = mi.cornell_box(); d["integrator"] = {"type": integrator, "max_depth": 1, "hide_emitters": hide}
+        sc = mi.load_dict(d)
+        gpu = mi.Context(0).upload(sc).sample_lanes(0, spp, pix * spp, (pix + 1) * spp)
+        cpu = orc.OracleScene(sc).sample_lanes(0, spp, pix * spp, (pix + 1) * spp)
+        assert np.allclose(gpu[:, :3], 0.0 if hide else [18.387, 13.9873, 6.75357], rtol=1e-5)
+        assert np.array_equal(gpu[:, :3], cpu[:, :3])
+
+
+def test_hide_emitters_whole_image_matches_oracle():
+    d = scenes.cornell_box_path(res=32, spp=4); d["integrator"] = {"type": "path", "max_depth": 4, "hide_emitters": True}
+    sc = mi.load_dict(d); n = 32 * 32 * 4
+    gpu = mi.Context(0).upload(sc).sample_lanes(0, 4, 0, n); cpu = orc.OracleScene(sc).sample_lanes(0, 4, 0, n)
+    assert path_match_fraction(gpu, cpu, 1e-4) > 0.995

@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the B200 volumetric path-tracing backend (BASELINE.json metric:
+samples/s + Mrays/s of the `volpath` forward render and the `prbvolpath` gradient step).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one full render of the workload scene (C3: Liver-SingleMesh, heterogeneous gridvolume, `volpath`,
+1080x1080, --spp samples per pixel) with every input already resident in HBM.  Multi-GPU: one process per GPU,
+weak scaling -- every rank renders the whole config with seed+rank (independent sample sets of the same image), the
+film accumulators are summed with one NCCL all-reduce per step; `value` = samples of all ranks / max-over-ranks time.
+The `prb` object is the C5 inverse step (primal + prbvolpath adjoint + NCCL all-reduce of the grid gradient).
+`e2e` is the same render through the public host API (`params.update()` + `mi.render`) with pinned HOST buffers:
+the density grid goes host->device and the developed image device->host inside the timed region.
+`--impl reference` times the CPU oracle (the restatement of the reference's algorithm, oracle/) on the host cores.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "volpath_fwd_samples_per_s"
+UNIT = "samples/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c3xl"])
+    ap.add_argument("--res", type=int, default=1080)
+    ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step (0 => the config's)")
+    ap.add_argument("--tracking", default="reference", choices=["reference", "dda"])
+    ap.add_argument("--no-prb", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-spp", type=int, default=4, help="spp of the bounded CPU-baseline sample")
+    return ap.parse_args()
+
+
+def workload_scene(args, for_cpu=False):
+    from liverrenderer_b200 import scenes
+    w = args.workload; res = args.res
+    if w == "c1":
+        spp = args.spp or 64
+        return scenes.cornell_box_path(res=256 if res == 1080 else res, spp=spp), spp, "C1 mi.cornell_box() 256x256 path"
+    if w == "c2":
+        spp = args.spp or 256
+        return scenes.cornell_box_fog(res=res, spp=spp), spp, f"C2 cornell-box fog homogeneous volpath {res}x{res}"
+    grid = 512 if w == "c3xl" else 256
+    spp = args.spp or 1024
+    tracking = "reference" if for_cpu else args.tracking
+    d = scenes.liver_single_mesh(res=res, spp=spp, grid_res=grid, tracking=tracking)
+    return d, spp, f"C3 Liver-SingleMesh heterogeneous gridvolume {grid}^3 volpath {res}x{res}"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows = []; self.p = None; self.index = index
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True); self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=2)
+        except Exception:
+            self.p.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except ValueError:
+                continue
+            for k, n in enumerate(names):
+                if r[3 + k].lower().startswith("active"):
+                    reasons.add(n)
+        # under load = the upper half of the power samples
+        if sm:
+            thr = np.median(pw); load = [s for s, p in zip(sm, pw) if p >= thr] or sm
+            return {"sm_mhz": float(np.median(load)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons),
+                    "power_w_max": float(max(pw)), "samples": len(sm)}
+        return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU side: the oracle (restatement of the reference's llvm_ad_rgb algorithm; the reference itself
+# cannot be built or imported here, DESIGN.md "Reference arm") on the box's host cores
+# --------------------------------------------------------------------------------------------------
+def cpu_sample(args, spp_cpu: int, repeats: int = 1):
+    """Renders the workload scene at `spp_cpu` spp with the oracle, all host threads.  Returns (samples/s, dict)."""
+    import liverrenderer_b200 as mi
+    from tests import orc
+    d, _, name = workload_scene(args, for_cpu=True)
+    d["sensor"]["sampler"]["sample_count"] = spp_cpu
+    sc = mi.load_dict(d); o = orc.OracleScene(sc, threads=0)
+    cores = os.cpu_count() or 1
+    best = None
+    for r in range(repeats):
+        o.stats_reset(); t = time.perf_counter(); o.render(seed=r, spp=spp_cpu); dt = time.perf_counter() - t
+        st = o.stats()
+        if best is None or dt < best[0]:
+            best = (dt, st)
+    dt, st = best
+    W, H = sc.film_size
+    return st["samples"] / dt, {"value": st["samples"] / dt, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{name} at {spp_cpu} spp ({W * H * spp_cpu} samples, {dt:.1f} s), oracle/ liborc.so, std::thread x{cores}, "
+                                          "global-majorant delta tracking as the reference",
+                                "mrays_per_s": st["rays"] / dt / 1e6, "collisions_per_s": st["collisions"] / dt}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    d, spp, name = workload_scene(args, for_cpu=True)
+    import liverrenderer_b200 as mi
+    from tests import orc
+    spp_cpu = args.cpu_spp
+    d["sensor"]["sampler"]["sample_count"] = spp_cpu
+    sc = mi.load_dict(d); o = orc.OracleScene(sc, threads=0); W, H = sc.film_size
+    cores = os.cpu_count() or 1
+    for w in range(min(args.warmup, 1)):                      # one warm-up pass is enough for a CPU code (page-in, thread pool)
+        o.render(seed=1000 + w, spp=spp_cpu)
+    o.stats_reset(); t = time.perf_counter()
+    for k in range(args.steps):
+        o.render(seed=k, spp=spp_cpu)
+    dt = time.perf_counter() - t; st = o.stats()
+    v = st["samples"] / dt
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": name, "spp_per_step": spp_cpu, "samples_per_step": W * H * spp_cpu,
+                                            "note": "each step is a bounded sample (reduced spp) of the same scene"},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{args.steps} x ({W}x{H} at {spp_cpu} spp) through oracle/liborc.so on {cores} threads"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "mrays_per_s": st["rays"] / dt / 1e6, "collisions_per_s": st["collisions"] / dt, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------------------------------
+# B200 arm
+# --------------------------------------------------------------------------------------------------
+def _film_allreduce(ctx, torch, dist, film_buf):
+    """Sum the [H,W,C] film accumulators over ranks (one collective per render)."""
+    ctx.film_read(film_buf); dist.all_reduce(film_buf); ctx.film_write(film_buf)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import liverrenderer_b200 as mi
+    from liverrenderer_b200 import scenes
+
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py: no CUDA device -- the B200 backend has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local); dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0)); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650 GB/s (B200_PROFILING.md)"
+
+    d, spp, name = workload_scene(args)
+    sc = mi.load_dict(d); W, H = sc.film_size
+    ctx = mi.Context(local).upload(sc)
+    stream = torch.cuda.current_stream(dev); ctx.set_stream(stream.cuda_stream)
+    C = ctx.film_channels()
+    film_buf = torch.empty((H, W, C), dtype=torch.float32, device=dev)
+    out_dev = torch.empty((H, W, sc.out_channels), dtype=torch.float32, device=dev)
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)          # > 126 MB L2
+
+    def fwd_step(k):
+        ctx.film_clear(); ctx.render_lanes(1000 * k + rank, spp, 0, 0)
+        st = ctx.stats()
+        if world > 1:
+            _film_allreduce(ctx, torch, dist, film_buf)
+        ctx.film_develop(out_dev)
+        return st
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for w in range(args.warmup):
+        fwd_step(-1 - w)
+    clocks = ClockSampler(local); barrier(); clocks.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    tot = {"samples": 0, "rays": 0, "collisions": 0, "real_scatters": 0, "launches": 0, "tracking_ms": 0.0, "tracking_launches": 0}
+    for k in range(args.steps):
+        flush.fill_(k & 0xff)                                                 # L2 flush between timed iterations
+        barrier()
+        ev[k][0].record(stream); st = fwd_step(k); ev[k][1].record(stream)
+        for key in tot:
+            tot[key] += st[key]
+        tot["launches"] += 1 + (2 if world > 1 else 0)                         # develop (+ 2 D2D copies around the NCCL all-reduce)
+    barrier(); clk = clocks.stop()
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([tot["samples"], tot["rays"], tot["collisions"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt)
+    ms_max = float(t.item()); samples, rays, colls = (float(x) for x in cnt.tolist())
+    value = samples / (ms_max * 1e-3)
+
+    # ---- roofline of the dominant kernel (rank 0): algorithmic 32 B per collision (8 fp32 corners of the sigma_t tap) ----
+    k_ms = tot["tracking_ms"] / max(tot["tracking_launches"], 1)
+    bytes_per_launch = tot["collisions"] / max(tot["tracking_launches"], 1) * 32.0
+    achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                "kernel": f"k_render<{sc.integrator_name}> (free-flight tracking + trilinear sigma_t taps; one launch per render)",
+                "algorithmic_bytes_per_unit": 32, "units_per_launch": tot["collisions"] / max(tot["tracking_launches"], 1),
+                "kernel_ms": k_ms, "peak_source": peak_src}
+    return dict(torch=torch, dist=dist, mi=mi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local, spp=spp, name=name,
+                W=W, H=H, value=value, ms_max=ms_max, rays=rays, colls=colls, samples=samples, tot=tot, roofline=roofline, clk=clk,
+                barrier=barrier, flush=flush, hbm_peak=hbm_peak)
+
+
+def run_e2e(R, args):
+    """Same render through the host API with HOST buffers: density grid pinned-host -> device (params.update():
+    lr_grid_update recomputes majorant + super-grid), render, developed image device -> pinned host."""
+    torch, ctx, sc, dev, world, rank = R["torch"], R["ctx"], R["sc"], R["dev"], R["world"], R["rank"]
+    dist = R["dist"]; W, H, spp = R["W"], R["H"], R["spp"]
+    gi = 0; n = ctx.grid_size(gi)
+    grid_host = torch.from_numpy(np.ascontiguousarray(sc.grid_arrays[gi]).reshape(-1)).pin_memory()
+    out_host = torch.empty((H, W, sc.out_channels), dtype=torch.float32).pin_memory()
+    film_buf = torch.empty((H, W, ctx.film_channels()), dtype=torch.float32, device=dev)
+    steps = max(1, min(args.steps, 2))
+
+    def step(k):
+        ctx.grid_update(gi, grid_host)                          # H2D of the step's input + majorant rebuild
+        if world == 1:
+            ctx.render(seed=1000 * k + rank, spp=spp, out=out_host)          # render + develop + D2H
+        else:
+            ctx.film_clear(); ctx.render_lanes(1000 * k + rank, spp, 0, 0)
+            _film_allreduce(ctx, torch, dist, film_buf); ctx.film_develop(out_host)
+        return float(out_host[H // 2, W // 2, 0])                # the result is read on the host
+
+    step(-1)
+    R["barrier"](); t0 = time.perf_counter()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e0.record(R["stream"])
+    for k in range(steps):
+        step(k)
+    e1.record(R["stream"]); R["barrier"](); wall = time.perf_counter() - t0
+    ms = max(e0.elapsed_time(e1), 0.0)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    return {"value": W * H * spp * steps * world / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(n * 4),
+            "d2h_bytes_per_step": int(out_host.numel() * 4), "steps": steps, "ms_per_step": ms / steps, "wall_ms_per_step": wall / steps * 1e3,
+            "api": "params.update() [lr_grid_update, pinned host grid] + mi.render [lr_render -> pinned host image]"}
+
+
+def run_prb(R, args):
+    """C5: SphereLiverConstEnv inverse step = primal render + prbvolpath adjoint (spp_grad 64) + NCCL all-reduce of the
+    128^3 density-grid gradient.  Lanes are dealt to ranks by contiguous ranges (strong split of one step) -- here the
+    bench keeps per-GPU work fixed instead: every rank replays the full lane set with seed+rank (weak)."""
+    torch, mi, dev, world, rank, dist = R["torch"], R["mi"], R["dev"], R["world"], R["rank"], R["dist"]
+    from liverrenderer_b200 import scenes
+    res, spp, gr = 512, 64, 128
+    sc = mi.load_dict(scenes.sphere_liver_inverse(res=res, spp=spp, grid_res=gr, tracking=args.tracking))
+    ctx = mi.Context(R["local"]).upload(sc); ctx.set_stream(R["stream"].cuda_stream)
+    img = torch.empty((res, res, 3), dtype=torch.float32, device=dev)
+    grad = torch.empty(ctx.grid_size(0), dtype=torch.float32, device=dev)
+    target = torch.full_like(img, 0.5)
+    steps = max(1, min(args.steps, 3)); tot = {"samples": 0, "rays": 0, "collisions": 0, "ms_bwd": 0.0}
+
+    def step(k):
+        ctx.render(seed=k + rank, spp=spp, out=img)
+        g = (2.0 / img.numel()) * (img - target)                 # L2 loss adjoint (notebook cell 11); torch elementwise = plumbing
+        ctx.grid_grad_zero(0)
+        ctx.render_backward(g, seed=mi.sample_tea_32(k + rank, 1)[0], spp=spp)
+        st = ctx.stats()
+        ctx.grid_grad_read(0, grad)
+        if world > 1:
+            dist.all_reduce(grad)
+        return st
+
+    step(-1); R["barrier"]()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e0.record(R["stream"])
+    for k in range(steps):
+        st = step(k)
+        tot["samples"] += st["samples"]; tot["rays"] += st["rays"]; tot["collisions"] += st["collisions"]; tot["ms_bwd"] += st["device_ms"]
+    e1.record(R["stream"]); R["barrier"]()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()); n = res * res * spp * steps * world
+    ach = tot["collisions"] * 64.0 / (tot["ms_bwd"] * 1e-3) / 1e9 if tot["ms_bwd"] > 0 else 0.0
+    return {"workload": f"C5 SphereLiverConstEnv prbvolpath {res}x{res}, spp {spp} primal + spp_grad {spp}, sigma_t grid {gr}^3",
+            "grad_samples_per_s": n / (ms * 1e-3), "ms_per_step": ms / steps, "steps": steps, "adjoint_kernel_ms": tot["ms_bwd"] / steps,
+            "adjoint_collisions_per_s": tot["collisions"] / (tot["ms_bwd"] * 1e-3) if tot["ms_bwd"] > 0 else 0.0,
+            "adjoint_GBps_algorithmic_64B_per_collision": ach, "adjoint_frac_of_hbm_peak": ach / R["hbm_peak"],
+            "allreduce_bytes": int(grad.numel() * 4) if world > 1 else 0, "grad_finite": bool(torch.isfinite(grad).all().item()),
+            "grad_abs_max": float(grad.abs().max().item())}
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args); return
+    R = run_b200(args)
+    e2e = run_e2e(R, args)
+    prb = None if args.no_prb else run_prb(R, args)
+    cpu = None
+    if R["rank"] == 0 and R["world"] == 1 and not args.no_cpu:
+        _, cpu = cpu_sample(args, args.cpu_spp)
+    if R["world"] > 1:
+        R["dist"].barrier()
+    if R["rank"] == 0:
+        secs = R["ms_max"] * 1e-3
+        line = {"metric": METRIC, "value": R["value"], "unit": UNIT, "n_gpus": R["world"], "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": R["ms_max"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": R["name"], "spp": R["spp"], "samples_per_step_per_gpu": R["W"] * R["H"] * R["spp"], "tracking": args.tracking,
+                           "l2": "flushed between timed iterations (512 MiB write)", "partition": "every rank renders the config with seed+rank; film all-reduce"},
+                "mrays_per_s": R["rays"] / secs / 1e6, "collisions_per_s": R["colls"] / secs,
+                "collisions_per_sample": R["colls"] / max(R["samples"], 1), "rays_per_sample": R["rays"] / max(R["samples"], 1),
+                "e2e": e2e, "gpu_launches": int(R["tot"]["launches"]), "clocks": R["clk"], "roofline": R["roofline"], "cpu_baseline": cpu, "prb": prb}
+        print(json.dumps(line), flush=True)
+    if R["world"] > 1:
+        R["dist"].destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <cstdio>
 #include <cmath>
+#include <cstdlib>
 
 using namespace lr;
 
@@ -21,6 +22,18 @@ struct DevBuf {
     DevBuf(const DevBuf &) = delete; DevBuf &operator=(const DevBuf &) = delete;
     cudaError_t alloc(size_t n) { if (p) { cudaFree(p); p = nullptr; } bytes = n; return n ? cudaMalloc(&p, n) : cudaSuccess; }
     template <typename T> T *as() const { return (T *) p; }
+};
+
+struct WavefrontBuffers {
+    DevBuf states, queues, counters; uint32_t cap = 0;
+    uint32_t *live_host = nullptr;                       // pinned ring of live counts
+    std::vector<cudaEvent_t> ring_ev;                    // one per ring slot
+    std::vector<cudaEvent_t> kev;                        // event pool timing the TRACK / NEE launches
+    ~WavefrontBuffers() {
+        if (live_host) cudaFreeHost(live_host);
+        for (auto e : ring_ev) cudaEventDestroy(e);
+        for (auto e : kev) cudaEventDestroy(e);
+    }
 };
 
 struct lr_ctx {
@@ -40,6 +53,9 @@ struct lr_ctx {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     lr_stats st{};
     int blocks_per_sm[8] = {0}; int n_sm = 148;
+    // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
+    WavefrontBuffers *wf = nullptr; uint64_t wf_pool_slots = 1ull << 22; uint32_t surf_bucket_mask = 0; bool use_wavefront = true;
+    uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;
     DevBuf *newbuf() { pool.push_back(new DevBuf()); return pool.back(); }
     void free_scene() { for (auto *b : pool) delete b; pool.clear(); h_grids.clear(); h_media.clear(); grid_floats.clear(); grid_fixed_max.clear(); has_scene = false; }
 };
@@ -68,6 +84,8 @@ int lr_create(int device, lr_ctx **out) {
         LR_FAIL((lr_ctx *) nullptr, LR_ERR_NO_DEVICE, "lr_create: no CUDA device available (%s); this backend has no CPU path", cudaGetErrorString(e));
     if (device < 0 || device >= n) LR_FAIL((lr_ctx *) nullptr, LR_ERR_INVALID_ARG, "lr_create: device %d out of range (0..%d)", device, n - 1);
     lr_ctx *c = new lr_ctx(); c->device = device;
+    if (const char *e = getenv("LR_WF_SLOTS")) { long long v = atoll(e); if (v >= 1024) c->wf_pool_slots = (uint64_t) v; }
+    if (const char *e = getenv("LR_MEGAKERNEL")) c->use_wavefront = atoi(e) == 0;
     LR_CUDA(c, cudaSetDevice(device));
     cudaDeviceProp prop; LR_CUDA(c, cudaGetDeviceProperties(&prop, device));
     c->n_sm = prop.multiProcessorCount;
@@ -84,7 +102,7 @@ void lr_destroy(lr_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->free_scene();
+    c->free_scene(); delete c->wf; c->wf = nullptr;
     if (c->cancel_host) cudaFreeHost(c->cancel_host);
     if (c->ev0) cudaEventDestroy(c->ev0); if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);

@@ -20,7 +20,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     LR_CUDA(c, c->scratch.alloc(256));
 
     // ---- meshes: concatenate triangles (gid order), upload per-mesh attribute arrays ----
-    std::vector<DTri> tris; std::vector<DMesh> meshes(s->n_meshes);
+    std::vector<DTri> tris; std::vector<DMesh> meshes(s->n_meshes); uint32_t surf_mask = 0;
     V3 lo = mk3(INFINITY), hi = mk3(-INFINITY);
     for (uint32_t i = 0; i < s->n_meshes; ++i) {
         const lr_mesh &m = s->meshes[i]; DMesh &d = meshes[i]; memset(&d, 0, sizeof d);
@@ -35,6 +35,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         d.tri_offset = (uint32_t) tris.size(); d.n_faces = m.n_faces;
         d.flags = ((m.interior_medium >= 0 || m.exterior_medium >= 0) ? 1u : 0u) | (m.flip_normals ? 2u : 0u);
         bool is_null = s->bsdfs[m.bsdf].kind == LR_BSDF_NULL; if (is_null) sc.any_null_bsdf = 1;
+        { uint32_t k = s->bsdfs[m.bsdf].kind; surf_mask |= 1u << (k == LR_BSDF_ROUGHDIELECTRIC ? 1 : (k == LR_BSDF_PRINCIPLED ? 2 : 0)); }
         std::vector<float> cdf(m.n_faces); float area = 0.f;
         for (uint32_t f = 0; f < m.n_faces; ++f) {
             const uint32_t *ix = m.indices + 3 * (size_t) f;
@@ -119,6 +120,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     LR_CUDA(c, cudaMemsetAsync(c->film.p, 0, c->film.bytes, c->stream));
     LR_CUDA(c, c->weight_img.alloc((size_t) c->W * c->H * 4));
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->surf_bucket_mask = surf_mask;
     c->has_scene = true; memset(&c->st, 0, sizeof c->st);
     return LR_OK;
 }
@@ -158,6 +160,8 @@ template <int C, bool TO_FILM> static int launch_render_k(lr_ctx *c, const Rende
     }
 }
 
+#include "lr_wavefront_host.inl"
+
 static int begin_call(lr_ctx *c, const char *what) {
     if (!c) { g_last_error = std::string(what) + ": NULL context"; return LR_ERR_INVALID_ARG; }
     if (!c->has_scene) LR_FAIL(c, LR_ERR_NO_SCENE, "%s: no scene uploaded", what);
@@ -176,6 +180,7 @@ static int end_call(lr_ctx *c, uint64_t launches, bool tracking) {
     c->st.samples = h[0]; c->st.rays = h[1]; c->st.collisions = h[2]; c->st.real_scatters = h[3];
     c->st.launches = launches; c->st.device_ms = ms;
     if (tracking) { c->st.tracking_ms = ms; c->st.tracking_launches = 1; }
+    if (tracking && c->wf_launches) { c->st.launches = launches - 1 + c->wf_launches; c->st.tracking_ms = c->wf_tracking_ms; c->st.tracking_launches = c->wf_tracking_launches; }
     if (*c->cancel_host) LR_FAIL(c, LR_ERR_CANCELLED, "render cancelled");
     return LR_OK;
 }
@@ -188,6 +193,12 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
     a.lane_begin = begin; a.lane_end = end; a.seed = seed; a.spp_per_pass = p.spp_per_pass; a.n_passes = p.n_passes; a.total_spp = spp;
     a.work_counter = c->work_counter.as<unsigned long long>(); a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev;
     if (begin == end) return LR_OK;
+    c->wf_launches = 0;
+    if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATH) {
+        if (int r = wf_prepare(c, (end - begin))) return r;
+        if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false>(c, a) : wavefront_render_t<4, false>(c, a);
+        return c->film_channels == 5 ? wavefront_render_t<5, true>(c, a) : wavefront_render_t<4, true>(c, a);
+    }
     if (lanes_out) return c->film_channels == 5 ? launch_render_k<5, false>(c, a) : launch_render_k<4, false>(c, a);
     return c->film_channels == 5 ? launch_render_k<5, true>(c, a) : launch_render_k<4, true>(c, a);
 }

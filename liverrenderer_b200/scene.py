@@ -368,7 +368,7 @@ class Scene:
         i.hide_emitters = 1 if v.get("hide_emitters", False) else 0
         i.tracking = {"reference": K.TRACKING_REFERENCE, "dda": K.TRACKING_DDA}[str(v.get("tracking", "reference")).lower()]
         i.base_seed = self.base_seed; i.majorant_cell = int(v.get("majorant_cell", 0))
-        self.integrator = i
+        self.integrator = i; self.integrator_name = v["type"]
 
     # ---- POD ---------------------------------------------------------------------
     def pod(self) -> K.lr_scene:

@@ -81,6 +81,41 @@ LR_DEV bool aabb_intersect(V3 bmin, V3 bmax, const Ray &ray, float &mint, float 
     mint = tminx; maxt = tmaxx; return active;
 }
 
+
+// ---- majorant super-grid DDA (production tracking mode, LR_TRACKING_DDA) -----------------------------------
+// The sigma_t grid is covered by super-voxels of `cell`^3 voxels; maj[c] bounds the raw grid over the trilinear
+// support of super-voxel c (k_majorant_grid).  A ray is walked through the super-voxels in grid-local coordinates
+// (same ray parameter t as in world space); inside a super-voxel the free-flight majorant is scale * maj[c].
+struct DDA { int ix, iy, iz, sx, sy, sz; float tnx, tny, tnz, tdx, tdy, tdz; };
+LR_DEV void dda_init(const DGrid &g, const Ray &ray, float t0, DDA &d) {
+    V3 ol = xform_point(g.to_local, ray_at(ray, t0)), dl = xform_vector(g.to_local, ray.d);
+    float Sx = (float) g.rx / (float) g.cell, Sy = (float) g.ry / (float) g.cell, Sz = (float) g.rz / (float) g.cell;
+    float gx = ol.x * Sx, gy = ol.y * Sy, gz = ol.z * Sz, vx = dl.x * Sx, vy = dl.y * Sy, vz = dl.z * Sz;
+    d.ix = min(max((int) floorf(gx), 0), g.mx - 1); d.iy = min(max((int) floorf(gy), 0), g.my - 1); d.iz = min(max((int) floorf(gz), 0), g.mz - 1);
+    d.sx = vx > 0.f ? 1 : -1; d.sy = vy > 0.f ? 1 : -1; d.sz = vz > 0.f ? 1 : -1;
+    d.tdx = vx != 0.f ? fabsf(1.f / vx) : LR_INF; d.tdy = vy != 0.f ? fabsf(1.f / vy) : LR_INF; d.tdz = vz != 0.f ? fabsf(1.f / vz) : LR_INF;
+    d.tnx = vx != 0.f ? t0 + fmaxf(((float) (d.ix + (vx > 0.f ? 1 : 0)) - gx) / vx, 0.f) : LR_INF;
+    d.tny = vy != 0.f ? t0 + fmaxf(((float) (d.iy + (vy > 0.f ? 1 : 0)) - gy) / vy, 0.f) : LR_INF;
+    d.tnz = vz != 0.f ? t0 + fmaxf(((float) (d.iz + (vz > 0.f ? 1 : 0)) - gz) / vz, 0.f) : LR_INF;
+}
+LR_DEV float dda_majorant(const DGrid &g, const DDA &d) { return __ldg(g.maj + ((size_t) d.iz * g.my + d.iy) * g.mx + d.ix); }
+LR_DEV void dda_advance(const DGrid &g, DDA &d) {
+    if (d.tnx <= d.tny && d.tnx <= d.tnz) { d.ix = min(max(d.ix + d.sx, 0), g.mx - 1); d.tnx += d.tdx; }
+    else if (d.tny <= d.tnz) { d.iy = min(max(d.iy + d.sy, 0), g.my - 1); d.tny += d.tdy; }
+    else { d.iz = min(max(d.iz + d.sz, 0), g.mz - 1); d.tnz += d.tdz; }
+}
+// clip of the segment against the volume's AABB exactly as Medium::sample_interaction does (medium.cpp:53-60)
+LR_DEV bool medium_clip(const DGrid &g, const Ray &ray, float &mint, float &maxt) {
+    bool its = aabb_intersect(g.bmin, g.bmax, ray, mint, maxt);
+    its &= (isfinite(mint) || isfinite(maxt));
+    if (!its) return false;
+    mint = fmaxf(0.f, mint); maxt = fminf(ray.maxt, maxt);
+    return true;
+}
+LR_DEV bool medium_uses_dda(const DScene &sc, const DMedium &m) {
+    return sc.integ.tracking == LR_TRACKING_DDA && m.m.kind == LR_MEDIUM_HETEROGENEOUS;
+}
+
 struct MediumInteraction {
     float t; V3 p; V3 wi; V3 sigma_s, sigma_n, sigma_t, combined_extinction; float mint; int medium;
 };

@@ -179,6 +179,39 @@ __global__ void __launch_bounds__(256) k_wf_track(const __grid_constant__ DScene
                 if (perform_rr) thr *= 1.f / q;
                 active &= depth < sc.max_depth;
                 if (!active) { event = 0; break; }
+                if (medium >= 0 && medium_uses_dda(sc, sc.media[medium])) {
+                    // production tracking: delta tracking against the local majorants of the super-grid.  The majorant is one
+                    // scalar for all channels (heterogeneous.cpp:163), so Tr/pdf reduces to 1/mu at a collision and 1 at a surface.
+                    const DMedium &m = sc.media[medium]; const DGrid &g = sc.grids[m.m.sigma_t_grid];
+                    float mint, maxt;
+                    if (medium_clip(g, ray, mint, maxt)) {
+                        const float t_end = fminf(maxt, hit_t);
+                        if (mint < t_end) {
+                            DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d());
+                            for (;;) {
+                                const float mu = m.m.scale * dda_majorant(g, dd);
+                                const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
+                                const float dtau = mu * (t_exit - t);
+                                if (dtau >= tau && mu > 0.f) {
+                                    t = fminf(t + tau / mu, t_exit); cnt.collisions++;
+                                    V3 p = ray_at(ray, t);
+                                    V3 st = grid_eval<false>(g, p, nullptr) * m.m.scale, sn = mk3(mu) - st;
+                                    float pn = hmean(sn / mu);
+                                    if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); continue; }
+                                    depth += 1; lsp = p; cnt.real_scatters++;
+                                    if (!(depth < sc.max_depth)) { event = 0; break; }
+                                    thr *= (st * medium_albedo(sc, m, p)) / (mu * hmean(st / mu));
+                                    ray.o = p; hit_t = hit_t - t; event = 1; break;
+                                }
+                                tau -= dtau; t = t_exit;
+                                if (t_exit >= t_end) break;
+                                dda_advance(g, dd);
+                            }
+                        }
+                    }
+                    if (event < 0) event = 2;
+                    break;
+                }
                 if (medium >= 0) {
                     const DMedium &m = sc.media[medium];
                     MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
@@ -350,7 +383,35 @@ __global__ void __launch_bounds__(256) k_wf_nee(const __grid_constant__ DScene s
                     active &= remaining_dist > 0.f;
                     if (!active) break;
                     bool escaped_medium = false, active_medium = medium >= 0, active_surface = !active_medium; float mei_t = LR_INF;
-                    if (active_medium) {
+                    if (active_medium && medium_uses_dda(sc, sc.media[medium])) {
+                        // ratio tracking over the whole medium segment against the local majorants: T *= sigma_n / mu per tentative collision
+                        const DMedium &m = sc.media[medium]; const DGrid &g = sc.grids[m.m.sigma_t_grid];
+                        if (needs_intersection) { cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false; }
+                        float mint, maxt;
+                        if (medium_clip(g, ray, mint, maxt)) {
+                            const float t_end = fminf(maxt, si_t);
+                            if (mint < t_end) {
+                                DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d());
+                                for (;;) {
+                                    const float mu = m.m.scale * dda_majorant(g, dd);
+                                    const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
+                                    const float dtau = mu * (t_exit - t);
+                                    if (dtau >= tau && mu > 0.f) {
+                                        t = fminf(t + tau / mu, t_exit); cnt.collisions++;
+                                        V3 st = grid_eval<false>(g, ray_at(ray, t), nullptr) * m.m.scale;
+                                        transmittance *= (mk3(mu) - st) / mu;
+                                        if (!any_nonzero(transmittance)) break;
+                                        tau = -logf(1.f - smp.next_1d()); continue;
+                                    }
+                                    tau -= dtau; t = t_exit;
+                                    if (t_exit >= t_end) break;
+                                    dda_advance(g, dd);
+                                }
+                            }
+                        }
+                        if (si_t > remaining_dist) total_dist = ds_dist;        // nothing but medium up to the emitter (volpath.cpp:494-496)
+                        escaped_medium = true; active_medium = false;
+                    } else if (active_medium) {
                         const DMedium &m = sc.media[medium];
                         MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
                         if (needs_intersection) {

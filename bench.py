@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--workload", default="c3", choices=["c1", "c2", "c3", "c3xl"])
     ap.add_argument("--res", type=int, default=1080)
     ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step (0 => the config's)")
-    ap.add_argument("--tracking", default="reference", choices=["reference", "dda"])
+    ap.add_argument("--tracking", default="dda", choices=["reference", "dda"])
     ap.add_argument("--no-prb", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-spp", type=int, default=4, help="spp of the bounded CPU-baseline sample")
@@ -245,10 +245,24 @@ def run_b200(args):
     bytes_per_launch = tot["collisions"] / max(tot["tracking_launches"], 1) * 32.0
     achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
-                "kernel": f"k_render<{sc.integrator_name}> (free-flight tracking + trilinear sigma_t taps; one launch per render)",
+                "kernel": "k_wf_track + k_wf_nee (free-flight / ratio tracking with trilinear sigma_t taps; CUDA events around every launch, "
+                          "lr_stats.tracking_ms / tracking_launches)",
                 "algorithmic_bytes_per_unit": 32, "units_per_launch": tot["collisions"] / max(tot["tracking_launches"], 1),
                 "kernel_ms": k_ms, "peak_source": peak_src}
-    return dict(torch=torch, dist=dist, mi=mi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local, spp=spp, name=name,
+    ref_order = None
+    if args.tracking == "dda" and args.workload in ("c3", "c3xl"):
+        # the same render with the reference's draw order (one global majorant): the mode the per-path parity tests use
+        a2 = argparse.Namespace(**vars(args)); a2.tracking = "reference"
+        d2, _, _ = workload_scene(a2); c2 = mi.Context(local).upload(mi.load_dict(d2)); c2.set_stream(stream.cuda_stream)
+        c2.film_clear(); c2.render_lanes(7, spp, 0, 0); barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(stream); c2.film_clear(); c2.render_lanes(8 + rank, spp, 0, 0); e1.record(stream); barrier()
+        st2 = c2.stats(); ms2 = e0.elapsed_time(e1)
+        ref_order = {"value": st2["samples"] / (ms2 * 1e-3), "unit": UNIT + " per GPU", "collisions_per_sample": st2["collisions"] / max(st2["samples"], 1),
+                     "collisions_per_s": st2["collisions"] / (ms2 * 1e-3), "tracking_GBps_algorithmic": st2["collisions"] * 32.0 / max(st2["tracking_ms"], 1e-9) / 1e6,
+                     "note": "LR_TRACKING_REFERENCE: identical PCG32 draw order to the reference (global majorant)"}
+        c2.close()
+    return dict(ref_order=ref_order, torch=torch, dist=dist, mi=mi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local, spp=spp, name=name,
                 W=W, H=H, value=value, ms_max=ms_max, rays=rays, colls=colls, samples=samples, tot=tot, roofline=roofline, clk=clk,
                 barrier=barrier, flush=flush, hbm_peak=hbm_peak)
 
@@ -354,7 +368,8 @@ def main():
                            "l2": "flushed between timed iterations (512 MiB write)", "partition": "every rank renders the config with seed+rank; film all-reduce"},
                 "mrays_per_s": R["rays"] / secs / 1e6, "collisions_per_s": R["colls"] / secs,
                 "collisions_per_sample": R["colls"] / max(R["samples"], 1), "rays_per_sample": R["rays"] / max(R["samples"], 1),
-                "e2e": e2e, "gpu_launches": int(R["tot"]["launches"]), "clocks": R["clk"], "roofline": R["roofline"], "cpu_baseline": cpu, "prb": prb}
+                "e2e": e2e, "gpu_launches": int(R["tot"]["launches"]), "clocks": R["clk"], "roofline": R["roofline"], "cpu_baseline": cpu, "prb": prb,
+                "reference_order_tracking": R["ref_order"]}
         print(json.dumps(line), flush=True)
     if R["world"] > 1:
         R["dist"].destroy_process_group()

@@ -42,7 +42,7 @@ struct lr_ctx {
     DScene sc{};
     // device storage
     std::vector<DevBuf *> pool;                     // everything referenced by sc
-    DevBuf film, weight_img, work_counter, stats, scratch;
+    DevBuf film, weight_img, work_counter, stats, scratch, prb_L;
     DevBuf *tris_gid = nullptr;
     std::vector<DGrid> h_grids; DevBuf *d_grids = nullptr;
     std::vector<DMedium> h_media; DevBuf *d_media = nullptr;

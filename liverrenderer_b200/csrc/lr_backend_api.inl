@@ -194,6 +194,13 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
     a.work_counter = c->work_counter.as<unsigned long long>(); a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev;
     if (begin == end) return LR_OK;
     c->wf_launches = 0;
+    if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_PRBVOLPATH) {        // primal prbvolpath (INTEGRATOR_MAPPING renders)
+        if (int r = wf_prepare(c, (end - begin))) return r;
+        c->wf_tracking_ms = 0; c->wf_tracking_launches = 0; WFPrbArgs pa{};
+        if (p.n_passes != 1) LR_FAIL(c, LR_ERR_UNSUPPORTED, "prbvolpath: W*H*spp exceeds 2^32 lanes");
+        if (lanes_out) return c->film_channels == 5 ? wavefront_prb_pass<5, false, false>(c, a, pa) : wavefront_prb_pass<4, false, false>(c, a, pa);
+        return c->film_channels == 5 ? wavefront_prb_pass<5, true, false>(c, a, pa) : wavefront_prb_pass<4, true, false>(c, a, pa);
+    }
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATH) {
         if (int r = wf_prepare(c, (end - begin))) return r;
         if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false>(c, a) : wavefront_render_t<4, false>(c, a);
@@ -285,10 +292,14 @@ int lr_render_backward(lr_ctx *c, uint32_t seed, uint32_t spp, const float *grad
     RenderArgs a{}; a.tris_gid = c->tris_gid->as<DTri>(); a.lane_begin = lane_begin; a.lane_end = lane_end; a.seed = seed;
     a.spp_per_pass = spp; a.n_passes = 1; a.total_spp = spp; a.work_counter = c->work_counter.as<unsigned long long>();
     a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev; a.grad_in = g; a.weight_img = c->weight_img.as<float>(); a.grad_channels = gc;
+    c->wf_launches = 0;
     if (lane_end > lane_begin) {
-        int grid; if (int r = grid_for(c, k_backward, 128, grid)) return r;
-        k_backward<<<grid, 128, 0, c->stream>>>(c->sc, a);
-        LR_CUDA(c, cudaGetLastError());
+        if (c->use_wavefront) { if (int r = wavefront_prb_backward(c, a, g, gc)) return r; }
+        else {
+            int grid; if (int r = grid_for(c, k_backward, 128, grid)) return r;
+            k_backward<<<grid, 128, 0, c->stream>>>(c->sc, a);
+            LR_CUDA(c, cudaGetLastError());
+        }
     }
     return end_call(c, 2, true);
 }

@@ -229,3 +229,4 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene
 } // namespace lr
 
 #include "lr_wavefront.cuh"
+#include "lr_wavefront_prb.cuh"

@@ -48,7 +48,8 @@ def test_adjoint_matches_oracle_adjoint():
     o = orc.OracleScene(sc); o.grid_grad_zero(0); o.render_backward(g, seed=11, spp=16)
     a, b = ctx.grid_grad_read(0), o.grid_grad_read(0)
     assert np.isfinite(a).all()
-    assert np.linalg.norm(a - b) / np.linalg.norm(b) < 2e-2
+    print("adjoint vs oracle adjoint: rel L2", np.linalg.norm(a - b) / np.linalg.norm(b), "sum ratio", a.sum() / b.sum())
+    assert np.linalg.norm(a - b) / np.linalg.norm(b) < 2e-2 and abs(a.sum() / b.sum() - 1) < 1e-2      # measured 1e-6
     # accumulation: a second call adds
     ctx.render_backward(g, seed=11, spp=16)
     np.testing.assert_allclose(ctx.grid_grad_read(0), 2 * a, rtol=1e-3, atol=1e-6 * np.abs(a).max())
@@ -166,3 +167,54 @@ def test_traverse_update_recomputes_majorant():
     o = orc.OracleScene(sc)           # oracle built from the updated host array
     ref = o.render(seed=1, spp=4)
     assert np.median(np.abs(img1 - ref) / np.maximum(np.abs(ref), 1e-2)) < 1e-4
+
+
+def test_wavefront_prb_equals_per_lane_kernel(monkeypatch):
+    """prbvolpath as a wavefront (primal pass + adjoint replay through queues) vs the per-lane kernel: same PCG32 streams,
+    same draw order => lane-for-lane equal primal radiance and the same gradient up to fp32 summation order."""
+    sc = mi.load_dict(_small_inverse(res=24, spp=64)); n = 24 * 24 * 64
+    rng = np.random.default_rng(3); g = rng.standard_normal((24, 24, 3)).astype(np.float32)
+    wf = mi.Context(0).upload(sc); a = wf.sample_lanes(5, 64, 0, n)
+    wf.grid_grad_zero(0); wf.render_backward(g, seed=7, spp=64); ga = wf.grid_grad_read(0); st = wf.stats()
+    monkeypatch.setenv("LR_MEGAKERNEL", "1")
+    mk = mi.Context(0).upload(sc); b = mk.sample_lanes(5, 64, 0, n)
+    mk.grid_grad_zero(0); mk.render_backward(g, seed=7, spp=64); gb = mk.grid_grad_read(0)
+    assert st["launches"] > 16
+    assert np.array_equal(a[:, 3], b[:, 3])
+    frac = float(((np.abs(a[:, :3] - b[:, :3]) / np.maximum(np.abs(b[:, :3]), 1e-3)).max(axis=1) < 1e-5).mean())
+    rel = float(np.linalg.norm(ga - gb) / np.linalg.norm(gb))
+    print("wavefront vs per-lane prb: lanes equal", frac, "gradient rel L2", rel, "sum ratio", ga.sum() / gb.sum())
+    assert frac > 0.999                     # measured 1.0; head-room for an ulp flipping a null/real decision
+    assert rel < 1e-2 and abs(ga.sum() / gb.sum() - 1) < 5e-3      # measured 3e-7
+
+
+def test_dda_adjoint_closed_form():
+    """The closed-form absorbing-cube gradient with the production (majorant-DDA) tracking mode: the local majorants are
+    detached like the reference's global one, the estimator stays unbiased."""
+    res, spp, gr, scale, rho = 12, 16384, 8, 2.0, 0.35
+    grid = np.full((gr, gr, gr, 1), rho, dtype=np.float32); grid[: gr // 2] *= 0.5           # two density levels => different local majorants
+    def scene(tracking):
+        return mi.load_dict({"type": "scene", "integrator": {"type": "prbvolpath", "max_depth": 8, "rr_depth": 64, "tracking": tracking, "majorant_cell": 2},
+            "sensor": {"type": "perspective", "fov": 30.0, "near_clip": 0.01, "far_clip": 100.0,
+                       "to_world": mi.T().look_at(origin=[0.3, 0.4, -4.0], target=[0, 0, 0], up=[0, 1, 0]),
+                       "sampler": {"type": "independent", "sample_count": spp},
+                       "film": {"type": "hdrfilm", "width": res, "height": res, "rfilter": {"type": "box"}, "pixel_format": "rgb"}},
+            "cube": {"type": "cube", "to_world": mi.T().scale(0.5), "bsdf": {"type": "null"},
+                     "interior": {"type": "heterogeneous", "scale": scale,
+                                  "sigma_t": {"type": "gridvolume", "grid": grid, "max_value": 2 * rho,      # sigma_n > 0 everywhere: the detached
+                                              "to_world": mi.T().translate([-0.5, -0.5, -0.5])},            # gradient estimator is singular at sigma_n = 0
+                                  "albedo": {"type": "rgb", "value": [0.0, 0.0, 0.0]}}},
+            "env": {"type": "constant", "radiance": {"type": "rgb", "value": [1, 1, 1]}}})
+    out = {}
+    for tr in ("reference", "dda"):
+        ctx = mi.Context(0).upload(scene(tr)); img = ctx.render(seed=1, spp=spp).astype(np.float64)
+        g_in = np.full((res, res, 3), 1.0 / (res * res * 3), dtype=np.float32)
+        ctx.grid_grad_zero(0); ctx.render_backward(g_in, seed=1, spp=spp)
+        out[tr] = (img.mean(), ctx.grid_grad_read(0).astype(np.float64).reshape(gr, gr, gr), ctx.stats()["collisions"])
+    (m_r, g_r, c_r), (m_d, g_d, c_d) = out["reference"], out["dda"]
+    assert abs(m_r - m_d) / m_r < 2e-3
+    # per-z-slab sums of the gradient (128 voxels each) agree between the two estimators
+    s_r, s_d = g_r.sum(axis=(1, 2)), g_d.sum(axis=(1, 2))
+    assert np.all(np.abs(s_r - s_d) < 3e-2 * np.abs(s_r).max()), (s_r, s_d)
+    assert abs(g_r.sum() - g_d.sum()) / abs(g_r.sum()) < 1e-2
+    assert c_d < c_r

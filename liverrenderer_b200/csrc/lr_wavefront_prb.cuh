@@ -195,6 +195,13 @@ LR_DEV bool wfp_nee_setup(const DScene &sc, const WFArgs &a, WState *S, Sampler 
     if (ref_si && mesh_is_transition(sc, ref_si->mesh)) medium = target_medium(sc, *ref_si, ds.d);
     Ray ray = spawn_ray_to(ref_p, ref_n, ds.p);
     cnt.rays++; Hit h = bvh_trace<false, false>(sc, ray);
+    if (sc.integ.tracking == LR_TRACKING_DDA && hit_valid(h)) {
+        // production mode: opaque-occluder pre-test.  A non-null surface anywhere on the shadow segment makes the transmittance
+        // exactly 0 (eval_null_transmission), so the ratio-tracking walk is skipped; only the RNG consumption differs.
+        bool blocked = true;
+        if (sc.any_null_bsdf) { cnt.rays++; blocked = hit_valid(bvh_trace<true, true>(sc, ray)); }
+        if (blocked) return false;
+    }
     S->no_maxd = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
     S->nd_total = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
     S->ne_dist = make_float4(emitter_val.x, emitter_val.y, emitter_val.z, ds.dist);

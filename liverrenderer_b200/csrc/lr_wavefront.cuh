@@ -49,11 +49,11 @@ static_assert(sizeof(WState) == 256, "WState layout");
 
 struct WQueues {                       // device-side counters, one 64-byte block
     uint32_t n_active[2]; uint32_t n_scatter; uint32_t n_surf[WF_N_SURF]; uint32_t n_regen; uint32_t live;
-    unsigned long long lane_next; uint32_t pad[6];
+    unsigned long long lane_next; uint32_t n_nee; uint32_t pad[5];
 };
 
 struct WFArgs {
-    WState *st; WQueues *q; uint32_t *q_active[2]; uint32_t *q_scatter; uint32_t *q_surf[WF_N_SURF]; uint32_t *q_regen;
+    WState *st; WQueues *q; uint32_t *q_active[2]; uint32_t *q_scatter; uint32_t *q_surf[WF_N_SURF]; uint32_t *q_regen; uint32_t *q_nee;   // q_nee: slots whose NEE walk is live
     uint32_t cap; int cur;            // slots; index of the input active queue
     const DTri *tris_gid; float *film; float *lanes_out;
     uint64_t lane_begin, lane_end; uint32_t seed, spp_per_pass, n_passes;
@@ -288,8 +288,9 @@ LR_DEV bool wf_nee_setup(const DScene &sc, const WFArgs &a, WState *S, Sampler &
 __global__ void __launch_bounds__(256) k_wf_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     WF_FOR_QUEUE(a.q->n_scatter) {
-        if (qi < _n) {
-            WState *S = a.st + a.q_scatter[qi];
+        bool item = qi < _n, nee = false; uint32_t slot = item ? a.q_scatter[qi] : 0;
+        if (item) {
+            WState *S = a.st + slot;
             Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
             uint32_t f = wf_flags(*S); int medium = wf_medium(f);
             const DMedium &m = sc.media[medium]; Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
@@ -306,8 +307,9 @@ __global__ void __launch_bounds__(256) k_wf_shade_a_medium(const __grid_constant
                 }
                 S->rng_state = smp.state; S->rng_inc = smp.inc;
             }
-            S->lsp_flags.w = __uint_as_float(f);
+            S->lsp_flags.w = __uint_as_float(f); nee = (f & WF_NEE_ACTIVE) != 0;
         }
+        wf_push(a.q_nee, &a.q->n_nee, slot, nee);
     }
     flush_counters(cnt, 0, a.stats);
 }
@@ -317,7 +319,7 @@ template <int C, bool TO_FILM>
 __global__ void __launch_bounds__(128) k_wf_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {
-        bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false;
+        bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false, nee = false;
         if (item) {
             WState *S = a.st + slot;
             Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
@@ -358,23 +360,23 @@ __global__ void __launch_bounds__(128) k_wf_shade_a_surface(const __grid_constan
             }
             S->rng_state = smp.state; S->rng_inc = smp.inc;
             S->res_depth = make_float4(result.x, result.y, result.z, r4.w);
-            S->lsp_flags.w = __uint_as_float(f);
+            S->lsp_flags.w = __uint_as_float(f); nee = (f & WF_NEE_ACTIVE) != 0;
         }
         wf_push(a.q_regen, &a.q->n_regen, slot, dead);
+        wf_push(a.q_nee, &a.q->n_nee, slot, nee);
     }
     flush_counters(cnt, 0, a.stats);
 }
 
 // ------------------------------------------------------------------------------------------
 // NEE: transmittance along the shadow segment (volpath.cpp:454-551), ratio tracking through media and
-// index-matched (null) boundaries.  Runs over the scatter queue and every surface bucket.
+// index-matched (null) boundaries.  Runs over the NEE queue the SHADE_A kernels fill.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_wf_nee(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, uint32_t surf_mask) {
-    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
-    for (int qsel = 0; qsel <= WF_N_SURF; ++qsel) {
-    if (qsel > 0 && !((surf_mask >> (qsel - 1)) & 1u)) continue;
-    const uint32_t *queue = qsel == 0 ? a.q_scatter : a.q_surf[qsel - 1];
-    WF_FOR_QUEUE(qsel == 0 ? a.q->n_scatter : a.q->n_surf[qsel - 1]) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; (void) surf_mask;
+    {
+    const uint32_t *queue = a.q_nee;
+    WF_FOR_QUEUE(a.q->n_nee) {
         if (qi < _n) {
             WState *S = a.st + queue[qi]; uint32_t f = wf_flags(*S);
             if ((f & WF_NEE_ACTIVE) && !(f & WF_DEAD)) {
@@ -538,12 +540,12 @@ __global__ void __launch_bounds__(128) k_wf_shade_b_surface(const __grid_constan
 }
 
 __global__ void k_wf_begin_iteration(WQueues *q, int cur) {     // counters of the queues this iteration fills
-    q->n_active[cur ^ 1] = 0; q->n_scatter = 0; q->n_regen = 0;
+    q->n_active[cur ^ 1] = 0; q->n_scatter = 0; q->n_regen = 0; q->n_nee = 0;
     for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
 }
 __global__ void k_wf_init(WQueues *q, uint32_t *q_regen, uint32_t cap, WState *st) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) { q->n_active[0] = q->n_active[1] = 0; q->n_scatter = 0; q->n_regen = cap; q->lane_next = 0; for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0; }
+    if (i == 0) { q->n_active[0] = q->n_active[1] = 0; q->n_scatter = 0; q->n_regen = cap; q->lane_next = 0; q->n_nee = 0; for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0; }
     if (i < cap) { q_regen[i] = i; st[i].lsp_flags.w = __uint_as_float(0u); }
 }
 

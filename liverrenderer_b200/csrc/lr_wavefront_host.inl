@@ -14,7 +14,7 @@ static int wf_prepare(lr_ctx *c, uint64_t n_lanes) {
     if (w.cap < want) {
         w.cap = (uint32_t) want;
         LR_CUDA(c, w.states.alloc((size_t) w.cap * sizeof(WState)));
-        LR_CUDA(c, w.queues.alloc((size_t) w.cap * 4 * (4 + WF_N_SURF)));
+        LR_CUDA(c, w.queues.alloc((size_t) w.cap * 4 * (5 + WF_N_SURF)));
         LR_CUDA(c, w.counters.alloc(sizeof(WQueues)));
     }
     if (!w.live_host) {
@@ -32,6 +32,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
     uint32_t *qb = w.queues.as<uint32_t>();
     a.q_active[0] = qb; a.q_active[1] = qb + w.cap; a.q_scatter = qb + 2 * (size_t) w.cap; a.q_regen = qb + 3 * (size_t) w.cap;
     for (int b = 0; b < WF_N_SURF; ++b) a.q_surf[b] = qb + (4 + b) * (size_t) w.cap;
+    a.q_nee = qb + (4 + WF_N_SURF) * (size_t) w.cap;
     a.tris_gid = ra.tris_gid; a.film = ra.film; a.lanes_out = ra.lanes_out; a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end;
     a.seed = ra.seed; a.spp_per_pass = ra.spp_per_pass; a.n_passes = ra.n_passes; a.stats = ra.stats;
     // surface buckets present in this scene (bucket 0 also takes escaped rays)
@@ -86,6 +87,7 @@ static int wavefront_prb_pass(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs &
     uint32_t *qb = w.queues.as<uint32_t>();
     a.q_active[0] = qb; a.q_active[1] = qb + w.cap; a.q_scatter = qb + 2 * (size_t) w.cap; a.q_regen = qb + 3 * (size_t) w.cap;
     for (int b = 0; b < WF_N_SURF; ++b) a.q_surf[b] = qb + (4 + b) * (size_t) w.cap;
+    a.q_nee = qb + (4 + WF_N_SURF) * (size_t) w.cap;
     a.tris_gid = ra.tris_gid; a.film = ra.film; a.lanes_out = ra.lanes_out; a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end;
     a.seed = ra.seed; a.spp_per_pass = ra.spp_per_pass; a.n_passes = 1; a.stats = ra.stats;
     uint32_t surf_mask = 1u | c->surf_bucket_mask;

@@ -214,8 +214,9 @@ LR_DEV bool wfp_nee_setup(const DScene &sc, const WFArgs &a, WState *S, Sampler 
 __global__ void __launch_bounds__(256) k_wfp_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     WF_FOR_QUEUE(a.q->n_scatter) {
-        if (qi < _n) {
-            WState *S = a.st + a.q_scatter[qi];
+        bool item = qi < _n, nee = false; uint32_t slot = item ? a.q_scatter[qi] : 0;
+        if (item) {
+            WState *S = a.st + slot;
             Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
             uint32_t f = wf_flags(*S); int medium = wf_medium(f);
             const DMedium &m = sc.media[medium]; Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
@@ -232,8 +233,9 @@ __global__ void __launch_bounds__(256) k_wfp_shade_a_medium(const __grid_constan
                 }
                 S->rng_state = smp.state; S->rng_inc = smp.inc;
             }
-            S->lsp_flags.w = __uint_as_float(f);
+            S->lsp_flags.w = __uint_as_float(f); nee = (f & WF_NEE_ACTIVE) != 0;
         }
+        wf_push(a.q_nee, &a.q->n_nee, slot, nee);
     }
     flush_counters(cnt, 0, a.stats);
 }
@@ -243,7 +245,7 @@ template <int C, bool TO_FILM, bool ADJ>
 __global__ void __launch_bounds__(128) k_wfp_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; const float sgn = ADJ ? -1.f : 1.f;
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {
-        bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false;
+        bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false, nee = false;
         if (item) {
             WState *S = a.st + slot;
             Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
@@ -284,9 +286,10 @@ __global__ void __launch_bounds__(128) k_wfp_shade_a_surface(const __grid_consta
             }
             S->rng_state = smp.state; S->rng_inc = smp.inc;
             S->res_depth = make_float4(L.x, L.y, L.z, r4.w);
-            S->lsp_flags.w = __uint_as_float(f);
+            S->lsp_flags.w = __uint_as_float(f); nee = (f & WF_NEE_ACTIVE) != 0;
         }
         wf_push(a.q_regen, &a.q->n_regen, slot, dead);
+        wf_push(a.q_nee, &a.q->n_nee, slot, nee);
     }
     flush_counters(cnt, 0, a.stats);
 }
@@ -384,10 +387,10 @@ LR_DEV V3 wfp_nee_walk(const DScene &sc, const WFArgs &a, const WState *S, Sampl
 template <bool ADJ>
 __global__ void __launch_bounds__(256) k_wfp_nee(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, uint32_t surf_mask) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; const float sgn = ADJ ? -1.f : 1.f;
-    for (int qsel = 0; qsel <= WF_N_SURF; ++qsel) {
-        if (qsel > 0 && !((surf_mask >> (qsel - 1)) & 1u)) continue;
-        const uint32_t *queue = qsel == 0 ? a.q_scatter : a.q_surf[qsel - 1];
-        WF_FOR_QUEUE(qsel == 0 ? a.q->n_scatter : a.q->n_surf[qsel - 1]) {
+    (void) surf_mask;
+    {
+        const uint32_t *queue = a.q_nee;
+        WF_FOR_QUEUE(a.q->n_nee) {
             if (qi < _n) {
                 WState *S = a.st + queue[qi]; uint32_t f = wf_flags(*S);
                 if ((f & WF_NEE_ACTIVE) && !(f & WF_DEAD)) {

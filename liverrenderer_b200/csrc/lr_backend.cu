@@ -253,4 +253,15 @@ static int build_lbvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi) {
     return LR_OK;
 }
 
+#include "lr_bvh_host.inl"
+
+// Builder choice: SAH on the host up to 4 Mi triangles (scene-load cost of milliseconds to seconds, cheapest traversal),
+// Morton LBVH on the device above that.  LR_BVH=lbvh|sah overrides.
+static int build_bvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi) {
+    const char *e = getenv("LR_BVH");
+    bool lbvh = e ? strcmp(e, "lbvh") == 0 : tris.size() > (size_t(1) << 22);
+    if (tris.size() < 2 || lbvh) return build_lbvh(c, tris, lo, hi);
+    return build_sah_bvh(c, tris, lo, hi);
+}
+
 #include "lr_backend_api.inl"

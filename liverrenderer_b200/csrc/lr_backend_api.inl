@@ -62,7 +62,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     }
     { DevBuf *b = c->newbuf(); if (int r = upload(c, b, meshes.data(), meshes.size())) return r; sc.meshes = b->as<DMesh>(); sc.n_meshes = s->n_meshes; }
     { DevBuf *b = c->newbuf(); if (int r = upload(c, b, s->bsdfs, s->n_bsdfs)) return r; sc.bsdfs = b->as<lr_bsdf>(); }
-    if (int r = build_lbvh(c, tris, lo, hi)) return r;
+    if (int r = build_bvh(c, tris, lo, hi)) return r;
 
     // ---- grids ----
     c->h_grids.resize(s->n_grids); c->grid_floats.resize(s->n_grids); c->grid_fixed_max.assign(s->n_grids, -1.f);

@@ -34,8 +34,12 @@ def test_no_scene_error():
         ctx._chk(ctx.lib.lr_render_lanes(ctx.ctx, 0, 1, 0, 0), "lr_render_lanes")
 
 
+@pytest.mark.parametrize("builder", ["sah", "lbvh"])
 @pytest.mark.parametrize("scene_name", ["cornell", "liver", "sphere_base"])
-def test_lbvh_closest_hit_exact(scene_name):
+def test_lbvh_closest_hit_exact(scene_name, builder, monkeypatch):
+    """Both acceleration-structure builders (host SAH: default; device Morton LBVH: large inputs) return the oracle's
+    brute-force closest hit bit for bit -- t, barycentrics and the primitive id (ties go to the lower id)."""
+    monkeypatch.setenv("LR_BVH", builder)
     rng = np.random.default_rng(12345)
     if scene_name == "cornell":
         sc = mi.load_dict(scenes.cornell_box_path(res=16, spp=1)); lo, hi = np.array([-1.2] * 3), np.array([1.2] * 3)
@@ -203,6 +207,14 @@ def test_wavefront_equals_per_lane_kernel(monkeypatch):
     assert np.array_equal(a[:, 3], b[:, 3])
     assert (rel_err(a[:, :3], b[:, :3], 1e-3).max(axis=1) < 1e-5).mean() > 0.999
     assert st_a["collisions"] == st_b["collisions"] and st_a["real_scatters"] == st_b["real_scatters"]
+
+
+def test_bvh_builders_agree(monkeypatch):
+    """The hit does not depend on the tree (same triangle test, ties by primitive id): SAH and LBVH renders are identical."""
+    sc = mi.load_dict(scenes.liver_multi_mesh(res=48, spp=4)); n = 48 * 48 * 4
+    monkeypatch.setenv("LR_BVH", "sah"); a = mi.Context(0).upload(sc).sample_lanes(5, 4, 0, n)
+    monkeypatch.setenv("LR_BVH", "lbvh"); b = mi.Context(0).upload(sc).sample_lanes(5, 4, 0, n)
+    assert np.array_equal(a, b)
 
 
 def test_wavefront_small_pool_and_film(monkeypatch):

@@ -104,6 +104,20 @@ LR_DEV void dda_advance(const DGrid &g, DDA &d) {
     else if (d.tny <= d.tnz) { d.iy = min(max(d.iy + d.sy, 0), g.my - 1); d.tny += d.tdy; }
     else { d.iz = min(max(d.iz + d.sz, 0), g.mz - 1); d.tnz += d.tdz; }
 }
+// Advance the DDA until the carried optical depth `tau` is used up -- tentative collision at `t` under majorant `mu`, returns
+// true -- or the end of the segment is reached (false).  Kept as its own loop so that a warp first brings every lane to its
+// next collision (cheap steps) and then evaluates the collisions together (expensive: 8 grid taps, RNG, log).
+LR_DEV bool dda_walk(const DGrid &g, float mu_scale, DDA &dd, float &t, float &tau, float t_end, float &mu) {
+    for (;;) {
+        mu = mu_scale * dda_majorant(g, dd);
+        const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
+        const float dtau = mu * (t_exit - t);
+        if (dtau >= tau && mu > 0.f) { t = fminf(t + tau / mu, t_exit); return true; }
+        tau -= dtau; t = t_exit;
+        if (t_exit >= t_end) return false;
+        dda_advance(g, dd);
+    }
+}
 // clip of the segment against the volume's AABB exactly as Medium::sample_interaction does (medium.cpp:53-60)
 LR_DEV bool medium_clip(const DGrid &g, const Ray &ray, float &mint, float &maxt) {
     bool its = aabb_intersect(g.bmin, g.bmax, ray, mint, maxt);

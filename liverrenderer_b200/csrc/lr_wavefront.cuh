@@ -187,25 +187,17 @@ __global__ void __launch_bounds__(256) k_wf_track(const __grid_constant__ DScene
                     if (medium_clip(g, ray, mint, maxt)) {
                         const float t_end = fminf(maxt, hit_t);
                         if (mint < t_end) {
-                            DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d());
-                            for (;;) {
-                                const float mu = m.m.scale * dda_majorant(g, dd);
-                                const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
-                                const float dtau = mu * (t_exit - t);
-                                if (dtau >= tau && mu > 0.f) {
-                                    t = fminf(t + tau / mu, t_exit); cnt.collisions++;
-                                    V3 p = ray_at(ray, t);
-                                    V3 st = grid_eval<false>(g, p, nullptr) * m.m.scale, sn = mk3(mu) - st;
-                                    float pn = hmean(sn / mu);
-                                    if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); continue; }
-                                    depth += 1; lsp = p; cnt.real_scatters++;
-                                    if (!(depth < sc.max_depth)) { event = 0; break; }
-                                    thr *= (st * medium_albedo(sc, m, p)) / (mu * hmean(st / mu));
-                                    ray.o = p; hit_t = hit_t - t; event = 1; break;
-                                }
-                                tau -= dtau; t = t_exit;
-                                if (t_exit >= t_end) break;
-                                dda_advance(g, dd);
+                            DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
+                            while (dda_walk(g, m.m.scale, dd, t, tau, t_end, mu)) {
+                                cnt.collisions++;
+                                V3 p = ray_at(ray, t);
+                                V3 st = grid_eval<false>(g, p, nullptr) * m.m.scale, sn = mk3(mu) - st;
+                                float pn = hmean(sn / mu);
+                                if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); continue; }
+                                depth += 1; lsp = p; cnt.real_scatters++;
+                                if (!(depth < sc.max_depth)) { event = 0; break; }
+                                thr *= (st * medium_albedo(sc, m, p)) / (mu * hmean(st / mu));
+                                ray.o = p; hit_t = hit_t - t; event = 1; break;
                             }
                         }
                     }
@@ -400,21 +392,13 @@ __global__ void __launch_bounds__(256) k_wf_nee(const __grid_constant__ DScene s
                         if (medium_clip(g, ray, mint, maxt)) {
                             const float t_end = fminf(maxt, si_t);
                             if (mint < t_end) {
-                                DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d());
-                                for (;;) {
-                                    const float mu = m.m.scale * dda_majorant(g, dd);
-                                    const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
-                                    const float dtau = mu * (t_exit - t);
-                                    if (dtau >= tau && mu > 0.f) {
-                                        t = fminf(t + tau / mu, t_exit); cnt.collisions++;
-                                        V3 st = grid_eval<false>(g, ray_at(ray, t), nullptr) * m.m.scale;
-                                        transmittance *= (mk3(mu) - st) / mu;
-                                        if (!any_nonzero(transmittance)) break;
-                                        tau = -logf(1.f - smp.next_1d()); continue;
-                                    }
-                                    tau -= dtau; t = t_exit;
-                                    if (t_exit >= t_end) break;
-                                    dda_advance(g, dd);
+                                DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
+                                while (dda_walk(g, m.m.scale, dd, t, tau, t_end, mu)) {
+                                    cnt.collisions++;
+                                    V3 st = grid_eval<false>(g, ray_at(ray, t), nullptr) * m.m.scale;
+                                    transmittance *= (mk3(mu) - st) / mu;
+                                    if (!any_nonzero(transmittance)) break;
+                                    tau = -logf(1.f - smp.next_1d());
                                 }
                             }
                         }

@@ -119,15 +119,7 @@ __global__ void __launch_bounds__(256) k_wfp_track(const __grid_constant__ DScen
                         const float t_end = fminf(maxt, hit_t);
                         if (mint < t_end) {
                             DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d());
-                            for (;;) {
-                                mu = m.m.scale * dda_majorant(g, dd) * kPrbMajorantSlack;
-                                const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
-                                const float dtau = mu * (t_exit - t);
-                                if (dtau >= tau && mu > 0.f) { t_c = fminf(t + tau / mu, t_exit); valid = true; break; }
-                                tau -= dtau; t = t_exit;
-                                if (t_exit >= t_end) break;
-                                dda_advance(g, dd);
-                            }
+                            valid = dda_walk(g, m.m.scale * kPrbMajorantSlack, dd, t, tau, t_end, mu); t_c = t;
                         }
                     }
                     if (!valid) { event = 2; break; }
@@ -319,28 +311,20 @@ LR_DEV V3 wfp_nee_walk(const DScene &sc, const WFArgs &a, const WState *S, Sampl
                 if (medium_clip(g, ray, mint, maxt)) {
                     const float t_end = fminf(maxt, si_t);
                     if (mint < t_end) {
-                        DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d());
-                        for (;;) {
-                            const float mu = m.m.scale * dda_majorant(g, dd) * kPrbMajorantSlack;
-                            const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
-                            const float dtau = mu * (t_exit - t);
-                            if (dtau >= tau && mu > 0.f) {
-                                t = fminf(t + tau / mu, t_exit); cnt.collisions++;
-                                GridTap tap; V3 st = grid_eval<SCATTER>(g, ray_at(ray, t), &tap) * m.m.scale; V3 tm = (mk3(mu) - st) / mu;
-                                if (SCATTER) {
-                                    float gs = 0.f;
-                                    if (tm.x > 0.f) gs += (dL.x * adj.x / tm.x) * (-m.m.scale / mu);
-                                    if (tm.y > 0.f) gs += (dL.y * adj.y / tm.y) * (-m.m.scale / mu);
-                                    if (tm.z > 0.f) gs += (dL.z * adj.z / tm.z) * (-m.m.scale / mu);
-                                    if (g.differentiable && g.ch == 1 && gs != 0.f) grid_grad_scatter(g, tap, gs, true);
-                                }
-                                transmittance *= tm;
-                                if (!any_nonzero(transmittance)) break;
-                                tau = -logf(1.f - smp.next_1d()); continue;
+                        DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
+                        while (dda_walk(g, m.m.scale * kPrbMajorantSlack, dd, t, tau, t_end, mu)) {
+                            cnt.collisions++;
+                            GridTap tap; V3 st = grid_eval<SCATTER>(g, ray_at(ray, t), &tap) * m.m.scale; V3 tm = (mk3(mu) - st) / mu;
+                            if (SCATTER) {
+                                float gs = 0.f;
+                                if (tm.x > 0.f) gs += (dL.x * adj.x / tm.x) * (-m.m.scale / mu);
+                                if (tm.y > 0.f) gs += (dL.y * adj.y / tm.y) * (-m.m.scale / mu);
+                                if (tm.z > 0.f) gs += (dL.z * adj.z / tm.z) * (-m.m.scale / mu);
+                                if (g.differentiable && g.ch == 1 && gs != 0.f) grid_grad_scatter(g, tap, gs, true);
                             }
-                            tau -= dtau; t = t_exit;
-                            if (t_exit >= t_end) break;
-                            dda_advance(g, dd);
+                            transmittance *= tm;
+                            if (!any_nonzero(transmittance)) break;
+                            tau = -logf(1.f - smp.next_1d());
                         }
                     }
                 }

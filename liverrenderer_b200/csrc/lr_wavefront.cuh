@@ -16,6 +16,11 @@
 #pragma once
 #include "lr_integrators.cuh"
 
+// resident 256-thread blocks per SM the stage kernels are compiled for (register cap = 65536 / (256 * LR_WF_OCC))
+#ifndef LR_WF_OCC
+#define LR_WF_OCC 4
+#endif
+
 namespace lr {
 
 enum : uint32_t {
@@ -105,7 +110,7 @@ LR_DEV void wf_finish(const DScene &sc, const WFArgs &a, const WState &S, V3 L, 
 // ------------------------------------------------------------------------------------------
 // GEN: every free slot takes the next pass of its lane or the next global lane (integrator.cpp:321-356)
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_wf_gen(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_gen(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; unsigned long long nsamples = 0;
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     WF_FOR_QUEUE(a.q->n_regen) {
@@ -156,7 +161,7 @@ __global__ void __launch_bounds__(256) k_wf_gen(const __grid_constant__ DScene s
 // TRACK: volpath.cpp:160-253 -- russian roulette, free-flight sampling, null collisions in registers
 // ------------------------------------------------------------------------------------------
 template <int C, bool TO_FILM>
-__global__ void __launch_bounds__(256) k_wf_track(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     const uint32_t *q_in = a.q_active[a.cur];
     WF_FOR_QUEUE(a.q->n_active[a.cur]) {
@@ -277,7 +282,7 @@ LR_DEV bool wf_nee_setup(const DScene &sc, const WFArgs &a, WState *S, Sampler &
 }
 
 // SHADE_A, medium scatter (volpath.cpp:256-283)
-__global__ void __launch_bounds__(256) k_wf_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     WF_FOR_QUEUE(a.q->n_scatter) {
         bool item = qi < _n, nee = false; uint32_t slot = item ? a.q_scatter[qi] : 0;
@@ -308,7 +313,7 @@ __global__ void __launch_bounds__(256) k_wf_shade_a_medium(const __grid_constant
 
 // SHADE_A, surface / escape (volpath.cpp:300-362)
 template <int C, bool TO_FILM>
-__global__ void __launch_bounds__(128) k_wf_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
+__global__ void __launch_bounds__(128, 2 * LR_WF_OCC) k_wf_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {
         bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false, nee = false;
@@ -364,7 +369,7 @@ __global__ void __launch_bounds__(128) k_wf_shade_a_surface(const __grid_constan
 // NEE: transmittance along the shadow segment (volpath.cpp:454-551), ratio tracking through media and
 // index-matched (null) boundaries.  Runs over the NEE queue the SHADE_A kernels fill.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_wf_nee(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, uint32_t surf_mask) {
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_nee(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, uint32_t surf_mask) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; (void) surf_mask;
     {
     const uint32_t *queue = a.q_nee;
@@ -460,7 +465,7 @@ __global__ void __launch_bounds__(256) k_wf_nee(const __grid_constant__ DScene s
 }
 
 // SHADE_B, medium scatter: phase-function sampling (volpath.cpp:285-297) + closest hit of the new ray
-__global__ void __launch_bounds__(256) k_wf_shade_b_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_shade_b_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     WF_FOR_QUEUE(a.q->n_scatter) {
@@ -484,7 +489,7 @@ __global__ void __launch_bounds__(256) k_wf_shade_b_medium(const __grid_constant
 }
 
 // SHADE_B, surface: BSDF sampling, next ray, medium transition (volpath.cpp:364-389)
-__global__ void __launch_bounds__(128) k_wf_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
+__global__ void __launch_bounds__(128, 2 * LR_WF_OCC) k_wf_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {

@@ -9,6 +9,10 @@
 #pragma once
 #include "lr_wavefront.cuh"
 
+#ifndef LR_WFP_OCC
+#define LR_WFP_OCC 4
+#endif
+
 namespace lr {
 
 // The detached-sampling gradient of a null collision is dL * L * (-scale) / sigma_n: singular where the majorant is tight.
@@ -25,7 +29,7 @@ struct WFPrbArgs {                     // extra inputs of the PRB passes
 // GEN (common.py:231-309 sample_rays; adjoint: delta L of the lane = adjoint of splat + develop, common.py:370-400)
 // ------------------------------------------------------------------------------------------
 template <bool ADJ>
-__global__ void __launch_bounds__(256) k_wfp_gen(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, const __grid_constant__ WFPrbArgs pa) {
+__global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_gen(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, const __grid_constant__ WFPrbArgs pa) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; unsigned long long nsamples = 0;
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     const bool box = sc.sensor.rfilter == LR_RFILTER_BOX, coalesce = a.spp_per_pass >= 4;
@@ -85,7 +89,7 @@ LR_DEV void wfp_scatter_main(const DScene &sc, const DMedium &m, const GridTap &
 // TRACK (prbvolpath.py:141-204)
 // ------------------------------------------------------------------------------------------
 template <int C, bool TO_FILM, bool ADJ>
-__global__ void __launch_bounds__(256) k_wfp_track(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_track(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     const uint32_t *q_in = a.q_active[a.cur];
     WF_FOR_QUEUE(a.q->n_active[a.cur]) {
@@ -203,7 +207,7 @@ LR_DEV bool wfp_nee_setup(const DScene &sc, const WFArgs &a, WState *S, Sampler 
 }
 
 // SHADE_A, medium scatter (prbvolpath.py:259-291, medium part)
-__global__ void __launch_bounds__(256) k_wfp_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     WF_FOR_QUEUE(a.q->n_scatter) {
         bool item = qi < _n, nee = false; uint32_t slot = item ? a.q_scatter[qi] : 0;
@@ -234,7 +238,7 @@ __global__ void __launch_bounds__(256) k_wfp_shade_a_medium(const __grid_constan
 
 // SHADE_A, surface / escape (prbvolpath.py:206-291, surface part).  sgn = +1 primal, -1 adjoint.
 template <int C, bool TO_FILM, bool ADJ>
-__global__ void __launch_bounds__(128) k_wfp_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
+__global__ void __launch_bounds__(128, 2 * LR_WFP_OCC) k_wfp_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; const float sgn = ADJ ? -1.f : 1.f;
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {
         bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false, nee = false;
@@ -369,7 +373,7 @@ LR_DEV V3 wfp_nee_walk(const DScene &sc, const WFArgs &a, const WState *S, Sampl
 }
 
 template <bool ADJ>
-__global__ void __launch_bounds__(256) k_wfp_nee(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, uint32_t surf_mask) {
+__global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_nee(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, uint32_t surf_mask) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; const float sgn = ADJ ? -1.f : 1.f;
     (void) surf_mask;
     {
@@ -398,7 +402,7 @@ __global__ void __launch_bounds__(256) k_wfp_nee(const __grid_constant__ DScene 
 }
 
 // SHADE_B, medium (prbvolpath.py:293-309)
-__global__ void __launch_bounds__(256) k_wfp_shade_b_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_shade_b_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     WF_FOR_QUEUE(a.q->n_scatter) {
@@ -425,7 +429,7 @@ __global__ void __launch_bounds__(256) k_wfp_shade_b_medium(const __grid_constan
 
 // SHADE_B, surface (prbvolpath.py:311-345): a BSDF sample with pdf = 0 ends the path
 template <int C, bool TO_FILM, bool ADJ>
-__global__ void __launch_bounds__(128) k_wfp_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
+__global__ void __launch_bounds__(128, 2 * LR_WFP_OCC) k_wfp_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {

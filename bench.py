@@ -272,14 +272,16 @@ def run_e2e(R, args):
     lr_grid_update recomputes majorant + super-grid), render, developed image device -> pinned host."""
     torch, ctx, sc, dev, world, rank = R["torch"], R["ctx"], R["sc"], R["dev"], R["world"], R["rank"]
     dist = R["dist"]; W, H, spp = R["W"], R["H"], R["spp"]
-    gi = 0; n = ctx.grid_size(gi)
-    grid_host = torch.from_numpy(np.ascontiguousarray(sc.grid_arrays[gi]).reshape(-1)).pin_memory()
+    has_grid = len(sc.grid_arrays) > 0                            # C1/C2 have no gridvolume: the step's only host traffic is the image
+    gi = 0; n = ctx.grid_size(gi) if has_grid else 0
+    grid_host = torch.from_numpy(np.ascontiguousarray(sc.grid_arrays[gi]).reshape(-1)).pin_memory() if has_grid else None
     out_host = torch.empty((H, W, sc.out_channels), dtype=torch.float32).pin_memory()
     film_buf = torch.empty((H, W, ctx.film_channels()), dtype=torch.float32, device=dev)
     steps = max(1, min(args.steps, 2))
 
     def step(k):
-        ctx.grid_update(gi, grid_host)                          # H2D of the step's input + majorant rebuild
+        if has_grid:
+            ctx.grid_update(gi, grid_host)                      # H2D of the step's input + majorant rebuild
         if world == 1:
             ctx.render(seed=1000 * k + rank, spp=spp, out=out_host)          # render + develop + D2H
         else:

@@ -54,7 +54,8 @@ struct lr_ctx {
     lr_stats st{};
     int blocks_per_sm[8] = {0}; int n_sm = 148;
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
-    WavefrontBuffers *wf = nullptr; uint64_t wf_pool_slots = 1ull << 22; uint32_t surf_bucket_mask = 0; bool use_wavefront = true;
+    WavefrontBuffers *wf = nullptr, *wf2 = nullptr; cudaStream_t stream2 = nullptr; cudaEvent_t fork_ev = nullptr;   // wf2/stream2: second batch in flight
+    uint64_t wf_pool_slots = 1ull << 24; uint32_t surf_bucket_mask = 0; bool use_wavefront = true;
     uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;
     DevBuf *newbuf() { pool.push_back(new DevBuf()); return pool.back(); }
     void free_scene() { for (auto *b : pool) delete b; pool.clear(); h_grids.clear(); h_media.clear(); grid_floats.clear(); grid_fixed_max.clear(); has_scene = false; }
@@ -102,7 +103,8 @@ void lr_destroy(lr_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->free_scene(); delete c->wf; c->wf = nullptr;
+    c->free_scene(); delete c->wf; c->wf = nullptr; delete c->wf2; c->wf2 = nullptr;
+    if (c->stream2) { cudaStreamDestroy(c->stream2); c->stream2 = nullptr; } if (c->fork_ev) { cudaEventDestroy(c->fork_ev); c->fork_ev = nullptr; }
     if (c->cancel_host) cudaFreeHost(c->cancel_host);
     if (c->ev0) cudaEventDestroy(c->ev0); if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);

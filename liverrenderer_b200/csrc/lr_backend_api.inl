@@ -202,7 +202,7 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
         return c->film_channels == 5 ? wavefront_prb_pass<5, true, false>(c, a, pa) : wavefront_prb_pass<4, true, false>(c, a, pa);
     }
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATH) {
-        if (int r = wf_prepare(c, (end - begin))) return r;
+        if (int r = wf_prepare(c, (end - begin), true)) return r;
         if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false>(c, a) : wavefront_render_t<4, false>(c, a);
         return c->film_channels == 5 ? wavefront_render_t<5, true>(c, a) : wavefront_render_t<4, true>(c, a);
     }

@@ -54,8 +54,9 @@ struct lr_ctx {
     lr_stats st{};
     int blocks_per_sm[8] = {0}; int n_sm = 148;
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
-    WavefrontBuffers *wf = nullptr, *wf2 = nullptr; cudaStream_t stream2 = nullptr; cudaEvent_t fork_ev = nullptr;   // wf2/stream2: second batch in flight
-    uint64_t wf_pool_slots = 1ull << 24; uint32_t surf_bucket_mask = 0; bool use_wavefront = true;
+    WavefrontBuffers *wf = nullptr, *wf_more[3] = {nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // further batches in flight
+    cudaEvent_t fork_ev = nullptr; int wf_runs = 3;
+    uint64_t wf_pool_slots = 1ull << 25; uint32_t surf_bucket_mask = 0; bool use_wavefront = true;
     uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;
     DevBuf *newbuf() { pool.push_back(new DevBuf()); return pool.back(); }
     void free_scene() { for (auto *b : pool) delete b; pool.clear(); h_grids.clear(); h_media.clear(); grid_floats.clear(); grid_fixed_max.clear(); has_scene = false; }
@@ -85,6 +86,7 @@ int lr_create(int device, lr_ctx **out) {
         LR_FAIL((lr_ctx *) nullptr, LR_ERR_NO_DEVICE, "lr_create: no CUDA device available (%s); this backend has no CPU path", cudaGetErrorString(e));
     if (device < 0 || device >= n) LR_FAIL((lr_ctx *) nullptr, LR_ERR_INVALID_ARG, "lr_create: device %d out of range (0..%d)", device, n - 1);
     lr_ctx *c = new lr_ctx(); c->device = device;
+    if (const char *e = getenv("LR_WF_RUNS")) { int v = atoi(e); if (v >= 1 && v <= 4) c->wf_runs = v; }
     if (const char *e = getenv("LR_WF_SLOTS")) { long long v = atoll(e); if (v >= 1024) c->wf_pool_slots = (uint64_t) v; }
     if (const char *e = getenv("LR_MEGAKERNEL")) c->use_wavefront = atoi(e) == 0;
     LR_CUDA(c, cudaSetDevice(device));
@@ -103,8 +105,9 @@ void lr_destroy(lr_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->free_scene(); delete c->wf; c->wf = nullptr; delete c->wf2; c->wf2 = nullptr;
-    if (c->stream2) { cudaStreamDestroy(c->stream2); c->stream2 = nullptr; } if (c->fork_ev) { cudaEventDestroy(c->fork_ev); c->fork_ev = nullptr; }
+    c->free_scene(); delete c->wf; c->wf = nullptr;
+    for (int k = 0; k < 3; ++k) { delete c->wf_more[k]; c->wf_more[k] = nullptr; if (c->stream_more[k]) { cudaStreamDestroy(c->stream_more[k]); c->stream_more[k] = nullptr; } }
+    if (c->fork_ev) { cudaEventDestroy(c->fork_ev); c->fork_ev = nullptr; }
     if (c->cancel_host) cudaFreeHost(c->cancel_host);
     if (c->ev0) cudaEventDestroy(c->ev0); if (c->ev1) cudaEventDestroy(c->ev1);
     if (c->own_stream && c->stream) cudaStreamDestroy(c->stream);

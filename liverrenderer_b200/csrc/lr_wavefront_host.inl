@@ -29,8 +29,11 @@ static int wf_prepare(lr_ctx *c, uint64_t n_lanes, bool two_runs = false) {
     want = std::max<uint64_t>(want, 1024);
     if (int r = wf_alloc(c, c->wf, want)) return r;
     if (two_runs && n_lanes > c->wf->cap) {
-        if (int r = wf_alloc(c, c->wf2, c->wf->cap)) return r;
-        if (!c->stream2) LR_CUDA(c, cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+        uint64_t batches = (n_lanes + c->wf->cap - 1) / c->wf->cap;
+        for (int k = 0; k + 1 < c->wf_runs && (uint64_t) (k + 1) < batches; ++k) {
+            if (int r = wf_alloc(c, c->wf_more[k], c->wf->cap)) return r;
+            if (!c->stream_more[k]) LR_CUDA(c, cudaStreamCreateWithFlags(&c->stream_more[k], cudaStreamNonBlocking));
+        }
         if (!c->fork_ev) LR_CUDA(c, cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
     }
     return LR_OK;
@@ -53,14 +56,21 @@ struct WfRun {
 // The lane range is cut into batches of one pool each.  A batch runs in lock step -- every lane of it starts in the same GEN
 // launch, so iteration k holds the k-th vertex of paths whose queue order is still lane (= pixel) order: warps stay spatially
 // coherent, which is worth 15-20 % over a steady-state pool that keeps refilling freed slots with unrelated lanes.  The price
-// is the thin tail of a batch; two batches are kept in flight on two streams so that the tail iterations (and the tail of
+// is the thin tail of a batch; two (LR_WF_RUNS, up to four) batches are kept in flight on separate streams so that the tail iterations (and the tail of
 // every single launch) are filled by the other batch.  Lanes are independent, so results do not depend on the batching.
 template <int C, bool TO_FILM>
 static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
     const uint64_t cap = c->wf->cap, n_lanes = ra.lane_end - ra.lane_begin;
-    const int n_runs = (n_lanes > cap && c->wf2) ? 2 : 1;
-    WfRun runs[2]; runs[0].w = c->wf; runs[0].s = c->stream; runs[1].w = c->wf2; runs[1].s = c->stream2;
-    if (n_runs == 2) { LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream)); LR_CUDA(c, cudaStreamWaitEvent(c->stream2, c->fork_ev, 0)); }
+    WfRun runs[4]; runs[0].w = c->wf; runs[0].s = c->stream; int n_runs = 1;
+    if (n_lanes > cap) {
+        const uint64_t batches = (n_lanes + cap - 1) / cap;
+        for (int k = 0; k < 3 && n_runs < c->wf_runs && (uint64_t) n_runs < batches && c->wf_more[k] && c->wf_more[k]->cap >= cap; ++k) {
+            runs[n_runs].w = c->wf_more[k]; runs[n_runs].s = c->stream_more[k]; ++n_runs; }
+    }
+    if (n_runs > 1) {                                                  // the extra streams start after whatever is queued on the caller's stream
+        LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream));
+        for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0));
+    }
     const uint32_t surf_mask = 1u | c->surf_bucket_mask;             // surface buckets present in this scene (bucket 0 also takes escaped rays)
     const int grid = c->n_sm * 8, grid128 = c->n_sm * 8;
     uint64_t launches = 0, next = ra.lane_begin;
@@ -112,7 +122,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
         }
     }
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (n_runs == 2) LR_CUDA(c, cudaStreamSynchronize(c->stream2));
+    for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamSynchronize(runs[k].s));
     double ms_track = 0, ms_nee = 0; uint64_t n_track = 0, n_nee = 0;
     for (int k = 0; k < n_runs; ++k)
         for (size_t i = 0; i < runs[k].kev_kind.size(); ++i) {

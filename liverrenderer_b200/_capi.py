@@ -105,7 +105,7 @@ API_SYMBOLS = [
 ]
 
 _LIB = None
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "liblr_b200.so")
+LIB_PATH = os.environ.get("LR_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc", "liblr_b200.so")   # LR_B200_LIB: A/B builds of the same backend
 
 
 def load_library(path: str | None = None):

@@ -56,7 +56,7 @@ struct lr_ctx {
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
     WavefrontBuffers *wf = nullptr, *wf_more[3] = {nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // further batches in flight
     cudaEvent_t fork_ev = nullptr; int wf_runs = 3;
-    uint64_t wf_pool_slots = 1ull << 25; uint32_t surf_bucket_mask = 0; bool use_wavefront = true;
+    uint64_t wf_pool_slots = 1ull << 25; uint32_t surf_bucket_mask = 0; bool use_wavefront = true, all_media_dda = false;
     uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;
     DevBuf *newbuf() { pool.push_back(new DevBuf()); return pool.back(); }
     void free_scene() { for (auto *b : pool) delete b; pool.clear(); h_grids.clear(); h_media.clear(); grid_floats.clear(); grid_fixed_max.clear(); has_scene = false; }

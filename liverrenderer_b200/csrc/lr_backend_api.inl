@@ -121,6 +121,8 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     LR_CUDA(c, c->weight_img.alloc((size_t) c->W * c->H * 4));
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
     c->surf_bucket_mask = surf_mask;
+    c->all_media_dda = s->integrator.tracking == LR_TRACKING_DDA && getenv("LR_TRACK_REFILL_OFF") == nullptr;   // persistent TRACK (k_wf_track_dda)
+    for (uint32_t i = 0; i < s->n_media; ++i) if (s->media[i].kind != LR_MEDIUM_HETEROGENEOUS) c->all_media_dda = false;
     c->has_scene = true; memset(&c->st, 0, sizeof c->st);
     return LR_OK;
 }

@@ -105,40 +105,35 @@ LR_DEV Hit bvh_trace(const DScene &sc, const Ray &ray) {
         return false;
     };
     if (sc.n_tris == 1) { leaf(0); return h; }
-    // "while-while" traversal: a lane first descends inner nodes until it holds a leaf reference (negative link), then the warp
-    // reconverges and the lanes run their Moeller-Trumbore tests together.  With one triangle per leaf the inline form ran the
-    // leaf test with 2-3 of 32 lanes active (ncu source view); leaves of the far side are deferred on the stack like nodes.
-    const int DONE = 0x7fffffff;
     int stack[48]; int sp = 0; int node = 0;
-    while (node != DONE) {
-        while (node >= 0 && node != DONE) {
-            const DNode n = sc.nodes[node];
-            // slab test of both children; bounds are padded at build time, far side scaled by 1+4ulp
-            float lo0x = (n.a.x - ray.o.x) * inv.x, hi0x = (n.a.w - ray.o.x) * inv.x;
-            float lo0y = (n.a.y - ray.o.y) * inv.y, hi0y = (n.b.x - ray.o.y) * inv.y;
-            float lo0z = (n.a.z - ray.o.z) * inv.z, hi0z = (n.b.y - ray.o.z) * inv.z;
-            float lo1x = (n.b.z - ray.o.x) * inv.x, hi1x = (n.c.y - ray.o.x) * inv.x;
-            float lo1y = (n.b.w - ray.o.y) * inv.y, hi1y = (n.c.z - ray.o.y) * inv.y;
-            float lo1z = (n.c.x - ray.o.z) * inv.z, hi1z = (n.c.w - ray.o.z) * inv.z;
-            // fminf/fmaxf drop NaNs (0 * inf on a slab boundary) like the usual robust formulation
-            float n0 = fmaxf(fmaxf(fminf(lo0x, hi0x), fminf(lo0y, hi0y)), fmaxf(fminf(lo0z, hi0z), 0.f));
-            float f0 = fminf(fminf(fmaxf(lo0x, hi0x), fmaxf(lo0y, hi0y)), fminf(fmaxf(lo0z, hi0z), tmax)) * 1.0000005f;
-            float n1 = fmaxf(fmaxf(fminf(lo1x, hi1x), fminf(lo1y, hi1y)), fmaxf(fminf(lo1z, hi1z), 0.f));
-            float f1 = fminf(fminf(fmaxf(lo1x, hi1x), fmaxf(lo1y, hi1y)), fminf(fmaxf(lo1z, hi1z), tmax)) * 1.0000005f;
-            bool h0 = n0 <= f0, h1 = n1 <= f1;
-            int c0 = __float_as_int(n.d.x), c1 = __float_as_int(n.d.y);
-            if (h0 && h1) {
-                bool swap = n1 < n0;
-                int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;
-                if (sp < 48) stack[sp++] = farc;
-                node = nearc;
-            } else if (h0) node = c0;
-            else if (h1) node = c1;
-            else node = sp ? stack[--sp] : DONE;
-        }
-        if (node < 0) {
-            if (leaf((uint32_t) ~node) && ANY_HIT) return h;
-            node = sp ? stack[--sp] : DONE;
+    while (true) {
+        const DNode n = sc.nodes[node];
+        // slab test of both children; bounds are padded at build time, far side scaled by 1+4ulp
+        float lo0x = (n.a.x - ray.o.x) * inv.x, hi0x = (n.a.w - ray.o.x) * inv.x;
+        float lo0y = (n.a.y - ray.o.y) * inv.y, hi0y = (n.b.x - ray.o.y) * inv.y;
+        float lo0z = (n.a.z - ray.o.z) * inv.z, hi0z = (n.b.y - ray.o.z) * inv.z;
+        float lo1x = (n.b.z - ray.o.x) * inv.x, hi1x = (n.c.y - ray.o.x) * inv.x;
+        float lo1y = (n.b.w - ray.o.y) * inv.y, hi1y = (n.c.z - ray.o.y) * inv.y;
+        float lo1z = (n.c.x - ray.o.z) * inv.z, hi1z = (n.c.w - ray.o.z) * inv.z;
+        // fminf/fmaxf drop NaNs (0 * inf on a slab boundary) like the usual robust formulation
+        float n0 = fmaxf(fmaxf(fminf(lo0x, hi0x), fminf(lo0y, hi0y)), fmaxf(fminf(lo0z, hi0z), 0.f));
+        float f0 = fminf(fminf(fmaxf(lo0x, hi0x), fmaxf(lo0y, hi0y)), fminf(fmaxf(lo0z, hi0z), tmax)) * 1.0000005f;
+        float n1 = fmaxf(fmaxf(fminf(lo1x, hi1x), fminf(lo1y, hi1y)), fmaxf(fminf(lo1z, hi1z), 0.f));
+        float f1 = fminf(fminf(fmaxf(lo1x, hi1x), fmaxf(lo1y, hi1y)), fminf(fmaxf(lo1z, hi1z), tmax)) * 1.0000005f;
+        bool h0 = n0 <= f0, h1 = n1 <= f1;
+        int c0 = __float_as_int(n.d.x), c1 = __float_as_int(n.d.y);
+        if (h0 && c0 < 0) { if (leaf((uint32_t) ~c0) && ANY_HIT) return h; h0 = false; }
+        if (h1 && c1 < 0) { if (leaf((uint32_t) ~c1) && ANY_HIT) return h; h1 = false; }
+        if (h0 && h1) {
+            bool swap = n1 < n0;
+            int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;
+            if (sp < 48) stack[sp++] = farc;
+            node = nearc;
+        } else if (h0) node = c0;
+        else if (h1) node = c1;
+        else {
+            if (sp == 0) break;
+            node = stack[--sp];
         }
     }
     return h;

@@ -54,7 +54,7 @@ static_assert(sizeof(WState) == 256, "WState layout");
 
 struct WQueues {                       // device-side counters, one 64-byte block
     uint32_t n_active[2]; uint32_t n_scatter; uint32_t n_surf[WF_N_SURF]; uint32_t n_regen; uint32_t live;
-    unsigned long long lane_next; uint32_t n_nee; uint32_t pad[5];
+    unsigned long long lane_next; uint32_t n_nee; uint32_t cursor; uint32_t pad[4];   // cursor: work cursor of k_wf_track_dda
 };
 
 struct WFArgs {
@@ -253,6 +253,116 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track(const __grid_consta
         wf_push(a.q_scatter, &a.q->n_scatter, slot, event == 1);
 #pragma unroll
         for (int b = 0; b < WF_N_SURF; ++b) wf_push(a.q_surf[b], &a.q->n_surf[b], slot, event == 2 + b);
+    }
+    flush_counters(cnt, 0, a.stats);
+}
+
+// TRACK for scenes whose media all use the majorant-DDA (production mode): the same per-item work as k_wf_track, run as a
+// persistent "while-while" loop.  The number of super-voxels a free flight crosses is roughly exponentially distributed, so a
+// warp that waits for its longest walk keeps 4-5 of 32 lanes busy (ncu source view of k_wf_track: lr_medium.cuh:101-118 at 4.5
+// threads per instruction).  Here a lane that has finished its item writes it out and, once half of the warp is idle, the idle
+// lanes pull the next queue entries (one atomicAdd on q->cursor per refill), so the walk loop stays populated.  Per-lane RNG
+// draw order is unchanged: RR, first optical depth, then (null test, next optical depth) per tentative collision.
+#ifndef LR_TRACK_REFILL
+#define LR_TRACK_REFILL 16            // refill when at most this many lanes of the warp are still walking
+#endif
+#ifndef LR_TRACK_STEPS
+#define LR_TRACK_STEPS 6              // super-voxel steps per lane between two converged points
+#endif
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+    const uint32_t *q_in = a.q_active[a.cur]; const uint32_t n_items = a.q->n_active[a.cur];
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    uint32_t slot = 0, depth = 0, f = 0; int event = -2;                  // -2 idle, -1 walking, 0 end of path, 1 scatter, 2 surface
+    Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f; V3 thr = mk3(0.f);
+    float hit_t = 0.f, t = 0.f, tau = 0.f, t_end = 0.f, mu_scale = 0.f; int grid_id = 0; DDA dd{};
+    bool exhausted = false;
+    for (;;) {
+        const unsigned walking = __ballot_sync(0xffffffffu, event == -1);
+        if (!exhausted && __popc(walking) <= LR_TRACK_REFILL) {
+            const unsigned idle = ~walking; uint32_t base = 0;
+            if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor, (uint32_t) __popc(idle));
+            base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+            exhausted = base + (uint32_t) __popc(idle) >= n_items;
+            const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+            if (event == -2 && qi < n_items) {
+                slot = q_in[qi]; const WState *S = a.st + slot;
+                smp.state = S->rng_state; smp.inc = S->rng_inc;
+                float4 t4 = S->o_maxt; ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+                t4 = S->d_eta; ray.d = mk3(t4.x, t4.y, t4.z); const float eta = t4.w;
+                t4 = S->thr_lpdf; thr = mk3(t4.x, t4.y, t4.z);
+                hit_t = S->hit.x; f = __float_as_uint(S->lsp_flags.w); depth = __float_as_uint(S->res_depth.w);
+                const int medium = wf_medium(f);
+                // volpath.cpp:160-178: russian roulette, depth test
+                bool active = any_nonzero(thr);
+                float q = fminf(hmax(thr) * sqr(eta), .95f);
+                bool perform_rr = depth > (uint32_t) sc.rr_depth;
+                if (active) { float u = smp.next_1d(); active &= (u < q) || !perform_rr; }
+                if (perform_rr) thr *= 1.f / q;
+                active &= depth < sc.max_depth;
+                event = active ? 2 : 0;
+                if (active && medium >= 0) {
+                    const DMedium &m = sc.media[medium]; grid_id = m.m.sigma_t_grid; mu_scale = m.m.scale; const DGrid &g = sc.grids[grid_id];
+                    float mint, maxt;
+                    if (medium_clip(g, ray, mint, maxt)) {
+                        t_end = fminf(maxt, hit_t);
+                        if (mint < t_end) { dda_init(g, ray, mint, dd); t = mint; tau = -logf(1.f - smp.next_1d()); event = -1; }
+                    }
+                }
+            }
+        }
+        // ---- walk: bring every walking lane to its next tentative collision (or the end of its segment) ----
+        bool collide = false; float mu = 0.f;
+        if (event == -1) {
+            const DGrid &g = sc.grids[grid_id];
+#pragma unroll 1
+            for (int k = 0; k < LR_TRACK_STEPS; ++k) {
+                mu = mu_scale * dda_majorant(g, dd);
+                const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
+                const float dtau = mu * (t_exit - t);
+                if (dtau >= tau && mu > 0.f) { t = fminf(t + tau / mu, t_exit); collide = true; break; }
+                tau -= dtau; t = t_exit;
+                if (t_exit >= t_end) { event = 2; break; }
+                dda_advance(g, dd);
+            }
+        }
+        // ---- tentative collisions, evaluated together ----
+        if (collide) {
+            const DGrid &g = sc.grids[grid_id]; const DMedium &m = sc.media[wf_medium(f)];
+            cnt.collisions++;
+            V3 p = ray_at(ray, t);
+            V3 st = grid_eval<false>(g, p, nullptr) * mu_scale, sn = mk3(mu) - st;
+            float pn = hmean(sn / mu);
+            if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); }
+            else {
+                depth += 1; cnt.real_scatters++;
+                WState *S = a.st + slot; S->lsp_flags.x = p.x; S->lsp_flags.y = p.y; S->lsp_flags.z = p.z;
+                if (!(depth < sc.max_depth)) event = 0;
+                else { thr *= (st * medium_albedo(sc, m, p)) / (mu * hmean(st / mu)); ray.o = p; hit_t = hit_t - t; event = 1; }
+            }
+        }
+        // ---- write finished items out and queue them (converged: wf_push uses warp ballots) ----
+        const bool fin = event >= 0;
+        if (__any_sync(0xffffffffu, fin)) {
+            WState *S = a.st + slot;
+            if (fin) {
+                S->rng_state = smp.state; S->rng_inc = smp.inc;            // a later pass of this lane continues the stream
+                if (event == 0) { float4 r4 = S->res_depth; wf_finish<C, TO_FILM>(sc, a, *S, mk3(r4.x, r4.y, r4.z), f); }
+                else {
+                    if (event == 2) event = 2 + wf_surf_bucket(sc, a.tris_gid, wf_hit(S->hit));
+                    S->o_maxt = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+                    S->thr_lpdf.x = thr.x; S->thr_lpdf.y = thr.y; S->thr_lpdf.z = thr.z;
+                    S->hit.x = hit_t; S->res_depth.w = __uint_as_float(depth);
+                }
+            }
+            wf_push(a.q_regen, &a.q->n_regen, slot, event == 0);
+            wf_push(a.q_scatter, &a.q->n_scatter, slot, event == 1);
+#pragma unroll
+            for (int b = 0; b < WF_N_SURF; ++b) wf_push(a.q_surf[b], &a.q->n_surf[b], slot, event == 2 + b);
+            if (fin) event = -2;
+        }
+        if (exhausted && !__any_sync(0xffffffffu, event == -1)) break;
     }
     flush_counters(cnt, 0, a.stats);
 }
@@ -529,12 +639,12 @@ __global__ void __launch_bounds__(128, 2 * LR_WF_OCC) k_wf_shade_b_surface(const
 }
 
 __global__ void k_wf_begin_iteration(WQueues *q, int cur) {     // counters of the queues this iteration fills
-    q->n_active[cur ^ 1] = 0; q->n_scatter = 0; q->n_regen = 0; q->n_nee = 0;
+    q->n_active[cur ^ 1] = 0; q->n_scatter = 0; q->n_regen = 0; q->n_nee = 0; q->cursor = 0;
     for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
 }
 __global__ void k_wf_init(WQueues *q, uint32_t *q_regen, uint32_t cap, WState *st) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) { q->n_active[0] = q->n_active[1] = 0; q->n_scatter = 0; q->n_regen = cap; q->lane_next = 0; q->n_nee = 0; for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0; }
+    if (i == 0) { q->n_active[0] = q->n_active[1] = 0; q->n_scatter = 0; q->n_regen = cap; q->lane_next = 0; q->n_nee = 0; q->cursor = 0; for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0; }
     if (i < cap) { q_regen[i] = i; st[i].lsp_flags.w = __uint_as_float(0u); }
 }
 

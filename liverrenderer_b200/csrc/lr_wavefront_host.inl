@@ -98,7 +98,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
             if (w.live_host[slot] == 0 || *c->cancel_host) { r.busy = false; return 1; }
         }
         k_wf_begin_iteration<<<1, 1, 0, s>>>(a.q, a.cur);
-        { cudaEvent_t *e = timed(r, 0); cudaEventRecord(e[0], s); k_wf_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); cudaEventRecord(e[1], s); }
+        { cudaEvent_t *e = timed(r, 0); cudaEventRecord(e[0], s); if (c->all_media_dda) k_wf_track_dda<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wf_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); cudaEventRecord(e[1], s); }
         k_wf_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); launches += 3;
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) { k_wf_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); ++launches; }
         { cudaEvent_t *e = timed(r, 1); cudaEventRecord(e[0], s); k_wf_nee<<<grid, 256, 0, s>>>(c->sc, a, surf_mask); cudaEventRecord(e[1], s); }

@@ -24,4 +24,4 @@ for r in range(rep):
         img = ctx.render(seed=r, spp=spp)
     st = ctx.stats(); dt = st["device_ms"]
     print(f"{w} res {res} spp {spp} {tracking}: {dt:.2f} ms  {st['samples'] / dt / 1e3:.2f} Msamples/s  {st['collisions'] / dt / 1e3:.1f} Mcoll/s "
-          f"{st['rays'] / dt / 1e3:.1f} Mrays/s  coll/sample {st['collisions'] / max(st['samples'], 1):.2f}  mean {float(img[..., :3].mean()):.5f}", flush=True)
+          f"{st['rays'] / dt / 1e3:.1f} Mrays/s  coll/sample {st['collisions'] / max(st['samples'], 1):.2f}  track+nee {st['tracking_ms']:.1f} ms/{st['tracking_launches']}  mean {float(img[..., :3].mean()):.5f}", flush=True)

@@ -55,7 +55,7 @@ struct lr_ctx {
     int blocks_per_sm[8] = {0}; int n_sm = 148;
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
     WavefrontBuffers *wf = nullptr, *wf_more[3] = {nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // further batches in flight
-    cudaEvent_t fork_ev = nullptr; int wf_runs = 3;
+    cudaEvent_t fork_ev = nullptr; int wf_runs = 3, wf_grid_mult = 8, wf_grid_mult128 = 8;
     uint64_t wf_pool_slots = 1ull << 25; uint32_t surf_bucket_mask = 0; bool use_wavefront = true, all_media_dda = false;
     uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;
     DevBuf *newbuf() { pool.push_back(new DevBuf()); return pool.back(); }
@@ -87,6 +87,8 @@ int lr_create(int device, lr_ctx **out) {
     if (device < 0 || device >= n) LR_FAIL((lr_ctx *) nullptr, LR_ERR_INVALID_ARG, "lr_create: device %d out of range (0..%d)", device, n - 1);
     lr_ctx *c = new lr_ctx(); c->device = device;
     if (const char *e = getenv("LR_WF_RUNS")) { int v = atoi(e); if (v >= 1 && v <= 4) c->wf_runs = v; }
+    if (const char *e = getenv("LR_WF_GRID")) { int v = atoi(e); if (v >= 1 && v <= 64) c->wf_grid_mult = v; }
+    if (const char *e = getenv("LR_WF_GRID128")) { int v = atoi(e); if (v >= 1 && v <= 64) c->wf_grid_mult128 = v; }
     if (const char *e = getenv("LR_WF_SLOTS")) { long long v = atoll(e); if (v >= 1024) c->wf_pool_slots = (uint64_t) v; }
     if (const char *e = getenv("LR_MEGAKERNEL")) c->use_wavefront = atoi(e) == 0;
     LR_CUDA(c, cudaSetDevice(device));

@@ -72,7 +72,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
         for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0));
     }
     const uint32_t surf_mask = 1u | c->surf_bucket_mask;             // surface buckets present in this scene (bucket 0 also takes escaped rays)
-    const int grid = c->n_sm * 8, grid128 = c->n_sm * 8;
+    const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128;   // blocks per SM handed to the grid-stride stage kernels (LR_WF_GRID / LR_WF_GRID128)
     uint64_t launches = 0, next = ra.lane_begin;
     auto timed = [&](WfRun &r, int kind) -> cudaEvent_t * {           // {start, stop} events for a TRACK (0) / NEE (1) launch
         auto &kev = r.w->kev;

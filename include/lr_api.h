@@ -73,6 +73,12 @@ typedef enum lr_phase_kind {
     LR_PHASE_HG        = 1        /* src/phase/hg.cpp:64-99                    */
 } lr_phase_kind;
 
+typedef enum lr_sampler_kind {
+    LR_SAMPLER_INDEPENDENT = 0,   /* src/samplers/independent.cpp (PCG32, src/render/sampler.cpp:129-148) */
+    LR_SAMPLER_LD          = 1    /* src/samplers/ldsampler.cpp:107-141: (0,2)-sequence, per-pixel scramble + per-dimension
+                                     permutation; spp must be a square power of two (set_sample_count, :80-89) */
+} lr_sampler_kind;
+
 typedef enum lr_medium_kind {
     LR_MEDIUM_HOMOGENEOUS   = 0,  /* src/media/homogeneous.cpp:137-181         */
     LR_MEDIUM_HETEROGENEOUS = 1   /* src/media/heterogeneous.cpp:155-201       */
@@ -208,7 +214,7 @@ typedef struct lr_integrator {
     uint32_t tracking;              /* lr_tracking_mode                         */
     uint32_t base_seed;             /* independent sampler `seed`               */
     uint32_t majorant_cell;         /* DDA super-voxel edge in voxels (0 => default 8) */
-    uint32_t reserved;
+    uint32_t sampler;               /* lr_sampler_kind: the sensor's sampler plugin */
 } lr_integrator;
 
 typedef struct lr_scene {

@@ -19,6 +19,7 @@ LR_ERR = {-1: "invalid argument", -2: "no CUDA device (this backend has no CPU p
 
 INTEGRATOR_PATH, INTEGRATOR_VOLPATH, INTEGRATOR_PRBVOLPATH = 0, 1, 2
 TRACKING_REFERENCE, TRACKING_DDA = 0, 1
+SAMPLER_INDEPENDENT, SAMPLER_LD = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHDIELECTRIC, BSDF_PRINCIPLED, BSDF_NULL, BSDF_DIELECTRIC = 0, 1, 2, 3, 4
 MF_BECKMANN, MF_GGX = 0, 1
 PHASE_ISOTROPIC, PHASE_HG = 0, 1
@@ -79,7 +80,7 @@ class lr_sensor(C.Structure):
 
 class lr_integrator(C.Structure):
     _fields_ = [("kind", C.c_uint32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("hide_emitters", C.c_uint32),
-                ("tracking", C.c_uint32), ("base_seed", C.c_uint32), ("majorant_cell", C.c_uint32), ("reserved", C.c_uint32)]
+                ("tracking", C.c_uint32), ("base_seed", C.c_uint32), ("majorant_cell", C.c_uint32), ("sampler", C.c_uint32)]
 
 
 class lr_scene(C.Structure):

@@ -134,6 +134,9 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
 // ---------------------------------------------------------------------------------------------
 struct PassPlan { uint32_t spp_per_pass, n_passes; uint64_t n_lanes; };
 // pass splitting when W*H*spp exceeds 2^32-1 lanes (src/render/integrator.cpp:275-293)
+// ldsampler: the sample count must be a square power of two (LowDiscrepancySampler::set_sample_count, ldsampler.cpp:80-89;
+// the host mirror rounds `sample_count` up the same way before it calls in)
+static bool ld_spp_ok(uint32_t spp) { return spp >= 4 && (spp & (spp - 1)) == 0 && (__builtin_ctz(spp) % 2) == 0; }
 static PassPlan plan_passes(const lr_ctx *c, uint32_t spp) {
     PassPlan p; p.spp_per_pass = spp; p.n_passes = 1;
     uint64_t wf = (uint64_t) c->W * c->H * spp, limit = 0xffffffffull;
@@ -189,6 +192,7 @@ static int end_call(lr_ctx *c, uint64_t launches, bool tracking) {
 
 static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t begin, uint64_t end, float *lanes_out) {
     PassPlan p = plan_passes(c, spp);
+    if (c->sc.integ.sampler == LR_SAMPLER_LD && !ld_spp_ok(spp)) LR_FAIL(c, LR_ERR_INVALID_ARG, "ldsampler: spp %u is not a square power of two", spp);
     if (end == 0 && begin == 0) end = p.n_lanes;
     if (begin > end || end > p.n_lanes) LR_FAIL(c, LR_ERR_INVALID_ARG, "lane range [%llu,%llu) outside [0,%llu)", (unsigned long long) begin, (unsigned long long) end, (unsigned long long) p.n_lanes);
     RenderArgs a{}; a.tris_gid = c->tris_gid->as<DTri>(); a.film = c->film.as<float>(); a.lanes_out = lanes_out;
@@ -282,6 +286,7 @@ int lr_render_backward(lr_ctx *c, uint32_t seed, uint32_t spp, const float *grad
     if (c->sc.integ.kind != LR_INTEGRATOR_PRBVOLPATH) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_render_backward: integrator is not prbvolpath");
     if (spp == 0 || !grad_in) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render_backward: bad arguments");
     PassPlan p = plan_passes(c, spp);
+    if (c->sc.integ.sampler == LR_SAMPLER_LD && !ld_spp_ok(spp)) LR_FAIL(c, LR_ERR_INVALID_ARG, "ldsampler: spp %u is not a square power of two", spp);
     if (p.n_passes != 1) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_render_backward: W*H*spp exceeds 2^32 (the reference raises as well, common.py:359-364)");
     if (lane_begin == 0 && lane_end == 0) lane_end = p.n_lanes;
     if (lane_begin > lane_end || lane_end > p.n_lanes) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render_backward: lane range out of bounds");

@@ -95,6 +95,11 @@ struct RenderArgs {
 
 struct LaneSetup { Sampler smp; V2 pos, sample_pos; Ray ray; };
 // lane -> (pixel, stream): integrator.cpp:321-338 + sampler.cpp:129-148; jitter + camera ray: :465-480
+// sampler->seed(seed, wavefront_size) of the render loop (integrator.cpp:303-308) for one lane
+LR_DEV void seed_sampler(const DScene &sc, Sampler &smp, uint32_t seed, uint64_t lane, uint32_t spp_per_pass, uint32_t n_passes) {
+    if (sc.integ.sampler == LR_SAMPLER_LD) smp.seed_ld(sc.integ.base_seed, seed, (uint32_t) lane, spp_per_pass, spp_per_pass * n_passes);
+    else smp.seed(sc.integ.base_seed + seed, (uint32_t) lane);
+}
 LR_DEV void lane_begin_sample(const DScene &sc, LaneSetup &L, uint64_t lane, uint32_t spp_per_pass) {
     uint32_t W = sc.sensor.film_width;
     uint32_t pix = (uint32_t) (lane / spp_per_pass), py = pix / W, px = pix - W * py;
@@ -137,9 +142,10 @@ __global__ void __launch_bounds__(128) k_render(const __grid_constant__ DScene s
         if (base == ~0ull || a.lane_begin + base >= a.lane_end) break;
         uint64_t lane = a.lane_begin + base + lane_id;
         if (lane < a.lane_end) {
-            LaneSetup L; L.smp.seed(sc.integ.base_seed + a.seed, (uint32_t) lane);
+            LaneSetup L; seed_sampler(sc, L.smp, a.seed, lane, a.spp_per_pass, a.n_passes);
             lane_begin_sample(sc, L, lane, a.spp_per_pass);
             for (uint32_t pass = 0; pass < a.n_passes; ++pass) {
+                if (pass) L.smp.advance(a.spp_per_pass);
                 lane_next_ray(sc, L);
                 LaneResult r = run_lane<KIND>(sc, a.tris_gid, L, cnt);
                 nsamples++;
@@ -187,7 +193,7 @@ __global__ void k_grid_max(const float *data, size_t n, float *out) {
 __global__ void __launch_bounds__(256) k_weight_image(const __grid_constant__ DScene sc, float *wimg, uint64_t n_lanes, uint32_t seed, uint32_t spp) {
     const bool box = sc.sensor.rfilter == LR_RFILTER_BOX, coalesce = spp >= 4;
     for (uint64_t lane = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; lane < n_lanes; lane += (uint64_t) gridDim.x * blockDim.x) {
-        LaneSetup L; L.smp.seed(sc.integ.base_seed + seed, (uint32_t) lane);
+        LaneSetup L; seed_sampler(sc, L.smp, seed, lane, spp, 1);
         lane_begin_sample(sc, L, lane, spp);
         V2 j = L.smp.next_2d(); L.sample_pos = mk2(L.pos.x + j.x, L.pos.y + j.y);
         float one = 1.f; film_put<1>(sc, wimg, box ? L.pos : L.sample_pos, &one, coalesce);
@@ -206,7 +212,7 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene
         if (base == ~0ull || a.lane_begin + base >= a.lane_end) break;
         uint64_t lane = a.lane_begin + base + lane_id;
         if (lane < a.lane_end) {
-            LaneSetup L; L.smp.seed(sc.integ.base_seed + a.seed, (uint32_t) lane);
+            LaneSetup L; seed_sampler(sc, L.smp, a.seed, lane, a.spp_per_pass, a.n_passes);
             lane_begin_sample(sc, L, lane, a.spp_per_pass);
             lane_next_ray(sc, L);
             Footprint fp; V3 dL = mk3(0.f);

@@ -114,8 +114,34 @@ LR_HD void tea32(uint32_t v0, uint32_t v1, int rounds, uint32_t &o0, uint32_t &o
 }
 // dr::PCG32 (ext/drjit/include/drjit/random.h:135-160, 287-289) seeded as
 // PCG32Sampler::seed does in the JIT variants (src/render/sampler.cpp:129-148)
+// permute() (include/mitsuba/core/random.h:196-213): bit-flip permutation of [0, size), size a power of two
+LR_HD uint32_t permute_pow2(uint32_t index, uint32_t size, uint32_t seed) {
+    for (uint32_t bit = 1; bit < size; bit <<= 1) {
+        uint32_t r0, r1; tea32(index | bit, seed, 2, r0, r1);
+        if ((r0 & bit) == bit) index ^= bit;
+    }
+    return index;
+}
+// radical_inverse_2 / sobol_2, single precision (include/mitsuba/core/qmc.h:190-212, 218-251)
+LR_HD uint32_t reverse_bits32(uint32_t index) {
+    index = (index << 16) | (index >> 16);
+    index = ((index & 0x00ff00ffu) << 8) | ((index & 0xff00ff00u) >> 8);
+    index = ((index & 0x0f0f0f0fu) << 4) | ((index & 0xf0f0f0f0u) >> 4);
+    index = ((index & 0x33333333u) << 2) | ((index & 0xccccccccu) >> 2);
+    index = ((index & 0x55555555u) << 1) | ((index & 0xaaaaaaaau) >> 1);
+    return index;
+}
+LR_HD uint32_t sobol_2_bits(uint32_t index, uint32_t scramble) {
+    for (uint32_t v = 1u << 31; index != 0u; index >>= 1, v ^= v >> 1) if (index & 1u) scramble ^= v;
+    return scramble;
+}
+
 struct Sampler {
+    // independent: PCG32 (state, inc) -- inc is always odd.
+    // ldsampler (src/samplers/ldsampler.cpp:107-141), marked by an even inc:
+    //   state = scramble_seed | dimension_index << 32,   inc = sample_count << 1 | sample_index << 32
     uint64_t state, inc;
+    LR_DEV bool is_ld() const { return (inc & 1ull) == 0ull; }
     LR_DEV uint32_t next_u32() {
         uint64_t old = state;
         state = old * 0x5851f42d4c957f2dULL + inc;
@@ -128,8 +154,34 @@ struct Sampler {
         state = 0; inc = ((uint64_t) v1 << 1) | 1u;
         next_u32(); state += (uint64_t) v0; next_u32();
     }
-    LR_DEV float next_1d() { return __uint_as_float((next_u32() >> 9) | 0x3f800000u) - 1.f; }
-    LR_DEV V2 next_2d() { float a = next_1d(); float b = next_1d(); return mk2(a, b); }
+    // Sampler::seed + compute_per_sequence_seed + current_sample_index (src/render/sampler.cpp:54-68, 101-121) for wavefront lane
+    // `lane` with samples_per_wavefront = spp_per_pass: one sequence per pixel, sample index = lane % spp_per_pass
+    LR_DEV void seed_ld(uint32_t base_seed, uint32_t seed, uint32_t lane, uint32_t spp_per_pass, uint32_t sample_count) {
+        uint32_t v0, v1; tea32(base_seed, (lane / spp_per_pass) * spp_per_pass + seed, 4, v0, v1);
+        state = (uint64_t) v0; inc = ((uint64_t) (lane % spp_per_pass) << 32) | ((uint64_t) sample_count << 1);
+    }
+    // Sampler::advance (sampler.cpp:70-73) between the passes of a multi-pass render: PCG32 streams simply continue
+    LR_DEV void advance(uint32_t spp_per_pass) { if (is_ld()) { state &= 0xffffffffull; inc += (uint64_t) spp_per_pass << 32; } }
+    LR_DEV uint32_t ld_index() {                     // shuffled sample index of the current dimension; bumps the dimension
+        uint32_t scr = (uint32_t) state, dim = (uint32_t) (state >> 32); state += 1ull << 32;
+        return permute_pow2((uint32_t) (inc >> 32), ((uint32_t) inc) >> 1, scr + dim);
+    }
+    LR_DEV float next_1d() {
+        if (is_ld()) {
+            uint32_t i = ld_index(), s0, s1; tea32((uint32_t) state, 0x48bc48ebu, 4, s0, s1);
+            return __uint_as_float(((reverse_bits32(i) ^ s0) >> 9) | 0x3f800000u) - 1.f;
+        }
+        return __uint_as_float((next_u32() >> 9) | 0x3f800000u) - 1.f;
+    }
+    LR_DEV V2 next_2d() {
+        if (is_ld()) {
+            uint32_t i = ld_index(), sx, sy; tea32((uint32_t) state, 0x98bc51abu, 4, sx, sy);
+            float x = __uint_as_float(((reverse_bits32(i) ^ sx) >> 9) | 0x3f800000u) - 1.f;
+            float y = __uint2float_rn(sobol_2_bits(i, sy)) / 4294967296.f;
+            return mk2(x, y);
+        }
+        float a = next_1d(); float b = next_1d(); return mk2(a, b);
+    }
 };
 
 // ---- warps (include/mitsuba/core/warp.h) ---------------------------------------------

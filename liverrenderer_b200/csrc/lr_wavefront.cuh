@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_gen(const __grid_constant
             uint32_t f = wf_flags(*S);
             if ((f & WF_HAS_LANE) && (f >> WF_PASS_SHIFT) + 1 < a.n_passes) {          // same lane, next pass: the stream continues
                 need_lane = false; live = true; pass = (f >> WF_PASS_SHIFT) + 1;
-                smp.state = S->rng_state; smp.inc = S->rng_inc;
+                smp.state = S->rng_state; smp.inc = S->rng_inc; smp.advance(a.spp_per_pass);
                 lane = ((uint64_t) __float_as_uint(S->lane_pos.y) << 32) | __float_as_uint(S->lane_pos.x);
             }
         }
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_gen(const __grid_constant
                 base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
                 if (need_lane) {
                     lane = a.lane_begin + base + __popc(m & ((1u << l) - 1u));
-                    if (lane < a.lane_end) { live = true; smp.seed(sc.integ.base_seed + a.seed, (uint32_t) lane); }
+                    if (lane < a.lane_end) { live = true; seed_sampler(sc, smp, a.seed, lane, a.spp_per_pass, a.n_passes); }
                 }
             }
         }

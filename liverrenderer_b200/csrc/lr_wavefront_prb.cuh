@@ -46,7 +46,7 @@ __global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_gen(const __grid_consta
         }
         if (item && !live) S->lsp_flags.w = __uint_as_float(WF_DEAD);
         if (live) {
-            LaneSetup L; L.smp.seed(sc.integ.base_seed + a.seed, (uint32_t) lane);
+            LaneSetup L; seed_sampler(sc, L.smp, a.seed, lane, a.spp_per_pass, 1);
             lane_begin_sample(sc, L, lane, a.spp_per_pass); lane_next_ray(sc, L);
             V2 fp2 = box ? L.pos : L.sample_pos;
             uint32_t channel = (uint32_t) fminf(3.f * L.smp.next_1d(), 2.f);                 // prbvolpath.py:136-139

@@ -70,6 +70,16 @@ def _ior(v, default):
     return float(v)
 
 
+def ld_sample_count(spp: int) -> int:
+    """LowDiscrepancySampler::set_sample_count (src/samplers/ldsampler.cpp:80-89): the sample count is rounded up to a
+    square power of two (4, 16, 64, 256, 1024, ...)."""
+    res = 2
+    while res * res < spp:
+        res += 1
+        res = 1 << (res - 1).bit_length()          # math::round_to_power_of_two
+    return res * res
+
+
 class Scene:
     """Flattened scene + the context handle of the backend it was uploaded to."""
 
@@ -351,9 +361,13 @@ class Scene:
         s.has_alpha = 1 if pf == "rgba" else 0
         s.medium = self._resolve_medium(v.get("medium"), "sensor.medium")
         smp = v.get("sampler", {"type": "independent"})
-        if smp.get("type", "independent") != "independent":
-            raise NotImplementedError("only the 'independent' sampler is on the hot path")
+        st = smp.get("type", "independent")
+        if st not in ("independent", "ldsampler"):
+            raise NotImplementedError("only the 'independent' and 'ldsampler' samplers are on the hot path")
+        self.sampler_kind = K.SAMPLER_LD if st == "ldsampler" else K.SAMPLER_INDEPENDENT
         self.spp = int(smp.get("sample_count", 4)); self.base_seed = int(smp.get("seed", 0))
+        if self.sampler_kind == K.SAMPLER_LD:
+            self.spp = ld_sample_count(self.spp)
         self.sensor = s
 
     def _build_integrator(self, v):
@@ -367,7 +381,7 @@ class Scene:
             raise RuntimeError('"rr_depth" must be set to a value greater than zero!')
         i.hide_emitters = 1 if v.get("hide_emitters", False) else 0
         i.tracking = {"reference": K.TRACKING_REFERENCE, "dda": K.TRACKING_DDA}[str(v.get("tracking", "reference")).lower()]
-        i.base_seed = self.base_seed; i.majorant_cell = int(v.get("majorant_cell", 0))
+        i.base_seed = self.base_seed; i.majorant_cell = int(v.get("majorant_cell", 0)); i.sampler = getattr(self, "sampler_kind", K.SAMPLER_INDEPENDENT)
         self.integrator = i; self.integrator_name = v["type"]
 
     # ---- POD ---------------------------------------------------------------------

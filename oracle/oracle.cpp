@@ -86,7 +86,8 @@ static void build_scene(OrcScene &o, const lr_scene *s) {
 struct LaneSetup { Sampler smp; V2 pos, sample_pos; Ray ray; };
 static LaneSetup lane_setup(const Scene &sc, uint32_t seed, uint32_t spp, uint64_t lane) {
     LaneSetup L; uint32_t W = sc.sensor.film_width;
-    L.smp.seed(sc.integ.base_seed + seed, (uint32_t) lane);
+    if (sc.integ.sampler == LR_SAMPLER_LD) L.smp.seed_ld(sc.integ.base_seed, seed, (uint32_t) lane, spp, spp);
+    else L.smp.seed(sc.integ.base_seed + seed, (uint32_t) lane);
     uint32_t pix = (uint32_t) (lane / spp), py = pix / W, px = pix - W * py;
     L.pos = {(float) px, (float) py};
     V2 j = L.smp.next_2d();
@@ -242,6 +243,15 @@ void orc_kat_tea32(uint32_t v0, uint32_t v1, int rounds, uint32_t *out2) { tea32
 float orc_kat_tea_float32(uint32_t v0, uint32_t v1, int rounds) { return tea_float32(v0, v1, rounds); }
 void orc_kat_pcg32_floats(uint64_t initstate, uint64_t initseq, int n, float *out) { PCG32 r; r.seed(initstate, initseq); for (int i = 0; i < n; ++i) out[i] = r.next_f32(); }
 void orc_kat_pcg32_uints(uint64_t initstate, uint64_t initseq, int n, uint32_t *out) { PCG32 r; r.seed(initstate, initseq); for (int i = 0; i < n; ++i) out[i] = r.next_u32(); }
+/* scalar-variant ldsampler (wavefront size 1, samples_per_wavefront 1): n1 next_1d then n2 next_2d per sample index, `advances` times */
+void orc_kat_ldsampler(uint32_t base_seed, uint32_t seed, uint32_t sample_count, int n1, int n2, int advances, float *out) {
+    Sampler s; s.seed_ld(base_seed, seed, 0, 1, sample_count);
+    for (int a = 0; a <= advances; ++a) {
+        if (a) s.advance(1);
+        for (int i = 0; i < n1; ++i) *out++ = s.next_1d();
+        for (int i = 0; i < n2; ++i) { V2 v = s.next_2d(); *out++ = v.x; *out++ = v.y; }
+    }
+}
 void orc_kat_sampler_floats(uint32_t seed, uint32_t lane, int n, float *out) { Sampler s; s.seed(seed, lane); for (int i = 0; i < n; ++i) out[i] = s.next_1d(); }
 void orc_kat_bsdf_eval_pdf(const lr_bsdf *b, const float *wi, const float *wo, float *eval3, float *pdf) {
     BSDF bs(*b); V3 e = bs.eval(V3(wi[0], wi[1], wi[2]), V3(wo[0], wo[1], wo[2])); eval3[0] = e.x; eval3[1] = e.y; eval3[2] = e.z;

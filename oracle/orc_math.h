@@ -150,14 +150,60 @@ struct PCG32 {
 /* independent sampler in the JIT variants: PCG32Sampler::seed
    (src/render/sampler.cpp:129-148) + IndependentSampler::next_1d/2d
    (src/samplers/independent.cpp:88-97) */
+/* permute() for power-of-two sizes (include/mitsuba/core/random.h:196-213) */
+inline uint32_t permute_pow2(uint32_t index, uint32_t size, uint32_t seed) {
+    uint32_t n = 0; while ((1u << n) < size) ++n;
+    for (uint32_t level = 0; level < n; ++level) {
+        uint32_t bit = 1u << level, r0, r1; tea32(index | bit, seed, 2, r0, r1);
+        if ((r0 & bit) == bit) index = index ^ bit;
+    }
+    return index;
+}
+/* radical_inverse_2 / sobol_2, single precision (include/mitsuba/core/qmc.h:190-212, 218-251) */
+inline float radical_inverse_2(uint32_t index, uint32_t scramble) {
+    index = (index << 16) | (index >> 16);
+    index = ((index & 0x00ff00ffu) << 8) | ((index & 0xff00ff00u) >> 8);
+    index = ((index & 0x0f0f0f0fu) << 4) | ((index & 0xf0f0f0f0u) >> 4);
+    index = ((index & 0x33333333u) << 2) | ((index & 0xccccccccu) >> 2);
+    index = ((index & 0x55555555u) << 1) | ((index & 0xaaaaaaaau) >> 1);
+    uint32_t bits = ((index ^ scramble) >> 9) | 0x3f800000u; float f; memcpy(&f, &bits, 4); return f - 1.f;
+}
+inline float sobol_2(uint32_t index, uint32_t scramble) {
+    uint32_t v = 1u << 31;
+    while (index != 0u) { if ((index & 1u) == 1u) scramble ^= v; index >>= 1; v ^= v >> 1; }
+    return (float) scramble / (float) (1ull << 32);
+}
+
+/* The sensor's sampler: `independent` (PCG32Sampler, src/render/sampler.cpp:129-148) or `ldsampler`
+   (src/samplers/ldsampler.cpp:107-141 on top of Sampler::seed / advance / compute_per_sequence_seed /
+   current_sample_index, src/render/sampler.cpp:54-121). */
 struct Sampler {
     PCG32 rng;
+    bool ld = false; uint32_t scramble_seed = 0, dimension_index = 0, sample_index = 0, sample_count = 0;
     void seed(uint32_t base_plus_seed, uint32_t lane) {
         uint32_t v0, v1; tea32(base_plus_seed, lane, 4, v0, v1);
-        rng.seed((uint64_t) v0, (uint64_t) v1);
+        rng.seed((uint64_t) v0, (uint64_t) v1); ld = false;
     }
-    float next_1d() { return rng.next_f32(); }
-    V2 next_2d() { float a = rng.next_f32(); float b = rng.next_f32(); return {a, b}; }
+    /* wavefront lane `lane`, samples_per_wavefront = spp: sequence = pixel, sample index = lane % spp */
+    void seed_ld(uint32_t base_seed, uint32_t seed, uint32_t lane, uint32_t spp, uint32_t count) {
+        uint32_t v0, v1; tea32(base_seed, spp * (lane / spp) + seed, 4, v0, v1);
+        ld = true; scramble_seed = v0; dimension_index = 0; sample_index = lane % spp; sample_count = count;
+    }
+    void advance(uint32_t samples_per_wavefront) { dimension_index = 0; sample_index += samples_per_wavefront; }
+    float next_1d() {
+        if (!ld) return rng.next_f32();
+        uint32_t perm_seed = scramble_seed + dimension_index++;
+        uint32_t i = permute_pow2(sample_index, sample_count, perm_seed);
+        uint32_t s0, s1; tea32(scramble_seed, 0x48bc48ebu, 4, s0, s1);
+        return radical_inverse_2(i, s0);
+    }
+    V2 next_2d() {
+        if (!ld) { float a = rng.next_f32(); float b = rng.next_f32(); return {a, b}; }
+        uint32_t perm_seed = scramble_seed + dimension_index++;
+        uint32_t i = permute_pow2(sample_index, sample_count, perm_seed);
+        uint32_t sx, sy; tea32(scramble_seed, 0x98bc51abu, 4, sx, sy);
+        return {radical_inverse_2(i, sx), sobol_2(i, sy)};
+    }
 };
 
 /* ---- warps (include/mitsuba/core/warp.h) ---------------------------------- */

@@ -46,6 +46,7 @@ def lib():
     L.orc_kat_pcg32_floats.argtypes = [C.c_uint64, C.c_uint64, C.c_int, vp]
     L.orc_kat_pcg32_uints.argtypes = [C.c_uint64, C.c_uint64, C.c_int, vp]
     L.orc_kat_sampler_floats.argtypes = [C.c_uint32, C.c_uint32, C.c_int, vp]
+    L.orc_kat_ldsampler.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, vp]
     L.orc_kat_bsdf_eval_pdf.argtypes = [C.POINTER(K.lr_bsdf), vp, vp, vp, vp]
     L.orc_kat_bsdf_sample.argtypes = [C.POINTER(K.lr_bsdf), vp, C.c_float, C.c_float, C.c_float, vp]; L.orc_kat_bsdf_sample.restype = C.c_uint32
     L.orc_kat_phase_sample.argtypes = [C.c_uint32, C.c_float, vp, C.c_float, C.c_float, vp]

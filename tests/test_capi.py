@@ -85,3 +85,23 @@ def test_unsupported_plugins_raise_like_the_reference():
     d = mi.cornell_box(); d["floor"]["bsdf"] = {"type": "roughdielectric", "int_ior": 1.5, "ext_ior": 1.5}
     with pytest.raises(RuntimeError, match="indices of refraction"):
         mi.load_dict(d)
+
+
+def test_ldsampler_host_rounding_and_oracle_image():
+    """`ldsampler` sample counts are rounded up to a square power of two like LowDiscrepancySampler::set_sample_count
+    (src/samplers/ldsampler.cpp:80-89); the oracle renders with it (CPU, tiny)."""
+    from liverrenderer_b200.scene import ld_sample_count
+    assert [ld_sample_count(n) for n in (1, 4, 5, 16, 17, 64, 100, 1024, 4096)] == [4, 4, 16, 16, 64, 64, 256, 1024, 4096]
+    d = mi.cornell_box(); d["sensor"]["film"]["width"] = d["sensor"]["film"]["height"] = 16
+    d["sensor"]["sampler"] = {"type": "ldsampler", "sample_count": 12}
+    sc = mi.load_dict(d)
+    assert sc.spp == 16 and sc.integrator.sampler == 1
+    from tests import orc
+    o = orc.OracleScene(sc); a = o.sample_lanes(0, 16, 0, 16 * 16 * 16)
+    d["sensor"]["sampler"] = {"type": "independent", "sample_count": 16}
+    b = orc.OracleScene(mi.load_dict(d)).sample_lanes(0, 16, 0, 16 * 16 * 16)
+    assert np.isfinite(a).all() and not np.array_equal(a, b)
+    assert abs(a[:, :3].mean() - b[:, :3].mean()) / b[:, :3].mean() < 0.15      # same integrand, different point sets
+    d["sensor"]["sampler"] = {"type": "stratified"}
+    with pytest.raises(NotImplementedError):
+        mi.load_dict(d)

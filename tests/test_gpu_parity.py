@@ -253,3 +253,48 @@ def test_dda_tracking_matches_reference_order_image():
     m_r, m_d = imgs["reference"].mean(0), imgs["dda"].mean(0)
     assert np.all(np.abs(m_d - m_r) / m_r < 3e-3), (m_r, m_d)
     assert colls["dda"] < 0.6 * colls["reference"], colls
+
+
+# ---------------------------------------------------------------- ldsampler (src/samplers/ldsampler.cpp)
+def _with_ldsampler(d, spp):
+    d["sensor"]["sampler"] = {"type": "ldsampler", "sample_count": spp}
+    return d
+
+
+def test_ldsampler_cornell_per_path():
+    """Same (0,2)-sequence points per lane as the oracle (pinned to the reference's golden values): per-path radiance 1e-4."""
+    sc = mi.load_dict(_with_ldsampler(scenes.cornell_box_path(res=64, spp=16), 16)); n = 64 * 64 * 16
+    gpu = mi.Context(0).upload(sc).sample_lanes(0, 16, 0, n); cpu = orc.OracleScene(sc).sample_lanes(0, 16, 0, n)
+    assert path_match_fraction(gpu, cpu, 1e-4) > 0.998
+    assert np.array_equal(gpu[:, 3], cpu[:, 3])
+    # and it is a different point set than the independent sampler's
+    ind = mi.Context(0).upload(mi.load_dict(scenes.cornell_box_path(res=64, spp=16))).sample_lanes(0, 16, 0, n)
+    assert path_match_fraction(gpu, ind, 1e-4) < 0.5
+
+
+def test_ldsampler_liver_volpath_wavefront_and_per_lane(monkeypatch):
+    """Heterogeneous volpath with the ldsampler: wavefront == per-lane kernel == oracle, lane for lane (reference-order tracking)."""
+    sc = mi.load_dict(_with_ldsampler(scenes.liver_single_mesh(res=32, spp=16, grid_res=32), 16)); n = 32 * 32 * 16
+    wf = mi.Context(0).upload(sc).sample_lanes(2, 16, 0, n)
+    cpu = orc.OracleScene(sc).sample_lanes(2, 16, 0, n)
+    assert path_match_fraction(wf, cpu, 1e-3) > 0.97
+    monkeypatch.setenv("LR_MEGAKERNEL", "1")
+    mk = mi.Context(0).upload(sc).sample_lanes(2, 16, 0, n)
+    assert (rel_err(wf[:, :3], mk[:, :3], 1e-3).max(axis=1) < 1e-5).mean() > 0.999
+
+
+def test_ldsampler_converges_faster_than_independent():
+    """What the sampler is for: at equal spp the ldsampler image of the (directly lit) Cornell box is closer to a converged
+    reference than the independent sampler's."""
+    ref = mi.render(mi.load_dict(scenes.cornell_box_path(res=48, spp=4096)), spp=4096, seed=11)
+    a = mi.render(mi.load_dict(_with_ldsampler(scenes.cornell_box_path(res=48, spp=64), 64)), spp=64, seed=1)
+    b = mi.render(mi.load_dict(scenes.cornell_box_path(res=48, spp=64)), spp=64, seed=1)
+    ea, eb = float(np.mean((a - ref) ** 2)), float(np.mean((b - ref) ** 2))
+    assert ea < eb, (ea, eb)
+
+
+def test_ldsampler_rejects_non_square_power_of_two_spp():
+    sc = mi.load_dict(_with_ldsampler(scenes.cornell_box_path(res=16, spp=16), 16))
+    ctx = mi.Context(0).upload(sc)
+    with pytest.raises(RuntimeError):
+        ctx.render(seed=0, spp=8)

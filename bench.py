@@ -244,7 +244,15 @@ def run_b200(args):
     k_ms = tot["tracking_ms"] / max(tot["tracking_launches"], 1)
     bytes_per_launch = tot["collisions"] / max(tot["tracking_launches"], 1) * 32.0
     achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+    traffic = None; traffic_src = None
+    try:                                                     # dram__bytes_read+write per TRACK/NEE launch from the committed ncu capture
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_tracking_traffic.json")))
+        if args.workload == "c3" and args.tracking == "dda":
+            traffic = float(tj["traffic_bytes_per_launch"]); traffic_src = "profiles/r1_tracking_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over %d launches of: %s)" % (tj["launches"], tj["command"])
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
+                "algorithmic_bytes_per_launch": bytes_per_launch,
                 "kernel": "k_wf_track + k_wf_nee (free-flight / ratio tracking with trilinear sigma_t taps; CUDA events around every launch, "
                           "lr_stats.tracking_ms / tracking_launches)",
                 "algorithmic_bytes_per_unit": 32, "units_per_launch": tot["collisions"] / max(tot["tracking_launches"], 1),

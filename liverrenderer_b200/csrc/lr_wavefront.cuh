@@ -375,7 +375,11 @@ LR_DEV bool wf_nee_setup(const DScene &sc, const WFArgs &a, WState *S, Sampler &
     if (ds.pdf == 0.f) return false;
     Ray ray = spawn_ray_to(ref_p, ref_n, ds.p);
     if (ref_si && mesh_is_transition(sc, ref_si->mesh)) medium = target_medium(sc, *ref_si, ray.d);
-    cnt.rays++; Hit h = bvh_trace<false, false>(sc, ray);
+    cnt.rays++; Hit h;
+    // production mode without index-matched boundaries: every surface blocks a shadow ray, so the first accepted triangle decides
+    // (any-hit query, no closest hit needed); a miss leaves the whole segment to the medium walk
+    if (sc.integ.tracking == LR_TRACKING_DDA && !sc.any_null_bsdf) { h = bvh_trace<true, false>(sc, ray); if (hit_valid(h)) return false; }
+    else h = bvh_trace<false, false>(sc, ray);
     if (sc.integ.tracking == LR_TRACKING_DDA && hit_valid(h)) {
         // production mode: opaque-occluder pre-test.  A non-null surface anywhere on the shadow segment makes the transmittance
         // exactly 0 (eval_null_transmission), so the ratio-tracking walk is skipped; only the RNG consumption differs.

@@ -270,7 +270,22 @@ def run_b200(args):
                      "collisions_per_s": st2["collisions"] / (ms2 * 1e-3), "tracking_GBps_algorithmic": st2["collisions"] * 32.0 / max(st2["tracking_ms"], 1e-9) / 1e6,
                      "note": "LR_TRACKING_REFERENCE: identical PCG32 draw order to the reference (global majorant)"}
         c2.close()
-    return dict(ref_order=ref_order, torch=torch, dist=dist, mi=mi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local, spp=spp, name=name,
+    bump = None
+    if args.workload == "c3":
+        # the same config with the fork's own boundary (bumpmap(bitmap) over a smooth dielectric, scene.xml:31-40) instead of
+        # SURVEY 8(d)'s roughdielectric substitute: exercises the bitmap-texture / bump-frame code on the full workload
+        from liverrenderer_b200 import scenes as _sc
+        d3 = _sc.liver_single_mesh(res=args.res, spp=spp, grid_res=256, tracking=args.tracking, surface="bumpmap")
+        c3 = mi.Context(local).upload(mi.load_dict(d3)); c3.set_stream(stream.cuda_stream)
+        c3.film_clear(); c3.render_lanes(7, spp, 0, 0); barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(stream); c3.film_clear(); c3.render_lanes(8 + rank, spp, 0, 0); e1.record(stream); barrier()
+        st3 = c3.stats(); ms3 = e0.elapsed_time(e1)
+        bump = {"value": st3["samples"] / (ms3 * 1e-3), "unit": UNIT + " per GPU", "mrays_per_s": st3["rays"] / (ms3 * 1e-3) / 1e6,
+                "collisions_per_sample": st3["collisions"] / max(st3["samples"], 1),
+                "note": "C3 with the boundary BSDF bumpmap(scale 0.005, bitmap 512^2 rgb) -> dielectric 1.38"}
+        c3.close()
+    return dict(ref_order=ref_order, bump=bump, torch=torch, dist=dist, mi=mi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local, spp=spp, name=name,
                 W=W, H=H, value=value, ms_max=ms_max, rays=rays, colls=colls, samples=samples, tot=tot, roofline=roofline, clk=clk,
                 barrier=barrier, flush=flush, hbm_peak=hbm_peak)
 
@@ -379,7 +394,7 @@ def main():
                 "mrays_per_s": R["rays"] / secs / 1e6, "collisions_per_s": R["colls"] / secs,
                 "collisions_per_sample": R["colls"] / max(R["samples"], 1), "rays_per_sample": R["rays"] / max(R["samples"], 1),
                 "e2e": e2e, "gpu_launches": int(R["tot"]["launches"]), "clocks": R["clk"], "roofline": R["roofline"], "cpu_baseline": cpu, "prb": prb,
-                "reference_order_tracking": R["ref_order"]}
+                "reference_order_tracking": R["ref_order"], "bumpmap_surface": R["bump"]}
         print(json.dumps(line), flush=True)
     if R["world"] > 1:
         R["dist"].destroy_process_group()

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define LR_API_VERSION 1
+#define LR_API_VERSION 2
 
 typedef enum lr_status {
     LR_OK                = 0,
@@ -65,6 +65,8 @@ typedef enum lr_bsdf_kind {
     LR_BSDF_NULL            = 3,  /* src/bsdfs/null.cpp (index-matched boundary) */
     LR_BSDF_DIELECTRIC      = 4   /* src/bsdfs/dielectric.cpp (smooth)         */
 } lr_bsdf_kind;
+/* `bumpmap` (src/bsdfs/bumpmap.cpp:96-281) is not a kind: it wraps any of the above through
+   lr_bsdf.bump_tex (the nested BSDF is the block itself).                                    */
 
 typedef enum lr_microfacet_kind { LR_MF_BECKMANN = 0, LR_MF_GGX = 1 } lr_microfacet_kind;
 
@@ -118,7 +120,23 @@ typedef struct lr_mesh {
     uint32_t reserved;
 } lr_mesh;
 
-/* BSDF parameter block; only constant (`rgb` / float) textures are on the path. */
+/* `bitmap` texture (src/textures/bitmap.cpp:395-930) evaluated the way the LLVM variants do:
+   dr::Texture<Float,2>::eval_nonaccel / eval_fetch_nonaccel
+   (ext/drjit/include/drjit/texture.h:484-556,704-735), wrap (:1369-1396).
+   `data` is what the reference holds after load: linear values (the host converts 8-bit sRGB
+   files unless `raw`), row-major [height][width][channels].                                  */
+typedef enum lr_tex_filter { LR_TEX_BILINEAR = 0, LR_TEX_NEAREST = 1 } lr_tex_filter;
+typedef struct lr_texture {
+    const float *data;              /* [height*width*channels]                  */
+    uint32_t width, height;
+    uint32_t channels;              /* 1 or 3                                   */
+    uint32_t filter;                /* lr_tex_filter (`filter_type`)            */
+    uint32_t wrap;                  /* lr_grid_wrap (`wrap_mode`, default repeat) */
+    uint32_t reserved;
+    float    to_uv[6];              /* 2x3 affine, row-major: uv' = to_uv * (u, v, 1) */
+} lr_texture;
+
+/* BSDF parameter block.  Texture slots hold 0 for "none" or 1 + index into lr_scene.textures. */
 typedef struct lr_bsdf {
     uint32_t kind;                  /* lr_bsdf_kind                             */
     uint32_t mf_kind;               /* lr_microfacet_kind (roughdielectric)     */
@@ -133,11 +151,21 @@ typedef struct lr_bsdf {
     float sheen, sheen_tint, flatness, clearcoat, clearcoat_gloss;
     float diff_refl_srate, main_spec_srate, clearcoat_srate;
     /* `reflectance` texture: 0 = constant, 1 = checkerboard (src/textures/checkerboard.cpp:70-89):
-       color0 = reflectance, color1 = tex_color1, uv' = tex_to_uv (2x3 affine, row-major) * (u, v, 1) */
+       color0 = reflectance, color1 = tex_color1, uv' = tex_to_uv (2x3 affine, row-major) * (u, v, 1);
+       2 = bitmap: Texture::eval of slot `refl_tex` (bitmap.cpp:443-485, 1-channel => grey)     */
     uint32_t tex_kind;
     float tex_color1[3];
     float tex_to_uv[6];
+    uint32_t refl_tex;              /* texture slot for tex_kind == 2           */
+    /* `bumpmap` wrapper (src/bsdfs/bumpmap.cpp): slot != 0 => sample/eval/pdf run in the frame
+       perturbed by `bump_scale * eval_1_grad(texture)` (:248-276)                            */
+    uint32_t bump_tex;              /* texture slot, 0 = no bump map            */
+    float    bump_scale;            /* `scale`, default 1                       */
+    uint32_t bump_flags;            /* LR_BUMP_*                                */
 } lr_bsdf;
+
+#define LR_BUMP_FLIP_INVALID_NORMALS (1u << 0)   /* `flip_invalid_normals`, default on  (:265-269) */
+#define LR_BUMP_SHADOWING_FUNCTION   (1u << 1)   /* `use_shadowing_function`, default on (normalmap_helpers.h:20-25) */
 
 #define LR_PR_HAS_ANISOTROPIC (1u << 0)
 #define LR_PR_HAS_METALLIC    (1u << 1)
@@ -220,6 +248,8 @@ typedef struct lr_integrator {
 typedef struct lr_scene {
     uint32_t api_version;           /* LR_API_VERSION                           */
     uint32_t n_meshes, n_bsdfs, n_media, n_grids, n_emitters;
+    uint32_t n_textures;
+    const lr_texture *textures;
     const lr_mesh    *meshes;
     const lr_bsdf    *bsdfs;
     const lr_medium  *media;

@@ -14,6 +14,7 @@ c_uint32_p = C.POINTER(C.c_uint32)
 
 # ---- enums (values mirror lr_api.h) -----------------------------------------
 LR_OK = 0
+LR_API_VERSION = 2
 LR_ERR = {-1: "invalid argument", -2: "no CUDA device (this backend has no CPU path)", -3: "CUDA error",
           -4: "unsupported plugin/option", -5: "no scene uploaded", -6: "cancelled", -7: "out of memory"}
 
@@ -28,6 +29,8 @@ EMITTER_AREA, EMITTER_CONSTANT, EMITTER_ENVMAP = 0, 1, 2
 RFILTER_BOX, RFILTER_GAUSSIAN, RFILTER_TENT = 0, 1, 2
 FILTER_NEAREST, FILTER_TRILINEAR = 0, 1
 WRAP_REPEAT, WRAP_MIRROR, WRAP_CLAMP = 0, 1, 2
+TEX_BILINEAR, TEX_NEAREST = 0, 1
+BUMP_FLIP_INVALID_NORMALS, BUMP_SHADOWING_FUNCTION = 1, 2
 
 PR_HAS_ANISOTROPIC, PR_HAS_METALLIC, PR_HAS_SPEC_TRANS, PR_HAS_SPEC_TINT = 1, 2, 4, 8
 PR_HAS_SHEEN, PR_HAS_SHEEN_TINT, PR_HAS_FLATNESS, PR_HAS_CLEARCOAT, PR_ETA_SPECULAR = 16, 32, 64, 128, 256
@@ -48,7 +51,13 @@ class lr_bsdf(C.Structure):
                 ("specular", C.c_float), ("spec_tint", C.c_float), ("sheen", C.c_float), ("sheen_tint", C.c_float),
                 ("flatness", C.c_float), ("clearcoat", C.c_float), ("clearcoat_gloss", C.c_float),
                 ("diff_refl_srate", C.c_float), ("main_spec_srate", C.c_float), ("clearcoat_srate", C.c_float),
-                ("tex_kind", C.c_uint32), ("tex_color1", C.c_float * 3), ("tex_to_uv", C.c_float * 6)]
+                ("tex_kind", C.c_uint32), ("tex_color1", C.c_float * 3), ("tex_to_uv", C.c_float * 6),
+                ("refl_tex", C.c_uint32), ("bump_tex", C.c_uint32), ("bump_scale", C.c_float), ("bump_flags", C.c_uint32)]
+
+
+class lr_texture(C.Structure):
+    _fields_ = [("data", c_float_p), ("width", C.c_uint32), ("height", C.c_uint32), ("channels", C.c_uint32),
+                ("filter", C.c_uint32), ("wrap", C.c_uint32), ("reserved", C.c_uint32), ("to_uv", C.c_float * 6)]
 
 
 class lr_grid(C.Structure):
@@ -85,8 +94,8 @@ class lr_integrator(C.Structure):
 
 class lr_scene(C.Structure):
     _fields_ = [("api_version", C.c_uint32), ("n_meshes", C.c_uint32), ("n_bsdfs", C.c_uint32), ("n_media", C.c_uint32),
-                ("n_grids", C.c_uint32), ("n_emitters", C.c_uint32),
-                ("meshes", C.POINTER(lr_mesh)), ("bsdfs", C.POINTER(lr_bsdf)), ("media", C.POINTER(lr_medium)),
+                ("n_grids", C.c_uint32), ("n_emitters", C.c_uint32), ("n_textures", C.c_uint32),
+                ("textures", C.POINTER(lr_texture)), ("meshes", C.POINTER(lr_mesh)), ("bsdfs", C.POINTER(lr_bsdf)), ("media", C.POINTER(lr_medium)),
                 ("grids", C.POINTER(lr_grid)), ("emitters", C.POINTER(lr_emitter)),
                 ("sensor", lr_sensor), ("integrator", lr_integrator)]
 

@@ -63,6 +63,28 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     { DevBuf *b = c->newbuf(); if (int r = upload(c, b, meshes.data(), meshes.size())) return r; sc.meshes = b->as<DMesh>(); sc.n_meshes = s->n_meshes; }
     { DevBuf *b = c->newbuf(); if (int r = upload(c, b, s->bsdfs, s->n_bsdfs)) return r; sc.bsdfs = b->as<lr_bsdf>(); }
     if (int r = build_bvh(c, tris, lo, hi)) return r;
+    sc.tris_gid = c->tris_gid ? c->tris_gid->as<DTri>() : nullptr;
+
+    // ---- bitmap textures (reflectance / bump maps) ----
+    {
+        std::vector<DTex> tex(std::max<uint32_t>(s->n_textures, 1)); memset(tex.data(), 0, tex.size() * sizeof(DTex));
+        for (uint32_t i = 0; i < s->n_textures; ++i) {
+            const lr_texture &t = s->textures[i]; DTex &d = tex[i];
+            if (!t.data || t.width < 2 || t.height < 2) LR_FAIL(c, LR_ERR_INVALID_ARG, "texture %u: needs data of at least 2x2 pixels", i);
+            if (t.channels != 1 && t.channels != 3) LR_FAIL(c, LR_ERR_UNSUPPORTED, "texture %u: channels must be 1 or 3", i);
+            if (t.filter > LR_TEX_NEAREST || t.wrap > LR_WRAP_CLAMP) LR_FAIL(c, LR_ERR_INVALID_ARG, "texture %u: unknown filter / wrap mode", i);
+            DevBuf *b = c->newbuf(); if (int r = upload(c, b, t.data, (size_t) t.width * t.height * t.channels)) return r;
+            d.data = b->as<float>(); d.w = (int) t.width; d.h = (int) t.height; d.ch = (int) t.channels; d.filter = t.filter; d.wrap = t.wrap;
+            memcpy(d.to_uv, t.to_uv, sizeof d.to_uv);
+        }
+        DevBuf *b = c->newbuf(); if (int r = upload(c, b, tex.data(), tex.size())) return r; sc.textures = b->as<DTex>();
+        for (uint32_t i = 0; i < s->n_bsdfs; ++i) {
+            const lr_bsdf &bs = s->bsdfs[i];
+            if (bs.bump_tex > s->n_textures || (bs.tex_kind == 2 && (bs.refl_tex == 0 || bs.refl_tex > s->n_textures)))
+                LR_FAIL(c, LR_ERR_INVALID_ARG, "bsdf %u: texture slot out of range", i);
+            if (bs.tex_kind > 2) LR_FAIL(c, LR_ERR_UNSUPPORTED, "bsdf %u: unknown reflectance texture kind %u", i, bs.tex_kind);
+        }
+    }
 
     // ---- grids ----
     c->h_grids.resize(s->n_grids); c->grid_floats.resize(s->n_grids); c->grid_fixed_max.assign(s->n_grids, -1.f);

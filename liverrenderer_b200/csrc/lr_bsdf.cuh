@@ -160,12 +160,133 @@ LR_DEV void calc_dist_params(float anisotropic, float roughness, bool has_aniso,
     ax = fmaxf(0.001f, r2 / aspect); ay = fmaxf(0.001f, r2 * aspect);
 }
 
+// ---- bitmap textures (src/textures/bitmap.cpp on dr::Texture<Float,2>::eval_nonaccel,
+//      ext/drjit/include/drjit/texture.h:484-556,704-735; wrap :1369-1396) -------------------------
+LR_DEV int tex_wrap(int p, int r, uint32_t wrap) {
+    if (wrap == LR_WRAP_CLAMP) return min(max(p, 0), r - 1);
+    int sh = p < 0 ? p + 1 : p; int div = sh / r;
+    int mod = p - div * r; if (mod < 0) mod += r;
+    if (wrap == LR_WRAP_MIRROR) { bool keep = ((div & 1) == 0) != (p < 0); if (!keep) mod = r - 1 - mod; }
+    return mod;
+}
+LR_DEV V2 tex_xform(const DTex &t, V2 uv) {
+    return mk2(fmaf(t.to_uv[0], uv.x, fmaf(t.to_uv[1], uv.y, t.to_uv[2])), fmaf(t.to_uv[3], uv.x, fmaf(t.to_uv[4], uv.y, t.to_uv[5])));
+}
+LR_DEV float tex_lum(const float *c) { return __fadd_rn(__fadd_rn(__fmul_rn(c[0], 0.212671f), __fmul_rn(c[1], 0.715160f)), __fmul_rn(c[2], 0.072169f)); }
+// the four bilinear taps (00, 10, 01, 11) and the fractional weights
+LR_DEV void tex_fetch4(const DTex &t, V2 uv, const float *tap[4], float &w1x, float &w1y) {
+    float fx = fmaf(uv.x, (float) t.w, -.5f), fy = fmaf(uv.y, (float) t.h, -.5f);
+    int ix = (int) floorf(fx), iy = (int) floorf(fy);
+    w1x = __fsub_rn(fx, (float) ix); w1y = __fsub_rn(fy, (float) iy);
+    int x0 = tex_wrap(ix, t.w, t.wrap), x1 = tex_wrap(ix + 1, t.w, t.wrap), y0 = tex_wrap(iy, t.h, t.wrap), y1 = tex_wrap(iy + 1, t.h, t.wrap);
+    tap[0] = t.data + ((size_t) y0 * t.w + x0) * t.ch; tap[1] = t.data + ((size_t) y0 * t.w + x1) * t.ch;
+    tap[2] = t.data + ((size_t) y1 * t.w + x0) * t.ch; tap[3] = t.data + ((size_t) y1 * t.w + x1) * t.ch;
+}
+// Texture::eval for *_rgb variants (bitmap.cpp:443-485): 1 channel => grey
+__device__ __noinline__ V3 tex_eval(const DTex &t, V2 uv_in) {
+    V2 uv = tex_xform(t, uv_in); float o[3] = {0.f, 0.f, 0.f};
+    if (t.filter == LR_TEX_NEAREST) {
+        int ix = tex_wrap((int) floorf(__fmul_rn(uv.x, (float) t.w)), t.w, t.wrap), iy = tex_wrap((int) floorf(__fmul_rn(uv.y, (float) t.h)), t.h, t.wrap);
+        const float *p = t.data + ((size_t) iy * t.w + ix) * t.ch;
+        for (int c = 0; c < t.ch; ++c) o[c] = __ldg(p + c);
+    } else {
+        const float *tp[4]; float w1x, w1y; tex_fetch4(t, uv, tp, w1x, w1y);
+        float w0x = __fsub_rn(1.f, w1x), w0y = __fsub_rn(1.f, w1y);
+        const float wt[4] = {__fmul_rn(w0x, w0y), __fmul_rn(w1x, w0y), __fmul_rn(w0x, w1y), __fmul_rn(w1x, w1y)};
+        for (int k = 0; k < 4; ++k) for (int c = 0; c < t.ch; ++c) o[c] = fmaf(__ldg(tp[k] + c), wt[k], o[c]);
+    }
+    return t.ch == 1 ? mk3(o[0]) : mk3(o[0], o[1], o[2]);
+}
+// eval_1_grad (bitmap.cpp:509-578)
+LR_DEV V2 tex_eval_1_grad(const DTex &t, V2 uv_in) {
+    if (t.filter != LR_TEX_BILINEAR) return mk2(0.f, 0.f);
+    V2 uv = tex_xform(t, uv_in);
+    const float *tp[4]; float w1x, w1y; tex_fetch4(t, uv, tp, w1x, w1y);
+    float f[4];
+    for (int k = 0; k < 4; ++k) {
+        if (t.ch == 1) f[k] = __ldg(tp[k]);
+        else { float c[3] = {__ldg(tp[k]), __ldg(tp[k] + 1), __ldg(tp[k] + 2)}; f[k] = tex_lum(c); }
+    }
+    float w0x = __fsub_rn(1.f, w1x), w0y = __fsub_rn(1.f, w1y);
+    float dx = fmaf(w0y, __fsub_rn(f[1], f[0]), __fmul_rn(w1y, __fsub_rn(f[3], f[2]))),
+          dy = fmaf(w0x, __fsub_rn(f[2], f[0]), __fmul_rn(w1x, __fsub_rn(f[3], f[1])));
+    float du = __fadd_rn(__fmul_rn(t.to_uv[0], dx), __fmul_rn(t.to_uv[3], dy)), dv = __fadd_rn(__fmul_rn(t.to_uv[1], dx), __fmul_rn(t.to_uv[4], dy));
+    return mk2(__fmul_rn((float) t.w, du), __fmul_rn((float) t.h, dv));
+}
+
+// ---- bumpmap (src/bsdfs/bumpmap.cpp) -------------------------------------------------------------
+// The perturbed frame is recomputed where it is needed (before and after the nested BSDF call) from the
+// few interaction fields below, so lanes on plain BSDFs carry no extra live state through the stage kernels.
+struct BumpIn { V3 n, shn, shs, sht, wi; V2 uv; uint32_t prim; int mesh; };
+// BumpMap::frame (bumpmap.cpp:248-276).  dp_du / dp_dv: Mesh::compute_surface_interaction (mesh.cpp:1540-1575),
+// recomputed from the triangle with the arithmetic of compute_si.
+LR_DEV Frame bump_frame(const DScene &sc, const lr_bsdf &b, const BumpIn in) {
+    const DTri tr = sc.tris_gid[in.prim];
+    const DMesh &me = sc.meshes[in.mesh];
+    V3 p0 = f4xyz(tr.v0), p1 = f4xyz(tr.v1), p2 = f4xyz(tr.v2);
+    V3 dp0 = p1 - p0, dp1 = p2 - p0;
+    V3 dp_du, dp_dv; coordinate_system(normalize(cross(dp0, dp1)), dp_du, dp_dv);
+    if (me.uv) {
+        uint32_t face = in.prim - me.tri_offset;
+        uint32_t i0 = me.idx[3 * face], i1 = me.idx[3 * face + 1], i2 = me.idx[3 * face + 2];
+        V2 uv0 = mk2(me.uv[2 * i0], me.uv[2 * i0 + 1]), uv1 = mk2(me.uv[2 * i1], me.uv[2 * i1 + 1]), uv2 = mk2(me.uv[2 * i2], me.uv[2 * i2 + 1]);
+        V2 duv0 = mk2(uv1.x - uv0.x, uv1.y - uv0.y), duv1 = mk2(uv2.x - uv0.x, uv2.y - uv0.y);
+        float det = fmaf(duv0.x, duv1.y, -__fmul_rn(duv0.y, duv1.x));
+        if (det != 0.f) {
+            float inv_det = 1.f / det;
+            dp_du = mk3(fmaf(duv1.y, dp0.x, -__fmul_rn(duv0.y, dp1.x)), fmaf(duv1.y, dp0.y, -__fmul_rn(duv0.y, dp1.y)),
+                        fmaf(duv1.y, dp0.z, -__fmul_rn(duv0.y, dp1.z))) * inv_det;
+            dp_dv = mk3(fmaf(-duv1.x, dp0.x, __fmul_rn(duv0.x, dp1.x)), fmaf(-duv1.x, dp0.y, __fmul_rn(duv0.x, dp1.y)),
+                        fmaf(-duv1.x, dp0.z, __fmul_rn(duv0.x, dp1.z))) * inv_det;
+        }
+    }
+    V2 g = tex_eval_1_grad(sc.textures[b.bump_tex - 1], in.uv);
+    g.x = __fmul_rn(g.x, b.bump_scale); g.y = __fmul_rn(g.y, b.bump_scale);
+    V3 pu = fma3(in.shn, __fsub_rn(g.x, dot(in.shn, dp_du)), dp_du), pv = fma3(in.shn, __fsub_rn(g.y, dot(in.shn, dp_dv)), dp_dv);
+    Frame r;
+    r.n = normalize(cross(pu, pv));
+    if (dot(in.n, r.n) < 0.f) r.n = -r.n;
+    r.n = mk3(dot(r.n, in.shs), dot(r.n, in.sht), dot(r.n, in.shn));          // si.to_local
+    if (b.bump_flags & LR_BUMP_FLIP_INVALID_NORMALS) {
+        if (in.wi.z * dot(in.wi, r.n) <= 0.f) r.n = mk3(-r.n.x, -r.n.y, r.n.z);
+    }
+    r.s = normalize(fma3(r.n, -dot(r.n, dp_du), dp_du));                       // (sic) world-space dp_du, as the reference
+    r.t = cross(r.n, r.s);
+    return r;
+}
+// eval_shadow_terminator (src/bsdfs/normalmap_helpers.h:20-25; Frame::tan_theta_2, frame.h:80-83)
+LR_DEV float tan_theta_2(V3 v) { return fmaxf(fmaf(-v.z, v.z, 1.f), 0.f) / sqr(v.z); }
+LR_DEV float shadow_terminator(V3 pn, V3 wo) {
+    float alpha2 = fminf(0.125f * tan_theta_2(pn), 1.f);
+    return 2.f / (1.f + sqrtf(1.f + alpha2 * tan_theta_2(wo)));
+}
+
+struct BumpSampleOut { BSDFSample bs; V3 weight; };
+__device__ __noinline__ BumpSampleOut bump_sample(const DScene &sc, const lr_bsdf &b, const BumpIn in, float s1, V2 s2);
+__device__ __noinline__ float4 bump_eval_pdf(const DScene &sc, const lr_bsdf &b, const BumpIn in, V3 wo);
+
 struct PrParams { float anisotropic, roughness, spec_trans, metallic, clearcoat, flatness, sheen, brdf, bsdf; };
 
 struct BSDF {
-    const lr_bsdf &b; V2 uv;
-    LR_DEV BSDF(const lr_bsdf &b_, V2 uv_) : b(b_), uv(uv_) {}
+    const DScene &sc; const lr_bsdf &b; V2 uv; const SurfaceInteraction *si;
+    LR_DEV BSDF(const DScene &sc_, const SurfaceInteraction &si_) : sc(sc_), b(sc_.bsdfs[sc_.meshes[si_.mesh].bsdf]), uv(si_.uv), si(&si_) {}
+    LR_DEV BSDF(const DScene &sc_, const lr_bsdf &b_, V2 uv_) : sc(sc_), b(b_), uv(uv_), si(nullptr) {}      // nested BSDF of a bump map
+    LR_DEV BumpIn bump_in() const {
+        BumpIn in; in.n = si->n; in.shn = si->sh.n; in.shs = si->sh.s; in.sht = si->sh.t; in.wi = si->wi; in.uv = si->uv; in.prim = si->prim; in.mesh = si->mesh;
+        return in;
+    }
+    // Bump-mapped BSDFs leave the stage kernel through one out-of-line call, so lanes on plain BSDFs keep the
+    // register allocation they had (the wrapper's state never lives across the inlined nested code).
+    LR_DEV BSDFSample sample(V3 wi, float s1, V2 s2, V3 &weight) const {
+        if (b.bump_tex) { BumpSampleOut o = bump_sample(sc, b, bump_in(), s1, s2); weight = o.weight; return o.bs; }
+        return sample_n(wi, s1, s2, weight);
+    }
+    LR_DEV V3 eval_pdf(V3 wi, V3 wo, float &pdf) const {
+        if (b.bump_tex) { float4 r = bump_eval_pdf(sc, b, bump_in(), wo); pdf = r.w; return mk3(r.x, r.y, r.z); }
+        return eval_pdf_n(wi, wo, pdf);
+    }
     LR_DEV V3 refl() const {
+        if (b.tex_kind == 2) return tex_eval(sc.textures[b.refl_tex - 1], uv);   // bitmap reflectance
         if (b.tex_kind == 1) {                      // checkerboard (src/textures/checkerboard.cpp:70-89)
             float u = fmaf(b.tex_to_uv[0], uv.x, fmaf(b.tex_to_uv[1], uv.y, b.tex_to_uv[2])),
                   v = fmaf(b.tex_to_uv[3], uv.x, fmaf(b.tex_to_uv[4], uv.y, b.tex_to_uv[5]));
@@ -331,7 +452,7 @@ struct BSDF {
         return bs;
     }
 
-    LR_DEV BSDFSample sample(V3 wi, float s1, V2 s2, V3 &weight) const {
+    LR_DEV BSDFSample sample_n(V3 wi, float s1, V2 s2, V3 &weight) const {
         BSDFSample bs; bs.wo = mk3(0.f); bs.pdf = 0.f; bs.eta = 0.f; bs.sampled_type = 0; weight = mk3(0.f);
         switch (b.kind) {
         case LR_BSDF_DIFFUSE: {
@@ -377,7 +498,7 @@ struct BSDF {
         return bs;
     }
     // eval and pdf in one go (the integrators always need both)
-    LR_DEV V3 eval_pdf(V3 wi, V3 wo, float &pdf) const {
+    LR_DEV V3 eval_pdf_n(V3 wi, V3 wo, float &pdf) const {
         pdf = 0.f;
         switch (b.kind) {
         case LR_BSDF_DIFFUSE: {
@@ -408,6 +529,28 @@ struct BSDF {
         }
     }
 };
+
+// BumpMap::sample / eval / pdf (src/bsdfs/bumpmap.cpp:136-233): the nested BSDF runs in the perturbed frame; `in.wi`
+// is the incident direction in the original shading frame.
+__device__ __noinline__ BumpSampleOut bump_sample(const DScene &sc, const lr_bsdf &b, const BumpIn in, float s1, V2 s2) {
+    Frame pf = bump_frame(sc, b, in); BSDF nested(sc, b, in.uv); BumpSampleOut o;
+    o.bs = nested.sample_n(pf.to_local(in.wi), s1, s2, o.weight);
+    bool active = o.weight.x != 0.f || o.weight.y != 0.f || o.weight.z != 0.f;
+    V3 pwo = pf.to_world(o.bs.wo);
+    active &= o.bs.wo.z * pwo.z > 0.f;
+    o.bs.wo = pwo;
+    if (b.bump_flags & LR_BUMP_SHADOWING_FUNCTION) o.weight = o.weight * shadow_terminator(pf.n, pwo);
+    if (!active) o.weight = mk3(0.f);
+    return o;
+}
+__device__ __noinline__ float4 bump_eval_pdf(const DScene &sc, const lr_bsdf &b, const BumpIn in, V3 wo) {
+    Frame pf = bump_frame(sc, b, in); V3 pwo = pf.to_local(wo);
+    if (!(wo.z * pwo.z > 0.f)) return make_float4(0.f, 0.f, 0.f, 0.f);
+    BSDF nested(sc, b, in.uv); float pdf;
+    V3 v = nested.eval_pdf_n(pf.to_local(in.wi), pwo, pdf);
+    if (b.bump_flags & LR_BUMP_SHADOWING_FUNCTION) v = v * shadow_terminator(pf.n, wo);
+    return make_float4(v.x, v.y, v.z, pdf);
+}
 
 // ---- phase functions -----------------------------------------------------------------------
 struct Phase {

@@ -82,7 +82,7 @@ LR_DEV LaneResult sample_path(const DScene &sc, const DTri *tris_gid, Sampler &s
         }
         bool active_next = (depth + 1 < sc.max_depth) && si_valid(si);
         if (!si_valid(si)) break;
-        BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+        BSDF bsdf(sc, si);
         bool active_em = active_next && (bsdf.flags() & F_SMOOTH);
         DirectionSample ds; ds.pdf = 0.f; ds.delta = false; ds.d = mk3(0.f); V3 em_weight = mk3(0.f), wo = mk3(0.f);
         V2 u_em = smp.next_2d();
@@ -163,7 +163,7 @@ LR_DEV V3 sample_emitter_vol(const DScene &sc, const DTri *tris_gid, V3 ref_p, V
         if (active_surface) total_dist += si.t;
         active_surface &= si_valid(si) && !active_medium;
         if (active_surface) {
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+            BSDF bsdf(sc, si);
             transmittance *= bsdf.eval_null_transmission();
             Ray r2 = spawn_ray(si.p, si.n, ray.d); ray.o = r2.o;
         }
@@ -263,7 +263,7 @@ LR_DEV LaneResult sample_volpath(const DScene &sc, const DTri *tris_gid, Sampler
         }
         active_surface &= si_valid(si);
         if (active_surface) {
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+            BSDF bsdf(sc, si);
             if ((bsdf.flags() & F_SMOOTH) && (depth + 1 < sc.max_depth)) {
                 DirectionSample ds;
                 V3 emitted = sample_emitter_vol(sc, tris_gid, si.p, si.n, &si, smp, medium, channel, ds, cnt);

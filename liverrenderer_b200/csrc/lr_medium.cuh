@@ -10,7 +10,7 @@ namespace lr {
 
 LR_DEV int wrap_i(int p, int r, uint32_t wrap) {
     if (wrap == LR_WRAP_CLAMP) return min(max(p, 0), r - 1);
-    int sh = p < 0 ? p + 1 : p; int div = sh / r; if (p < 0) div -= 1;
+    int sh = p < 0 ? p + 1 : p; int div = sh / r;
     int mod = p - div * r; if (mod < 0) mod += r;
     if (wrap == LR_WRAP_MIRROR) { bool keep = ((div & 1) == 0) != (p < 0); if (!keep) mod = r - 1 - mod; }
     return mod;

@@ -73,7 +73,7 @@ LR_DEV V3 sample_emitter_prb(const DScene &sc, const DTri *tris_gid, V3 ref_p, V
         }
         active_surface |= escaped_medium;
         active_surface &= si_valid(si) && !active_medium;
-        if (active_surface) { BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv); tr_multiplier *= bsdf.eval_null_transmission(); }
+        if (active_surface) { BSDF bsdf(sc, si); tr_multiplier *= bsdf.eval_null_transmission(); }
         if (ADJ) {
             bool do_adj = active_medium && sc.media[medium].m.kind == LR_MEDIUM_HETEROGENEOUS;
             float gsum = 0.f;
@@ -184,7 +184,7 @@ LR_DEV LaneResult sample_prb(const DScene &sc, const DTri *tris_gid, Sampler &sm
         active_surface &= si_valid(si);
         {   // NEE (:259-291)
             bool active_e_surface = false;
-            if (active_surface) { BSDF b(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv); active_e_surface = (b.flags() & F_SMOOTH) && (depth + 1 < sc.max_depth); }
+            if (active_surface) { BSDF b(sc, si); active_e_surface = (b.flags() & F_SMOOTH) && (depth + 1 < sc.max_depth); }
             bool sample_emitters = act_medium_scatter ? sc.media[mei.medium].m.sample_emitters != 0 : false;
             if (act_medium_scatter) specular_chain = !sample_emitters;
             bool active_e_medium = act_medium_scatter && sample_emitters;
@@ -193,7 +193,7 @@ LR_DEV LaneResult sample_prb(const DScene &sc, const DTri *tris_gid, Sampler &sm
                 V3 rp = active_e_medium ? mei.p : si.p, rn = active_e_medium ? mk3(0.f) : si.n;
                 V3 emitted = sample_emitter_prb<false>(sc, tris_gid, rp, rn, active_e_surface ? &si : nullptr, smp, medium, channel, ds, mk3(0.f), mk3(0.f), cnt);
                 V3 nee_weight; float nee_pdf;
-                if (active_e_surface) { BSDF b(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv); nee_weight = b.eval_pdf(si.wi, si.sh.to_local(ds.d), nee_pdf); }
+                if (active_e_surface) { BSDF b(sc, si); nee_weight = b.eval_pdf(si.wi, si.sh.to_local(ds.d), nee_pdf); }
                 else { float pv = phase.eval_pdf(mei.wi, ds.d); nee_weight = mk3(pv); nee_pdf = pv; }
                 V3 contrib = throughput * nee_weight * mis_weight(ds.pdf, ds.delta ? 0.f : nee_pdf) * emitted;
                 L += contrib * sgn;
@@ -208,7 +208,7 @@ LR_DEV LaneResult sample_prb(const DScene &sc, const DTri *tris_gid, Sampler &sm
             if (act_medium_scatter) { ray.o = mei.p; ray.d = wo; ray.maxt = LR_LARGEST; needs_intersection = true; last_scatter_direction_pdf = phase_pdf; }
         }
         if (active_surface) {
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+            BSDF bsdf(sc, si);
             float s1 = smp.next_1d(); V2 s2 = smp.next_2d();
             V3 bsdf_weight; BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_weight);
             active_surface &= bs.pdf > 0.f;

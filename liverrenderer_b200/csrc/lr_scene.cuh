@@ -31,6 +31,9 @@ struct DGrid {
 
 struct DMedium { lr_medium m; float max_density; };
 
+// `bitmap` texture (src/textures/bitmap.cpp); row-major [h][w][ch] floats in HBM
+struct DTex { const float *data; int w, h, ch; uint32_t filter, wrap; float to_uv[6]; };
+
 struct DEmitter {
     lr_emitter e;                     // host pointers inside are NOT valid on the device
     const float *pixels;              // envmap (W+1) x H x 3 with the duplicated column
@@ -48,6 +51,8 @@ struct DEmitter {
 // so every field is a uniform constant-bank load.
 struct DScene {
     const DNode *nodes; const DTri *tris; const DMesh *meshes;
+    const DTri *tris_gid;             // triangles by global primitive id (tris is in BVH order)
+    const DTex *textures;
     const lr_bsdf *bsdfs; const DMedium *media; const DGrid *grids; const DEmitter *emitters;
     uint32_t n_tris, n_meshes, n_emitters; int env;
     V3 bs_center; float bs_radius;

@@ -457,7 +457,7 @@ __global__ void __launch_bounds__(128, 2 * LR_WF_OCC) k_wf_shade_a_surface(const
             if (!si_valid(si)) {                                   // escaped to the environment: the path ends here
                 dead = true; f |= WF_DEAD; wf_finish<C, TO_FILM>(sc, a, *S, result, f);
             } else {
-                BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+                BSDF bsdf(sc, si);
                 if ((bsdf.flags() & F_SMOOTH) && (depth + 1 < sc.max_depth)) {                                           // :350-362
                     DirectionSample ds;
                     if (wf_nee_setup(sc, a, S, smp, si.p, si.n, &si, medium, ds, cnt)) {
@@ -555,7 +555,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_nee(const __grid_constant
                     SurfaceInteraction si;
                     if (active_surface) {
                         h.t = si_t; si = compute_si(sc, ray, h, a.tris_gid);
-                        BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+                        BSDF bsdf(sc, si);
                         transmittance *= bsdf.eval_null_transmission();
                         Ray r2 = spawn_ray(si.p, si.n, ray.d); ray.o = r2.o;
                     }
@@ -616,7 +616,7 @@ __global__ void __launch_bounds__(128, 2 * LR_WF_OCC) k_wf_shade_b_surface(const
                 float4 o = S->o_maxt, d = S->d_eta, t = S->thr_lpdf;
                 Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
                 SurfaceInteraction si = compute_si(sc, ray, wf_hit(S->hit), a.tris_gid);
-                BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+                BSDF bsdf(sc, si);
                 float s1 = smp.next_1d(); V2 s2 = smp.next_2d();
                 V3 bsdf_val; BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_val);
                 V3 thr = mk3(t.x, t.y, t.z) * bsdf_val; float eta = d.w * bs.eta, lpdf = t.w;

@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(128, 2 * LR_WFP_OCC) k_wfp_shade_a_surface(con
             if (!si_valid(si) || !(depth < sc.max_depth)) {
                 dead = true; f |= WF_DEAD; if (!ADJ) wf_finish<C, TO_FILM>(sc, a, *S, L, f);
             } else {
-                BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+                BSDF bsdf(sc, si);
                 if ((bsdf.flags() & F_SMOOTH) && (depth + 1 < sc.max_depth)) {
                     DirectionSample ds;
                     if (wfp_nee_setup(sc, a, S, smp, si.p, si.n, &si, medium, ds, cnt)) {
@@ -363,7 +363,7 @@ LR_DEV V3 wfp_nee_walk(const DScene &sc, const WFArgs &a, const WState *S, Sampl
         SurfaceInteraction si;
         if (active_surface) {
             h.t = si_t; si = compute_si(sc, ray, h, a.tris_gid);
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv); tr_multiplier *= bsdf.eval_null_transmission();
+            BSDF bsdf(sc, si); tr_multiplier *= bsdf.eval_null_transmission();
         }
         transmittance *= tr_multiplier;
         if (active_surface) { Ray r2 = spawn_ray(si.p, si.n, ray.d); ray.o = r2.o; }
@@ -445,7 +445,7 @@ __global__ void __launch_bounds__(128, 2 * LR_WFP_OCC) k_wfp_shade_b_surface(con
                 float4 o = S->o_maxt, d = S->d_eta, t = S->thr_lpdf;
                 Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
                 SurfaceInteraction si = compute_si(sc, ray, wf_hit(S->hit), a.tris_gid);
-                BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+                BSDF bsdf(sc, si);
                 float s1 = smp.next_1d(); V2 s2 = smp.next_2d();
                 V3 bsdf_weight; BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_weight);
                 S->rng_state = smp.state; S->rng_inc = smp.inc;

@@ -15,6 +15,7 @@ from . import _capi as K
 from . import shapes as S
 from .transforms import ScalarTransform4f, parse_fov, perspective_projection
 from .volume_io import read_vol
+from .image_io import read_texture, texture_from_pixels
 
 
 def _rgb(v, default=None):
@@ -59,6 +60,16 @@ def _xf(d, key="to_world"):
     return ScalarTransform4f(np.asarray(t, dtype=np.float64))
 
 
+def _uv6(d, key="to_uv"):
+    """`to_uv` as a 2x3 affine: a 3x3 (ScalarTransform3f) or a 4x4 (ScalarTransform4f, z ignored) matrix."""
+    t = d.get(key)
+    if t is not None and not isinstance(t, ScalarTransform4f) and np.asarray(t).shape == (3, 3):
+        m = np.asarray(t, dtype=np.float64)
+        return (C.c_float * 6)(m[0, 0], m[0, 1], m[0, 2], m[1, 0], m[1, 1], m[1, 2])
+    m = _xf(d, key).matrix
+    return (C.c_float * 6)(m[0, 0], m[0, 1], m[0, 3], m[1, 0], m[1, 1], m[1, 3])
+
+
 _IOR = {"vacuum": 1.0, "air": 1.000277, "water": 1.3330, "bk7": 1.5046, "diamond": 2.419, "glass": 1.5046}
 
 
@@ -89,6 +100,7 @@ class Scene:
         self.base_dir = base_dir
         self._keep = []                       # numpy buffers referenced by the POD
         self.meshes, self.bsdfs, self.media, self.grids, self.emitters = [], [], [], [], []
+        self.textures = []
         self._bsdf_ids, self._medium_ids = {}, {}
         self.grid_arrays = []                 # numpy views of grid data, index-aligned with self.grids
         self.param_keys = {}                  # 'shape.interior_medium.sigma_t.data' -> grid index
@@ -98,7 +110,7 @@ class Scene:
         # first pass: named BSDFs / media so that {'type':'ref','id':...} resolves
         for name, v in self._named.items():
             t = v.get("type")
-            if t in ("diffuse", "roughdielectric", "principled", "null", "dielectric"):
+            if t in ("diffuse", "roughdielectric", "principled", "null", "dielectric", "bumpmap"):
                 self._bsdf_ids[name] = self._add_bsdf(v)
             elif t in ("homogeneous", "heterogeneous"):
                 self._medium_ids[name] = self._add_medium(v, name)
@@ -126,7 +138,59 @@ class Scene:
             return self._bsdf_ids[v["id"]]
         return self._add_bsdf(v)
 
+    def _add_texture(self, v) -> int:
+        """`bitmap` texture (src/textures/bitmap.cpp:172-290) -> texture slot (1 + index)."""
+        if v.get("type") != "bitmap":
+            raise NotImplementedError(f"texture plugin '{v.get('type')}' is outside the hot path")
+        raw = bool(v.get("raw", False))
+        if "filename" in v:
+            px = read_texture(os.path.join(self.base_dir, v["filename"]), raw)
+        elif "data" in v:                                      # tensor input is used as is (:236-262)
+            px = np.ascontiguousarray(np.asarray(v["data"], dtype=np.float32))
+            if px.ndim != 3:
+                raise RuntimeError(f"Bitmap raw tensor has dimension {px.ndim}, expected 3")
+        elif "bitmap" in v:
+            px = texture_from_pixels(np.asarray(v["bitmap"]), raw)
+        else:
+            raise RuntimeError('bitmap: one of "filename", "data" or "bitmap" must be given')
+        if px.shape[2] not in (1, 3):
+            raise RuntimeError("bitmap: only textures with 1 or 3 channels are supported!")
+        if px.shape[0] < 2 or px.shape[1] < 2:
+            raise RuntimeError("bitmap: image must be at least 2x2 pixels in size")
+        t = K.lr_texture(); self._keep.append(px)
+        t.data = px.ctypes.data_as(K.c_float_p); t.height, t.width, t.channels = px.shape
+        ft = str(v.get("filter_type", "bilinear")).lower()
+        if ft not in ("bilinear", "nearest"):
+            raise RuntimeError(f'Invalid filter type "{ft}", must be one of: "nearest", or "bilinear"!')
+        t.filter = K.TEX_BILINEAR if ft == "bilinear" else K.TEX_NEAREST
+        wm = str(v.get("wrap_mode", "repeat")).lower()
+        if wm not in ("repeat", "mirror", "clamp"):
+            raise RuntimeError(f'Invalid wrap mode "{wm}", must be one of: "repeat", "mirror", or "clamp"!')
+        t.wrap = {"repeat": K.WRAP_REPEAT, "mirror": K.WRAP_MIRROR, "clamp": K.WRAP_CLAMP}[wm]
+        t.to_uv = _uv6(v)
+        self.textures.append(t)
+        return len(self.textures)
+
     def _add_bsdf(self, v):
+        if v["type"] == "bumpmap":                             # src/bsdfs/bumpmap.cpp:101-127
+            nested = [x for x in v.values() if isinstance(x, dict) and x.get("type") in
+                      ("diffuse", "roughdielectric", "principled", "null", "dielectric", "ref", "bumpmap")]
+            texs = [x for x in v.values() if isinstance(x, dict) and x.get("type") in ("bitmap", "checkerboard")]
+            if len(nested) != 1:
+                raise RuntimeError("Exactly one BSDF child object must be specified." if not nested
+                                   else "Only a single BSDF child object can be specified.")
+            if len(texs) != 1:
+                raise RuntimeError("Exactly one Texture child object must be specified." if not texs
+                                   else "Only a single Texture child object can be specified.")
+            if nested[0]["type"] == "bumpmap":
+                raise NotImplementedError("nested bumpmap BSDFs are outside the hot path")
+            src = self.bsdfs[self._resolve_bsdf(nested[0])]
+            b = K.lr_bsdf.from_buffer_copy(src)
+            b.bump_tex = self._add_texture(texs[0]); b.bump_scale = _flt(v.get("scale"), 1.0)
+            b.bump_flags = (K.BUMP_FLIP_INVALID_NORMALS if v.get("flip_invalid_normals", True) else 0) | \
+                           (K.BUMP_SHADOWING_FUNCTION if v.get("use_shadowing_function", True) else 0)
+            self.bsdfs.append(b)
+            return len(self.bsdfs) - 1
         b = K.lr_bsdf(); t = v["type"]
         b.sample_visible = 1; b.eta = 1.0
         b.reflectance = _f3([1, 1, 1]); b.transmittance = _f3([1, 1, 1])
@@ -138,6 +202,8 @@ class Scene:
                 b.reflectance = _f3(_rgb(r.get("color0"), 0.4)); b.tex_color1 = _f3(_rgb(r.get("color1"), 0.2))
                 m = _xf(r, "to_uv").matrix
                 b.tex_to_uv = (C.c_float * 6)(m[0, 0], m[0, 1], m[0, 3], m[1, 0], m[1, 1], m[1, 3])
+            elif isinstance(r, dict) and r.get("type") == "bitmap":         # src/textures/bitmap.cpp
+                b.tex_kind = 2; b.refl_tex = self._add_texture(r)
             else:
                 b.reflectance = _f3(_rgb(r, 0.5))
         elif t == "null":
@@ -386,11 +452,12 @@ class Scene:
 
     # ---- POD ---------------------------------------------------------------------
     def pod(self) -> K.lr_scene:
-        sc = K.lr_scene(); sc.api_version = 1
+        sc = K.lr_scene(); sc.api_version = K.LR_API_VERSION
         def arr(T, lst):
             a = (T * max(len(lst), 1))(*lst); self._keep.append(a); return a
         sc.n_meshes, sc.n_bsdfs, sc.n_media = len(self.meshes), len(self.bsdfs), len(self.media)
-        sc.n_grids, sc.n_emitters = len(self.grids), len(self.emitters)
+        sc.n_grids, sc.n_emitters, sc.n_textures = len(self.grids), len(self.emitters), len(self.textures)
+        sc.textures = arr(K.lr_texture, self.textures)
         sc.meshes = arr(K.lr_mesh, self.meshes); sc.bsdfs = arr(K.lr_bsdf, self.bsdfs); sc.media = arr(K.lr_medium, self.media)
         sc.grids = arr(K.lr_grid, self.grids); sc.emitters = arr(K.lr_emitter, self.emitters)
         sc.sensor = self.sensor; sc.integrator = self.integrator

@@ -28,6 +28,20 @@ def sigmat_field(res: int) -> np.ndarray:
     return np.ascontiguousarray(f[..., None], dtype=np.float32)
 
 
+def tissue_texture(res: int = 512, seed: int = 7) -> np.ndarray:
+    """Synthetic stand-in for the fork's `tissue_n.png` bump texture (scenes/Liver-SingleMesh/mitsuba3/scene.xml:31-35):
+    a tileable band-limited RGB field in [0, 1], [res][res][3] fp32 (used `raw`)."""
+    rng = np.random.default_rng(seed); c = np.arange(res, dtype=np.float64) / res
+    y, x = np.meshgrid(c, c, indexing="ij"); out = np.zeros((res, res, 3))
+    for ch in range(3):
+        f = np.zeros((res, res))
+        for _ in range(24):
+            kx, ky = rng.integers(1, 24, size=2) * rng.choice([-1, 1], size=2); amp = 1.0 / np.hypot(kx, ky)
+            f += amp * np.sin(2 * np.pi * (kx * x + ky * y) + rng.uniform(0, 2 * np.pi))
+        out[..., ch] = (f - f.min()) / (f.max() - f.min())
+    return np.ascontiguousarray(out, dtype=np.float32)
+
+
 def _liver_mesh(name: str):
     z = np.load(os.path.join(_DATA, "liver_meshes.npz"))
     return {"type": "mesh", "positions": z[f"{name}_positions"], "indices": z[f"{name}_indices"],
@@ -88,12 +102,20 @@ def _liver_env():
 
 
 def liver_single_mesh(res: int = 1080, spp: int = 1024, grid_res: int = 256, phase: str = "isotropic",
-                      tracking: str = "reference", max_depth: int = 12):
-    """C3: Liver-SingleMesh restated with volpath + heterogeneous gridvolume."""
+                      tracking: str = "reference", max_depth: int = 12, surface: str = "roughdielectric"):
+    """C3: Liver-SingleMesh restated with volpath + heterogeneous gridvolume.
+    `surface="bumpmap"` keeps the fork's own boundary instead of the SURVEY substitute: `bumpmap` (scale 0.005,
+    bitmap texture) over a smooth `dielectric` 1.38 (scene.xml:31-40), with a synthetic tissue texture."""
     mesh = _liver_mesh("liver2"); mesh["to_world"] = _LIVER_T
     pos = _LIVER_T.transform_affine(mesh["positions"].astype(np.float64))
     bmin, bmax = pos.min(0), pos.max(0)
     mesh["bsdf"] = {"type": "roughdielectric", "int_ior": 1.38, "ext_ior": 1.0, "alpha": 0.1, "distribution": "beckmann"}
+    if surface == "bumpmap":
+        mesh["bsdf"] = {"type": "bumpmap", "scale": 0.005,
+                        "texture": {"type": "bitmap", "bitmap": tissue_texture(), "raw": True},
+                        "bsdf": {"type": "dielectric", "int_ior": 1.38, "ext_ior": 1.0}}
+    elif surface != "roughdielectric":
+        raise ValueError(f"unknown surface '{surface}'")
     mesh["interior"] = {"type": "heterogeneous", "scale": 0.4,
                         "sigma_t": {"type": "gridvolume", "grid": sigmat_field(grid_res), "to_world": _grid_to_world(bmin, bmax)},
                         "albedo": {"type": "rgb", "value": [0.92, 0.45, 0.35]},

@@ -28,11 +28,18 @@ struct OrcScene {
 
 static std::string g_err;
 
+static Texture2D make_texture(const lr_texture &t) {
+    Texture2D x; x.w = (int) t.width; x.h = (int) t.height; x.ch = (int) t.channels; x.filter = t.filter; x.wrap = t.wrap;
+    memcpy(x.to_uv, t.to_uv, sizeof x.to_uv); x.data.assign(t.data, t.data + (size_t) t.width * t.height * t.channels);
+    return x;
+}
+
 static void build_scene(OrcScene &o, const lr_scene *s) {
     Scene &sc = o.sc;
     sc.sensor = s->sensor; sc.integ = s->integrator;
     memcpy(sc.cam_to_world.m, s->sensor.to_world, 64); memcpy(sc.sample_to_camera.m, s->sensor.sample_to_camera, 64);
     sc.bsdfs.assign(s->bsdfs, s->bsdfs + s->n_bsdfs);
+    for (uint32_t i = 0; i < s->n_textures; ++i) sc.textures.push_back(make_texture(s->textures[i]));
     V3 lo(Inf), hi(-Inf);
     for (uint32_t i = 0; i < s->n_meshes; ++i) {
         const lr_mesh &m = s->meshes[i]; Mesh me;
@@ -261,6 +268,23 @@ void orc_kat_bsdf_eval_pdf(const lr_bsdf *b, const float *wi, const float *wo, f
 uint32_t orc_kat_bsdf_sample(const lr_bsdf *b, const float *wi, float s1, float s2x, float s2y, float *out) {
     BSDF bs(*b); V3 w; BSDFSample r = bs.sample(V3(wi[0], wi[1], wi[2]), s1, {s2x, s2y}, w);
     out[0] = r.wo.x; out[1] = r.wo.y; out[2] = r.wo.z; out[3] = r.pdf; out[4] = r.eta; out[5] = w.x; out[6] = w.y; out[7] = w.z; return r.sampled_type;
+}
+/* bitmap texture probes: out[6] = eval rgb(3), eval_1, eval_1_grad(2) at each of the n uv pairs */
+void orc_kat_texture(const lr_texture *t, int n, const float *uv, float *out) {
+    Texture2D x = make_texture(*t);
+    for (int i = 0; i < n; ++i) {
+        V2 p{uv[2 * i], uv[2 * i + 1]}; V3 c = x.eval(p); V2 g = x.eval_1_grad(p);
+        out[6 * i] = c.x; out[6 * i + 1] = c.y; out[6 * i + 2] = c.z; out[6 * i + 3] = x.eval_1(p); out[6 * i + 4] = g.x; out[6 * i + 5] = g.y;
+    }
+}
+/* bumpmap: frame (n, s, t; 9 floats) perturbed by texture `t` for a synthetic interaction:
+   si = {n, sh.n, sh.s (t = n x s), dp_du, dp_dv, wi (local), uv}, 20 floats */
+void orc_kat_bump_frame(const lr_bsdf *b, const lr_texture *t, const float *sif, float *out9) {
+    Texture2D x = make_texture(*t); SurfaceInteraction si;
+    si.n = V3(sif[0], sif[1], sif[2]); si.sh.n = V3(sif[3], sif[4], sif[5]); si.sh.s = V3(sif[6], sif[7], sif[8]); si.sh.t = cross(si.sh.n, si.sh.s);
+    si.dp_du = V3(sif[9], sif[10], sif[11]); si.dp_dv = V3(sif[12], sif[13], sif[14]); si.wi = V3(sif[15], sif[16], sif[17]); si.uv = {sif[18], sif[19]};
+    Frame f = BSDF::bump_frame(x, *b, si);
+    out9[0] = f.n.x; out9[1] = f.n.y; out9[2] = f.n.z; out9[3] = f.s.x; out9[4] = f.s.y; out9[5] = f.s.z; out9[6] = f.t.x; out9[7] = f.t.y; out9[8] = f.t.z;
 }
 /* out[4] = wo(3), pdf */
 void orc_kat_phase_sample(uint32_t kind, float g, const float *wi, float u1, float u2, float *out) {

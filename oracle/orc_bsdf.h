@@ -197,8 +197,64 @@ inline V3 lerp3(V3 a, V3 b, float t) { return {lerp(a.x, b.x, t), lerp(a.y, b.y,
 /* ---- BSDF dispatch --------------------------------------------------------- */
 struct BSDF {
     const lr_bsdf &b; V2 uv;
+    const Scene *scene = nullptr;
+    bool bump = false; Frame pf;        /* bumpmap: perturbed frame, relative to the original shading frame */
     explicit BSDF(const lr_bsdf &b_, V2 uv_ = {0.f, 0.f}) : b(b_), uv(uv_) {}
+    /* the constructor the integrators use: resolves texture slots and the bump-mapped frame */
+    BSDF(const Scene &sc, const SurfaceInteraction &si) : b(sc.bsdfs[sc.meshes[si.mesh].bsdf]), uv(si.uv), scene(&sc) {
+        if (b.bump_tex) { bump = true; pf = bump_frame(sc.textures[b.bump_tex - 1], b, si); }
+    }
+    /* BumpMap::frame (src/bsdfs/bumpmap.cpp:248-276) */
+    static Frame bump_frame(const Texture2D &tex, const lr_bsdf &b, const SurfaceInteraction &si) {
+        V2 g = tex.eval_1_grad(si.uv); g.x *= b.bump_scale; g.y *= b.bump_scale;
+        V3 dp_du = fma3(si.sh.n, g.x - dot(si.sh.n, si.dp_du), si.dp_du);
+        V3 dp_dv = fma3(si.sh.n, g.y - dot(si.sh.n, si.dp_dv), si.dp_dv);
+        Frame r;
+        r.n = normalize(cross(dp_du, dp_dv));
+        if (dot(si.n, r.n) < 0.f) r.n = -r.n;
+        r.n = si.to_local(r.n);
+        if (b.bump_flags & LR_BUMP_FLIP_INVALID_NORMALS) {
+            if (si.wi.z * dot(si.wi, r.n) <= 0.f) r.n = V3(-r.n.x, -r.n.y, r.n.z);
+        }
+        /* Gram-Schmidt against the (world-space) dp_du, exactly as the reference writes it */
+        r.s = normalize(fma3(r.n, -dot(r.n, si.dp_du), si.dp_du));
+        r.t = cross(r.n, r.s);
+        return r;
+    }
+    /* eval_shadow_terminator (src/bsdfs/normalmap_helpers.h:20-25; Frame::tan_theta_2, frame.h:80-83) */
+    static float tan_theta_2(V3 v) { float t = fmaf(-v.z, v.z, 1.f); return std::max(t, 0.f) / sqr(v.z); }
+    float shadow_terminator(V3 wo) const {
+        float alpha2 = std::min(0.125f * tan_theta_2(pf.n), 1.f);
+        return 2.f / (1.f + sqrtf(1.f + alpha2 * tan_theta_2(wo)));
+    }
+    /* BumpMap::sample / eval / pdf (bumpmap.cpp:136-201): nested BSDF in the perturbed frame */
+    BSDFSample sample(V3 wi, float s1, V2 s2, V3 &weight) const {
+        if (!bump) return sample_n(wi, s1, s2, weight);
+        BSDFSample bs = sample_n(pf.to_local(wi), s1, s2, weight);
+        bool active = weight.x != 0.f || weight.y != 0.f || weight.z != 0.f;
+        V3 pwo = pf.to_world(bs.wo);
+        active &= bs.wo.z * pwo.z > 0.f;
+        bs.wo = pwo;
+        if (b.bump_flags & LR_BUMP_SHADOWING_FUNCTION) weight = weight * shadow_terminator(bs.wo);
+        if (!active) weight = V3(0.f);
+        return bs;
+    }
+    V3 eval(V3 wi, V3 wo) const {
+        if (!bump) return eval_n(wi, wo);
+        V3 pwo = pf.to_local(wo);
+        if (!(wo.z * pwo.z > 0.f)) return V3(0.f);
+        V3 v = eval_n(pf.to_local(wi), pwo);
+        if (b.bump_flags & LR_BUMP_SHADOWING_FUNCTION) v = v * shadow_terminator(wo);
+        return v;
+    }
+    float pdf(V3 wi, V3 wo) const {
+        if (!bump) return pdf_n(wi, wo);
+        V3 pwo = pf.to_local(wo);
+        if (!(wo.z * pwo.z > 0.f)) return 0.f;
+        return pdf_n(pf.to_local(wi), pwo);
+    }
     V3 refl() const {
+        if (b.tex_kind == 2 && scene) return scene->textures[b.refl_tex - 1].eval(uv);   /* bitmap reflectance */
         if (b.tex_kind == 1) {                      /* checkerboard (src/textures/checkerboard.cpp:70-89) */
             float u = fmaf(b.tex_to_uv[0], uv.x, fmaf(b.tex_to_uv[1], uv.y, b.tex_to_uv[2])),
                   v = fmaf(b.tex_to_uv[3], uv.x, fmaf(b.tex_to_uv[4], uv.y, b.tex_to_uv[5]));
@@ -224,7 +280,7 @@ struct BSDF {
     float eval_null_transmission() const { return b.kind == LR_BSDF_NULL ? 1.f : 0.f; }
 
     /* ---------------- sample ---------------- */
-    BSDFSample sample(V3 wi, float s1, V2 s2, V3 &weight) const {
+    BSDFSample sample_n(V3 wi, float s1, V2 s2, V3 &weight) const {
         BSDFSample bs; weight = V3(0.f);
         switch (b.kind) {
         case LR_BSDF_DIFFUSE: {                     /* src/bsdfs/diffuse.cpp:100-123 */
@@ -275,7 +331,7 @@ struct BSDF {
     }
 
     /* ---------------- eval / pdf ---------------- */
-    V3 eval(V3 wi, V3 wo) const {
+    V3 eval_n(V3 wi, V3 wo) const {
         switch (b.kind) {
         case LR_BSDF_DIFFUSE: {                     /* diffuse.cpp:125-141 */
             if (!(wi.z > 0.f && wo.z > 0.f)) return V3(0.f);
@@ -298,7 +354,7 @@ struct BSDF {
         default: return V3(0.f);
         }
     }
-    float pdf(V3 wi, V3 wo) const {
+    float pdf_n(V3 wi, V3 wo) const {
         switch (b.kind) {
         case LR_BSDF_DIFFUSE: return (wi.z > 0.f && wo.z > 0.f) ? square_to_cosine_hemisphere_pdf(wo) : 0.f;
         case LR_BSDF_ROUGHDIELECTRIC: {             /* roughdielectric.cpp:436-499 */

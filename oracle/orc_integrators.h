@@ -76,7 +76,7 @@ struct Integrator {
             }
             bool active_next = (depth + 1 < max_depth) && si.is_valid();       /* :227 */
             if (!si.is_valid()) break;      /* JIT: masked lane, no further side effects */
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+            BSDF bsdf(sc, si);
             bool active_em = active_next && (bsdf.flags() & F_SMOOTH);
             DirectionSample ds; V3 em_weight(0.f), wo(0.f);
             V2 u_em = smp.next_2d();                                         /* :247-248, drawn by every loop-active lane */

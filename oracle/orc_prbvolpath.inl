@@ -69,7 +69,7 @@ V3 sample_emitter_prb(const Interaction &ref, const SurfaceInteraction *ref_si, 
         }
         active_surface |= escaped_medium;
         active_surface &= si.is_valid() && !active_medium;
-        if (active_surface) { BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv); tr_multiplier *= bsdf.eval_null_transmission(); }
+        if (active_surface) { BSDF bsdf(sc, si); tr_multiplier *= bsdf.eval_null_transmission(); }
         if (adj && active_medium && sc.media[medium].m.kind == LR_MEDIUM_HETEROGENEOUS) {
             /* d tr_multiplier_c / d grid = -scale / majorant_c ; backward(tr_mult * dL*adj/tr_mult) */
             const Medium &m = sc.media[medium]; double g = 0.0;
@@ -181,7 +181,7 @@ LaneResult sample_prb(bool primal, Sampler &smp, Ray ray, V3 dL, V3 state_in) {
         /* ---- NEE (:259-291) ---- */
         {
             bool active_e_surface = false;
-            if (active_surface) { BSDF b(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv); active_e_surface = (b.flags() & F_SMOOTH) && (depth + 1 < max_depth); }
+            if (active_surface) { BSDF b(sc, si); active_e_surface = (b.flags() & F_SMOOTH) && (depth + 1 < max_depth); }
             bool sample_emitters = act_medium_scatter ? sc.media[mei.medium].m.sample_emitters != 0 : false;
             if (act_medium_scatter) { specular_chain = false; specular_chain |= !sample_emitters; }
             bool active_e_medium = act_medium_scatter && sample_emitters;
@@ -191,7 +191,7 @@ LaneResult sample_prb(bool primal, Sampler &smp, Ray ray, V3 dL, V3 state_in) {
                 const Interaction &ref = active_e_medium ? (const Interaction &) mei : (const Interaction &) si;
                 V3 emitted = sample_emitter_prb(ref, active_e_surface ? &si : nullptr, smp, medium, channel, ds, nullptr, V3(0.f));
                 V3 nee_weight; float nee_pdf;
-                if (active_e_surface) { BSDF b(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv); V3 wo = si.to_local(ds.d); nee_weight = b.eval(si.wi, wo); nee_pdf = b.pdf(si.wi, wo); }
+                if (active_e_surface) { BSDF b(sc, si); V3 wo = si.to_local(ds.d); nee_weight = b.eval(si.wi, wo); nee_pdf = b.pdf(si.wi, wo); }
                 else { float pv = phase.eval_pdf(mei.wi, ds.d); nee_weight = V3(pv); nee_pdf = pv; }
                 V3 contrib = throughput * nee_weight * mis_weight(ds.pdf, ds.delta ? 0.f : nee_pdf) * emitted;
                 L += contrib * sgn;
@@ -208,7 +208,7 @@ LaneResult sample_prb(bool primal, Sampler &smp, Ray ray, V3 dL, V3 state_in) {
         }
         /* ---- BSDF sampling (:318-349) ---- */
         if (active_surface) {
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+            BSDF bsdf(sc, si);
             float s1 = smp.next_1d(); V2 s2 = smp.next_2d();
             V3 bsdf_weight; BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_weight);
             active_surface &= bs.pdf > 0.f;

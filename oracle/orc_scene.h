@@ -144,7 +144,7 @@ struct Grid {
     int wrap_i(int p, int r) const {
         if (wrap == LR_WRAP_CLAMP) return std::min(std::max(p, 0), r - 1);
         /* texture.h:1369-1395 (repeat / mirror) */
-        int sh = p < 0 ? p + 1 : p; int div = sh / r; if (p < 0) div -= 1;
+        int sh = p < 0 ? p + 1 : p; int div = sh / r;
         int mod = p - div * r; if (mod < 0) mod += r;
         if (wrap == LR_WRAP_MIRROR) { bool keep = ((div & 1) == 0) != (p < 0); if (!keep) mod = r - 1 - mod; }
         return mod;
@@ -182,6 +182,65 @@ struct Grid {
     void recompute_max() { maxv = 0.f; for (float v : data) maxv = std::max(maxv, v); }
 };
 
+/* `bitmap` texture (src/textures/bitmap.cpp) on dr::Texture<Float,2>::eval_nonaccel /
+   eval_fetch_nonaccel (ext/drjit/include/drjit/texture.h:484-556,704-735; wrap :1369-1396) */
+struct Texture2D {
+    std::vector<float> data; int w = 0, h = 0, ch = 1; uint32_t filter = 0, wrap = 0; float to_uv[6] = {1, 0, 0, 0, 1, 0};
+    static float lum(const float *c) { return c[0] * 0.212671f + c[1] * 0.715160f + c[2] * 0.072169f; }
+    int wrap_i(int p, int r) const {
+        if (wrap == LR_WRAP_CLAMP) return std::min(std::max(p, 0), r - 1);
+        int sh = p < 0 ? p + 1 : p; int div = sh / r;
+        int mod = p - div * r; if (mod < 0) mod += r;
+        if (wrap == LR_WRAP_MIRROR) { bool keep = ((div & 1) == 0) != (p < 0); if (!keep) mod = r - 1 - mod; }
+        return mod;
+    }
+    /* m_transform * si.uv (AffineTransform3f on a Point2f: fmadd chain of Matrix * point) */
+    V2 xform(V2 uv) const {
+        return {fmaf(to_uv[0], uv.x, fmaf(to_uv[1], uv.y, to_uv[2])), fmaf(to_uv[3], uv.x, fmaf(to_uv[4], uv.y, to_uv[5]))};
+    }
+    /* the four bilinear taps (x-fastest order 00,10,01,11) and the fractional weights */
+    void fetch4(V2 uv, const float *tap[4], float &w1x, float &w1y) const {
+        float fx = fmaf(uv.x, (float) w, -.5f), fy = fmaf(uv.y, (float) h, -.5f);
+        int ix = (int) floorf(fx), iy = (int) floorf(fy);
+        w1x = fx - (float) ix; w1y = fy - (float) iy;
+        int x0 = wrap_i(ix, w), x1 = wrap_i(ix + 1, w), y0 = wrap_i(iy, h), y1 = wrap_i(iy + 1, h);
+        tap[0] = &data[((size_t) y0 * w + x0) * ch]; tap[1] = &data[((size_t) y0 * w + x1) * ch];
+        tap[2] = &data[((size_t) y1 * w + x0) * ch]; tap[3] = &data[((size_t) y1 * w + x1) * ch];
+    }
+    /* interpolate_1 / interpolate_3 (bitmap.cpp:781-813); `out` has `ch` entries */
+    void eval_raw(V2 uv_in, float *out) const {
+        V2 uv = xform(uv_in);
+        if (filter == LR_TEX_NEAREST) {
+            int ix = wrap_i((int) floorf(uv.x * (float) w), w), iy = wrap_i((int) floorf(uv.y * (float) h), h);
+            for (int c = 0; c < ch; ++c) out[c] = data[((size_t) iy * w + ix) * ch + c];
+            return;
+        }
+        const float *t[4]; float w1x, w1y; fetch4(uv, t, w1x, w1y);
+        float w0x = 1.f - w1x, w0y = 1.f - w1y;
+        const float wt[4] = {w0x * w0y, w1x * w0y, w0x * w1y, w1x * w1y};
+        for (int c = 0; c < ch; ++c) out[c] = 0.f;
+        for (int k = 0; k < 4; ++k) for (int c = 0; c < ch; ++c) out[c] = fmaf(t[k][c], wt[k], out[c]);
+    }
+    /* Texture::eval for *_rgb variants (bitmap.cpp:443-485) */
+    V3 eval(V2 uv) const { float o[3]; eval_raw(uv, o); return ch == 1 ? V3(o[0]) : V3(o[0], o[1], o[2]); }
+    /* eval_1 (:487-507) */
+    float eval_1(V2 uv) const { float o[3]; eval_raw(uv, o); return ch == 1 ? o[0] : lum(o); }
+    /* eval_1_grad (:509-578) */
+    V2 eval_1_grad(V2 uv_in) const {
+        if (filter != LR_TEX_BILINEAR) return {0.f, 0.f};
+        V2 uv = xform(uv_in);
+        const float *t[4]; float w1x, w1y; fetch4(uv, t, w1x, w1y);
+        float f00, f10, f01, f11;
+        if (ch == 1) { f00 = t[0][0]; f10 = t[1][0]; f01 = t[2][0]; f11 = t[3][0]; }
+        else { f00 = lum(t[0]); f10 = lum(t[1]); f01 = lum(t[2]); f11 = lum(t[3]); }
+        float w0x = 1.f - w1x, w0y = 1.f - w1y;
+        float dx = fmaf(w0y, f10 - f00, w1y * (f11 - f01)), dy = fmaf(w0x, f01 - f00, w1x * (f11 - f10));
+        /* transpose multiply by the uv transform, then scale by the resolution */
+        float du = to_uv[0] * dx + to_uv[3] * dy, dv = to_uv[1] * dx + to_uv[4] * dy;
+        return {(float) w * du, (float) h * dv};
+    }
+};
+
 struct Medium {
     lr_medium m; float max_density = 0.f;     /* heterogeneous: scale * sigma_t->max() (heterogeneous.cpp:163) */
 };
@@ -197,7 +256,7 @@ struct Emitter {
 
 struct Scene {
     std::vector<Mesh> meshes; std::vector<Tri> tris; BVH bvh;
-    std::vector<lr_bsdf> bsdfs; std::vector<Medium> media; std::vector<Grid> grids; std::vector<Emitter> emitters;
+    std::vector<lr_bsdf> bsdfs; std::vector<Texture2D> textures; std::vector<Medium> media; std::vector<Grid> grids; std::vector<Emitter> emitters;
     lr_sensor sensor; lr_integrator integ;
     int env = -1;                   /* index of the environment emitter */
     V3 bs_center; float bs_radius = 0.f;   /* scene bounding sphere (Scene bbox, src/render/scene.cpp) */

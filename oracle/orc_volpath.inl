@@ -61,7 +61,7 @@ V3 sample_emitter_vol(const Interaction &ref, const SurfaceInteraction *ref_si, 
         if (active_surface) total_dist += si.t;
         active_surface &= si.is_valid() && !active_medium;
         if (active_surface) {
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+            BSDF bsdf(sc, si);
             transmittance *= bsdf.eval_null_transmission();
         }
         if (active_surface) { Ray r2 = si.spawn_ray(ray.d); ray.o = r2.o; ray.d = r2.d; }
@@ -178,7 +178,7 @@ LaneResult sample_volpath(Sampler &smp, Ray ray, int initial_medium) {
         }
         active_surface &= si.is_valid();
         if (active_surface) {
-            BSDF bsdf(sc.bsdfs[sc.meshes[si.mesh].bsdf], si.uv);
+            BSDF bsdf(sc, si);
             bool active_e = (bsdf.flags() & F_SMOOTH) && (depth + 1 < max_depth);
             if (active_e) {                                                            /* :351-363 */
                 DirectionSample ds;

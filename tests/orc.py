@@ -49,6 +49,8 @@ def lib():
     L.orc_kat_ldsampler.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, vp]
     L.orc_kat_bsdf_eval_pdf.argtypes = [C.POINTER(K.lr_bsdf), vp, vp, vp, vp]
     L.orc_kat_bsdf_sample.argtypes = [C.POINTER(K.lr_bsdf), vp, C.c_float, C.c_float, C.c_float, vp]; L.orc_kat_bsdf_sample.restype = C.c_uint32
+    L.orc_kat_texture.argtypes = [C.POINTER(K.lr_texture), C.c_int, vp, vp]
+    L.orc_kat_bump_frame.argtypes = [C.POINTER(K.lr_bsdf), C.POINTER(K.lr_texture), vp, vp]
     L.orc_kat_phase_sample.argtypes = [C.c_uint32, C.c_float, vp, C.c_float, C.c_float, vp]
     L.orc_kat_phase_eval.argtypes = [C.c_uint32, C.c_float, vp, vp]; L.orc_kat_phase_eval.restype = C.c_float
     L.orc_kat_grid_eval.argtypes = [vp, C.c_uint32, vp, vp]
@@ -67,6 +69,18 @@ def _p(a):
 
 def f3(v):
     return np.ascontiguousarray(v, dtype=np.float32)
+
+
+def texture_probe(tex, uv):
+    """eval rgb(3), eval_1, eval_1_grad(2) of lr_texture `tex` at each uv pair -> [n, 6]."""
+    uv = np.ascontiguousarray(uv, dtype=np.float32).reshape(-1, 2); out = np.empty((uv.shape[0], 6), dtype=np.float32)
+    lib().orc_kat_texture(C.byref(tex), uv.shape[0], _p(uv), _p(out)); return out
+
+
+def bump_frame(bsdf, tex, n, sh_n, sh_s, dp_du, dp_dv, wi, uv):
+    """BumpMap::frame for a synthetic interaction -> rows n, s, t of the perturbed frame."""
+    si = np.concatenate([n, sh_n, sh_s, dp_du, dp_dv, wi, uv]).astype(np.float32); out = np.empty(9, dtype=np.float32)
+    lib().orc_kat_bump_frame(C.byref(bsdf), C.byref(tex), _p(si), _p(out)); return out.reshape(3, 3)
 
 
 class OracleScene:

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 24
     for n in names:
         assert hasattr(lib, n), f"liblr_b200.so does not export {n}"
-    assert lib.lr_api_version() == 1
+    assert lib.lr_api_version() == 2
 
 
 def test_no_torch_or_cxx_types_in_header():
@@ -41,7 +41,7 @@ def test_no_torch_or_cxx_types_in_header():
 
 def test_ctypes_struct_layout_matches_header():
     """Compile a tiny C program against include/lr_api.h that prints sizeof() of every POD struct."""
-    structs = ["lr_mesh", "lr_bsdf", "lr_grid", "lr_medium", "lr_emitter", "lr_sensor", "lr_integrator", "lr_scene", "lr_stats"]
+    structs = ["lr_mesh", "lr_bsdf", "lr_grid", "lr_medium", "lr_emitter", "lr_sensor", "lr_integrator", "lr_scene", "lr_stats", "lr_texture"]
     body = "".join(f'printf("{s} %zu\\n", sizeof({s}));' for s in structs)
     with tempfile.TemporaryDirectory() as td:
         c = os.path.join(td, "sz.c"); exe = os.path.join(td, "sz")

@@ -141,6 +141,19 @@ def test_grid_trilinear_vs_numpy():
         assert abs(_grid_eval(o, p)[0] - ref) < 2e-6
 
 
+@pytest.mark.parametrize("wrap", ["repeat", "mirror"])
+def test_grid_wrap_identities(wrap):
+    """dr::Texture::wrap (ext/drjit/include/drjit/texture.h:1369-1396): repeat is 1-periodic, mirror reflects about
+    0 and 1 (the same identities src/textures/tests/test_bitmap.py:55-125 checks for 2D textures)."""
+    rng = np.random.default_rng(5); g = rng.random((5, 6, 7)).astype(np.float32)
+    o = orc.OracleScene(_grid_scene(g, wrap))
+    for _ in range(60):
+        p = rng.random(3).astype(np.float32); ref = _grid_eval(o, p)[0]
+        others = [p - 1, p + 1, p + [1, -1, 2]] if wrap == "repeat" else [-p, 2 - p, p * [-1, 1, 1], [2 - p[0], -p[1], p[2]]]
+        for q in others:
+            assert abs(_grid_eval(o, np.asarray(q, dtype=np.float32))[0] - ref) < 2e-5, (p, q)
+
+
 # ---------------------------------------------------------------- BSDFs / phase functions
 def _bsdf_pod(d):
     sc = mi.load_dict({**mi.cornell_box(), "probe": {"type": "rectangle", "bsdf": d}})

@@ -10,6 +10,8 @@ Outputs
   tests/golden/participating_media.npz       the reference's own golden mean/variance images
                                              (resources/data/tests/scenes/participating_media/refs/*_ref_rgb{,_var}.exr)
                                              + their inputs (sigmat.vol, albedo.vol, meshes, museum.exr)
+  tests/golden/textures.npz                  decoded pixels of the images src/textures/tests/test_bitmap.py evaluates
+                                             (carrot.png, noise_02.png, noise_8x8.png; integer data as stored in the files)
 """
 import os
 import sys
@@ -43,6 +45,17 @@ def mesh_arrays(path):
     return d
 
 
+def make_textures():
+    tex = f"{REF}/resources/data/common/textures"; t = {}
+    for name in ("carrot", "noise_02", "noise_8x8"):
+        img = cv2.imread(f"{tex}/{name}.png", cv2.IMREAD_UNCHANGED)
+        if img.ndim == 3 and img.shape[2] >= 3:
+            img = np.concatenate([img[..., 2::-1], img[..., 3:]], axis=2)      # BGR(A) -> RGB(A)
+        t[name] = np.ascontiguousarray(img)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "textures.npz"), **t)
+    print("tests/golden/textures.npz", os.path.getsize(os.path.join(ROOT, "tests", "golden", "textures.npz")) // 1024, "KiB")
+
+
 def main():
     os.makedirs(os.path.join(ROOT, "liverrenderer_b200", "data"), exist_ok=True)
     os.makedirs(os.path.join(ROOT, "tests", "golden"), exist_ok=True)
@@ -74,6 +87,7 @@ def main():
             g[f"mesh_{mesh}_{k}"] = v
     g["museum"] = exr_rgb(f"{REF}/resources/data/common/textures/museum.exr")
     np.savez_compressed(os.path.join(ROOT, "tests", "golden", "participating_media.npz"), **g)
+    make_textures()
     for f in ("liverrenderer_b200/data/liver_meshes.npz", "liverrenderer_b200/data/cavity_env_256x128.npz",
               "tests/golden/participating_media.npz"):
         print(f, os.path.getsize(os.path.join(ROOT, f)) // 1024, "KiB")

@@ -21,10 +21,11 @@ from .transforms import ScalarTransform4f, T
 from .scene import Scene, load_dict
 from .backend import Context
 from .volume_io import read_vol, write_vol
+from .image_io import write_bitmap, read_texture
 from . import _capi
 
 __all__ = ["ScalarTransform4f", "T", "Scene", "load_dict", "load_file", "Context", "render", "render_backward",
-           "cornell_box", "traverse", "sample_tea_32", "read_vol", "write_vol", "variant", "set_variant"]
+           "cornell_box", "traverse", "sample_tea_32", "read_vol", "write_vol", "write_bitmap", "read_texture", "variant", "set_variant"]
 
 _variant = "cuda_b200_rgb"
 

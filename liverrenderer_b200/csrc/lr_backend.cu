@@ -2,6 +2,7 @@
 // (flatten -> HBM, LBVH build, envmap warp, majorants), kernel launches, film / gradient I/O.
 // sm_100a only; no CPU path: every entry point fails with LR_ERR_NO_DEVICE without a GPU.
 #include "lr_kernels.cuh"
+#include "lr_lanes.h"
 #include <cub/device/device_radix_sort.cuh>
 #include <vector>
 #include <string>

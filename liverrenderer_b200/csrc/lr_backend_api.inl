@@ -167,24 +167,9 @@ static PassPlan plan_passes(const lr_ctx *c, uint32_t spp) {
     return p;
 }
 
-template <typename K> static int grid_for(lr_ctx *c, K kernel, int block, int &grid) {
-    int per_sm = 0; LR_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0));
-    grid = std::max(per_sm, 1) * c->n_sm; return LR_OK;           // persistent: a whole number of CTAs per SM
-}
-
-template <int KIND, int C, bool TO_FILM> static int launch_render_t(lr_ctx *c, const RenderArgs &a) {
-    int grid; if (int r = grid_for(c, k_render<KIND, C, TO_FILM>, 128, grid)) return r;
-    uint64_t warps_needed = (a.lane_end - a.lane_begin + 31) / 32;
-    grid = (int) std::min<uint64_t>((uint64_t) grid, (warps_needed + 3) / 4); if (grid < 1) grid = 1;
-    k_render<KIND, C, TO_FILM><<<grid, 128, 0, c->stream>>>(c->sc, a);
-    LR_CUDA(c, cudaGetLastError()); return LR_OK;
-}
-template <int C, bool TO_FILM> static int launch_render_k(lr_ctx *c, const RenderArgs &a) {
-    switch (c->sc.integ.kind) {
-        case LR_INTEGRATOR_PATH: return launch_render_t<LR_INTEGRATOR_PATH, C, TO_FILM>(c, a);
-        case LR_INTEGRATOR_VOLPATH: return launch_render_t<LR_INTEGRATOR_VOLPATH, C, TO_FILM>(c, a);
-        default: return launch_render_t<LR_INTEGRATOR_PRBVOLPATH, C, TO_FILM>(c, a);
-    }
+// per-lane kernels (k_render / k_backward): compiled in lr_lanes.cu, launched through lr_lanes.h
+static int launch_render_lanes(lr_ctx *c, const RenderArgs &a, bool to_film) {
+    LR_CUDA(c, lanes_launch_render(c->film_channels, to_film, c->n_sm, c->stream, c->sc, a)); return LR_OK;
 }
 
 #include "lr_wavefront_host.inl"
@@ -234,8 +219,7 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
         if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false>(c, a) : wavefront_render_t<4, false>(c, a);
         return c->film_channels == 5 ? wavefront_render_t<5, true>(c, a) : wavefront_render_t<4, true>(c, a);
     }
-    if (lanes_out) return c->film_channels == 5 ? launch_render_k<5, false>(c, a) : launch_render_k<4, false>(c, a);
-    return c->film_channels == 5 ? launch_render_k<5, true>(c, a) : launch_render_k<4, true>(c, a);
+    return launch_render_lanes(c, a, lanes_out == nullptr);
 }
 
 static int copy_out(lr_ctx *c, void *dst, const void *src_dev, size_t bytes, int dst_is_device) {
@@ -325,9 +309,7 @@ int lr_render_backward(lr_ctx *c, uint32_t seed, uint32_t spp, const float *grad
     if (lane_end > lane_begin) {
         if (c->use_wavefront) { if (int r = wavefront_prb_backward(c, a, g, gc)) return r; }
         else {
-            int grid; if (int r = grid_for(c, k_backward, 128, grid)) return r;
-            k_backward<<<grid, 128, 0, c->stream>>>(c->sc, a);
-            LR_CUDA(c, cudaGetLastError());
+            LR_CUDA(c, lanes_launch_backward(c->n_sm, c->stream, c->sc, a));
         }
     }
     return end_call(c, 2, true);

@@ -183,7 +183,7 @@ LR_DEV void tex_fetch4(const DTex &t, V2 uv, const float *tap[4], float &w1x, fl
     tap[2] = t.data + ((size_t) y1 * t.w + x0) * t.ch; tap[3] = t.data + ((size_t) y1 * t.w + x1) * t.ch;
 }
 // Texture::eval for *_rgb variants (bitmap.cpp:443-485): 1 channel => grey
-__device__ __noinline__ V3 tex_eval(const DTex &t, V2 uv_in) {
+static __device__ __noinline__ V3 tex_eval(const DTex &t, V2 uv_in) {
     V2 uv = tex_xform(t, uv_in); float o[3] = {0.f, 0.f, 0.f};
     if (t.filter == LR_TEX_NEAREST) {
         int ix = tex_wrap((int) floorf(__fmul_rn(uv.x, (float) t.w)), t.w, t.wrap), iy = tex_wrap((int) floorf(__fmul_rn(uv.y, (float) t.h)), t.h, t.wrap);
@@ -262,8 +262,8 @@ LR_DEV float shadow_terminator(V3 pn, V3 wo) {
 }
 
 struct BumpSampleOut { BSDFSample bs; V3 weight; };
-__device__ __noinline__ BumpSampleOut bump_sample(const DScene &sc, const lr_bsdf &b, const BumpIn in, float s1, V2 s2);
-__device__ __noinline__ float4 bump_eval_pdf(const DScene &sc, const lr_bsdf &b, const BumpIn in, V3 wo);
+static __device__ __noinline__ BumpSampleOut bump_sample(const DScene &sc, const lr_bsdf &b, const BumpIn in, float s1, V2 s2);
+static __device__ __noinline__ float4 bump_eval_pdf(const DScene &sc, const lr_bsdf &b, const BumpIn in, V3 wo);
 
 struct PrParams { float anisotropic, roughness, spec_trans, metallic, clearcoat, flatness, sheen, brdf, bsdf; };
 
@@ -532,7 +532,7 @@ struct BSDF {
 
 // BumpMap::sample / eval / pdf (src/bsdfs/bumpmap.cpp:136-233): the nested BSDF runs in the perturbed frame; `in.wi`
 // is the incident direction in the original shading frame.
-__device__ __noinline__ BumpSampleOut bump_sample(const DScene &sc, const lr_bsdf &b, const BumpIn in, float s1, V2 s2) {
+static __device__ __noinline__ BumpSampleOut bump_sample(const DScene &sc, const lr_bsdf &b, const BumpIn in, float s1, V2 s2) {
     Frame pf = bump_frame(sc, b, in); BSDF nested(sc, b, in.uv); BumpSampleOut o;
     o.bs = nested.sample_n(pf.to_local(in.wi), s1, s2, o.weight);
     bool active = o.weight.x != 0.f || o.weight.y != 0.f || o.weight.z != 0.f;
@@ -543,7 +543,7 @@ __device__ __noinline__ BumpSampleOut bump_sample(const DScene &sc, const lr_bsd
     if (!active) o.weight = mk3(0.f);
     return o;
 }
-__device__ __noinline__ float4 bump_eval_pdf(const DScene &sc, const lr_bsdf &b, const BumpIn in, V3 wo) {
+static __device__ __noinline__ float4 bump_eval_pdf(const DScene &sc, const lr_bsdf &b, const BumpIn in, V3 wo) {
     Frame pf = bump_frame(sc, b, in); V3 pwo = pf.to_local(wo);
     if (!(wo.z * pwo.z > 0.f)) return make_float4(0.f, 0.f, 0.f, 0.f);
     BSDF nested(sc, b, in.uv); float pdf;

@@ -5,6 +5,7 @@
 
 namespace lr {
 
+#ifndef LR_LANES_TU      // set-up / utility kernels live in lr_backend.cu only
 // ------------------------------------------------------------------------------------------
 // LBVH build (Karras 2012): Morton keys -> radix sort (host calls cub) -> hierarchy -> refit.
 // ------------------------------------------------------------------------------------------
@@ -79,6 +80,8 @@ __global__ void k_gather_tris(const DTri *tris_gid, const uint32_t *order, uint3
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
     tris_sorted[i] = tris_gid[order[i]];
 }
+
+#endif // !LR_LANES_TU
 
 // ------------------------------------------------------------------------------------------
 // Lane rendering.  Persistent warps pull 32 consecutive global lanes at a time from a device
@@ -163,6 +166,7 @@ __global__ void __launch_bounds__(128) k_render(const __grid_constant__ DScene s
     flush_counters(cnt, nsamples, a.stats);
 }
 
+#ifndef LR_LANES_TU
 // HDRFilm::develop: out = value / (W == 0 ? 1 : W)
 __global__ void k_develop(const float *film, float *out, uint32_t npix, int C) {
     uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; if (p >= npix) return;
@@ -199,6 +203,9 @@ __global__ void __launch_bounds__(256) k_weight_image(const __grid_constant__ DS
         float one = 1.f; film_put<1>(sc, wimg, box ? L.pos : L.sample_pos, &one, coalesce);
     }
 }
+#endif // !LR_LANES_TU
+
+#ifdef LR_LANES_TU         // the per-lane adjoint kernel is compiled in lr_lanes.cu only
 // passes 1+2: primal (cloned sampler) then adjoint replay with dL = sum_px w(px) grad_in[px] / W[px]
 __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene sc, const __grid_constant__ RenderArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; unsigned long long nsamples = 0;
@@ -232,7 +239,11 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene
     flush_counters(cnt, nsamples, a.stats);
 }
 
+#endif // LR_LANES_TU
+
 } // namespace lr
 
+#ifndef LR_LANES_TU
 #include "lr_wavefront.cuh"
 #include "lr_wavefront_prb.cuh"
+#endif

@@ -20,6 +20,10 @@
 #ifndef LR_WF_OCC
 #define LR_WF_OCC 4
 #endif
+// resident 128-thread blocks per SM of the two surface-shading kernels (register cap = 65536 / (128 * LR_WF_OCC_SURF))
+#ifndef LR_WF_OCC_SURF
+#define LR_WF_OCC_SURF (2 * LR_WF_OCC)
+#endif
 
 namespace lr {
 
@@ -427,7 +431,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_shade_a_medium(const __gr
 
 // SHADE_A, surface / escape (volpath.cpp:300-362)
 template <int C, bool TO_FILM>
-__global__ void __launch_bounds__(128, 2 * LR_WF_OCC) k_wf_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
+__global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wf_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {
         bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false, nee = false;
@@ -603,7 +607,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_shade_b_medium(const __gr
 }
 
 // SHADE_B, surface: BSDF sampling, next ray, medium transition (volpath.cpp:364-389)
-__global__ void __launch_bounds__(128, 2 * LR_WF_OCC) k_wf_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
+__global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wf_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {

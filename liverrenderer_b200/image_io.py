@@ -1,5 +1,6 @@
-"""Host-side image input for `envmap` bitmaps (EXR/HDR via OpenCV, .npy/.npz arrays).
-Image *output* stays with the host application; the backend returns float tensors."""
+"""Host-side image I/O: `envmap` / `bitmap` inputs (EXR/HDR/PNG/JPG via OpenCV, .npy/.npz arrays) and
+`write_bitmap` for results (mi.util.write_bitmap, src/python/python/util.py:528-561), so a render can leave the
+process without the reference's host library."""
 from __future__ import annotations
 
 import os
@@ -60,3 +61,36 @@ def read_texture(path: str, raw: bool) -> np.ndarray:
     if img.ndim == 3 and img.shape[2] >= 3:
         img = np.concatenate([img[..., 2::-1], img[..., 3:]], axis=2)      # BGR(A) -> RGB(A)
     return texture_from_pixels(img, raw)
+
+
+def linear_to_srgb(v: np.ndarray) -> np.ndarray:
+    """Forward sRGB gamma (include/mitsuba/core/math.h linear_to_srgb), fp32."""
+    v = np.asarray(v, dtype=np.float32)
+    lo = v * np.float32(12.92)
+    hi = np.float32(1.055) * np.power(np.maximum(v, 0), np.float32(1.0 / 2.4), dtype=np.float32) - np.float32(0.055)
+    return np.where(v <= np.float32(0.0031308), lo, hi).astype(np.float32)
+
+
+def write_bitmap(filename: str, data) -> None:
+    """`mi.util.write_bitmap`: .png/.jpg/.jpeg => 8-bit sRGB (clamped, rounded as Bitmap::convert does: x*255 + 0.5),
+    anything else OpenCV can write (.exr, .hdr) => linear float32.  `data` is [H, W, 1|3|4] (or [H, W])."""
+    img = np.asarray(data.detach().cpu().numpy() if hasattr(data, "detach") else data, dtype=np.float32)
+    if img.ndim == 2:
+        img = img[..., None]
+    if img.ndim != 3 or img.shape[2] not in (1, 3, 4):
+        raise RuntimeError(f"write_bitmap(): expected an [H, W, 1|3|4] image, got {img.shape}")
+    ext = os.path.splitext(filename)[1].lower()
+    if ext in (".npy",):
+        np.save(filename, img); return
+    os.environ.setdefault("OPENCV_IO_ENABLE_OPENEXR", "1")
+    import cv2
+    if ext in (".png", ".jpg", ".jpeg"):
+        rgb = linear_to_srgb(np.clip(img[..., :3], 0.0, 1.0)) if img.shape[2] >= 3 else linear_to_srgb(np.clip(img, 0.0, 1.0))
+        out = np.concatenate([rgb, np.clip(img[..., 3:], 0.0, 1.0)], axis=2) if img.shape[2] == 4 else rgb
+        out = np.floor(out * np.float32(255.0) + np.float32(0.5)).astype(np.uint8)
+    else:
+        out = img
+    if out.shape[2] >= 3:
+        out = np.concatenate([out[..., 2::-1], out[..., 3:]], axis=2)          # RGB(A) -> BGR(A)
+    if not cv2.imwrite(filename, np.ascontiguousarray(out)):
+        raise RuntimeError(f'could not write image "{filename}"')

@@ -60,3 +60,25 @@ def test_c4_full_size_two_passes():
     rel = np.abs(hi - lo) / np.maximum(hi, 1e-2)
     assert np.quantile(rel, 0.99) < 0.12, float(np.quantile(rel, 0.99))
     ctx.close()
+
+
+def test_c3_full_size_bumpmap_boundary():
+    """C3 at full size with the fork's own boundary (bumpmap(bitmap) over a smooth dielectric):
+    weight checksum, and the converged image against an independent low-spp render and against the same scene with the
+    bump scale set to zero (a 0.005-scale bump map must not change the image mean by more than a few percent, but must
+    change the image)."""
+    W = H = 1080; spp = 256
+    d = scenes.liver_single_mesh(res=W, spp=spp, grid_res=256, tracking="dda", surface="bumpmap")
+    ctx = mi.Context(0).upload(mi.load_dict(d))
+    ctx.film_clear(); ctx.render_lanes(5, spp, 0, 0); st = ctx.stats(); film = ctx.film_read()
+    assert st["samples"] == W * H * spp and np.isfinite(film).all()
+    assert np.array_equal(film[..., 4], np.full((H, W), float(spp), np.float32))
+    img = film[..., :3] / spp
+    ctx.film_clear(); ctx.render_lanes(11, 16, 0, 0); low = ctx.film_read()[..., :3] / 16
+    assert abs(low.mean() - img.mean()) / img.mean() < 1e-2
+    ctx.close()
+    d["liver"]["bsdf"]["scale"] = 0.0
+    c0 = mi.Context(0).upload(mi.load_dict(d)); c0.film_clear(); c0.render_lanes(5, spp, 0, 0); flat = c0.film_read()[..., :3] / spp; c0.close()
+    assert abs(flat.mean() - img.mean()) / img.mean() < 5e-2
+    b = lambda x: x.reshape(H // 8, 8, W // 8, 8, 3).mean(axis=(1, 3))
+    assert np.quantile(np.abs(b(flat) - b(img)) / np.maximum(b(img), 1e-2), 0.999) > 1e-2      # the perturbed normals are visible

@@ -56,7 +56,7 @@ struct lr_ctx {
     int blocks_per_sm[8] = {0}; int n_sm = 148;
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
     WavefrontBuffers *wf = nullptr, *wf_more[3] = {nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // further batches in flight
-    cudaEvent_t fork_ev = nullptr; int wf_runs = 3, wf_grid_mult = 8, wf_grid_mult128 = 8;
+    cudaEvent_t fork_ev = nullptr; int wf_runs = 3, wf_grid_mult = LR_WF_OCC, wf_grid_mult128 = LR_WF_OCC_SURF;   // one resident wave of CTAs per stage launch (profiles/r1_ab_register_budgets.txt)
     uint64_t wf_pool_slots = 1ull << 25; uint32_t surf_bucket_mask = 0; bool use_wavefront = true, all_media_dda = false;
     uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;
     DevBuf *newbuf() { pool.push_back(new DevBuf()); return pool.back(); }

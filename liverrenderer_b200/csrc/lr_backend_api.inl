@@ -67,6 +67,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
 
     // ---- bitmap textures (reflectance / bump maps) ----
     {
+        if (s->n_textures && !s->textures) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_scene_upload: n_textures = %u but textures is NULL", s->n_textures);
         std::vector<DTex> tex(std::max<uint32_t>(s->n_textures, 1)); memset(tex.data(), 0, tex.size() * sizeof(DTex));
         for (uint32_t i = 0; i < s->n_textures; ++i) {
             const lr_texture &t = s->textures[i]; DTex &d = tex[i];

@@ -171,6 +171,19 @@ class Scene:
         self.textures.append(t)
         return len(self.textures)
 
+    def _set_reflectance(self, b, r, default):
+        """The colour texture slot of a BSDF block (diffuse `reflectance`, principled `base_color`): constant,
+        `checkerboard` (src/textures/checkerboard.cpp) or `bitmap` (src/textures/bitmap.cpp)."""
+        if isinstance(r, dict) and r.get("type") == "checkerboard":
+            b.tex_kind = 1
+            b.reflectance = _f3(_rgb(r.get("color0"), 0.4)); b.tex_color1 = _f3(_rgb(r.get("color1"), 0.2))
+            m = _xf(r, "to_uv").matrix
+            b.tex_to_uv = (C.c_float * 6)(m[0, 0], m[0, 1], m[0, 3], m[1, 0], m[1, 1], m[1, 3])
+        elif isinstance(r, dict) and r.get("type") == "bitmap":
+            b.tex_kind = 2; b.refl_tex = self._add_texture(r)
+        else:
+            b.reflectance = _f3(_rgb(r, default))
+
     def _add_bsdf(self, v):
         if v["type"] == "bumpmap":                             # src/bsdfs/bumpmap.cpp:101-127
             nested = [x for x in v.values() if isinstance(x, dict) and x.get("type") in
@@ -196,16 +209,7 @@ class Scene:
         b.reflectance = _f3([1, 1, 1]); b.transmittance = _f3([1, 1, 1])
         if t == "diffuse":                                     # diffuse.cpp: reflectance default 0.5
             b.kind = K.BSDF_DIFFUSE
-            r = v.get("reflectance")
-            if isinstance(r, dict) and r.get("type") == "checkerboard":     # src/textures/checkerboard.cpp
-                b.tex_kind = 1
-                b.reflectance = _f3(_rgb(r.get("color0"), 0.4)); b.tex_color1 = _f3(_rgb(r.get("color1"), 0.2))
-                m = _xf(r, "to_uv").matrix
-                b.tex_to_uv = (C.c_float * 6)(m[0, 0], m[0, 1], m[0, 3], m[1, 0], m[1, 1], m[1, 3])
-            elif isinstance(r, dict) and r.get("type") == "bitmap":         # src/textures/bitmap.cpp
-                b.tex_kind = 2; b.refl_tex = self._add_texture(r)
-            else:
-                b.reflectance = _f3(_rgb(r, 0.5))
+            self._set_reflectance(b, v.get("reflectance"), 0.5)
         elif t == "null":
             b.kind = K.BSDF_NULL
         elif t in ("dielectric", "roughdielectric"):           # roughdielectric.cpp:165-220
@@ -228,7 +232,7 @@ class Scene:
                     b.alpha_u = b.alpha_v = _flt(v.get("alpha"), 0.1)
         elif t == "principled":                                # principled.cpp:190-238
             b.kind = K.BSDF_PRINCIPLED
-            b.reflectance = _f3(_rgb(v.get("base_color"), 0.5)); b.roughness = _flt(v.get("roughness"), 0.5)
+            self._set_reflectance(b, v.get("base_color"), 0.5); b.roughness = _flt(v.get("roughness"), 0.5)
             flags = 0
             def opt(name, bit, default=0.0):
                 nonlocal flags

@@ -12,7 +12,8 @@ rep = int(sys.argv[5]) if len(sys.argv) > 5 else 1
 if w == "c1": d = scenes.cornell_box_path(res=res, spp=spp)
 elif w == "c2": d = scenes.cornell_box_fog(res=res, spp=spp)
 elif w == "c5": d = scenes.sphere_liver_inverse(res=res, spp=spp, grid_res=128, tracking=tracking)
-else: d = scenes.liver_single_mesh(res=res, spp=spp, grid_res=512 if w == "c3xl" else 256, tracking=tracking)
+else: d = scenes.liver_single_mesh(res=res, spp=spp, grid_res=512 if w == "c3xl" else 256, tracking=tracking,
+                                   surface=os.environ.get("LR_SURFACE", "roughdielectric"))   # LR_SURFACE=bumpmap: the fork's own boundary
 if os.environ.get("LR_CELL"): d["integrator"]["majorant_cell"] = int(os.environ["LR_CELL"])
 sc = mi.load_dict(d); ctx = mi.Context(0).upload(sc)
 for r in range(rep):

@@ -124,6 +124,9 @@ class Scene:
                 self._sensor_dict = v
             elif t in ("path", "volpath", "prbvolpath"):
                 self._integrator_dict = v
+            elif t in ("biovolpath", "biovolpath06", "volpathmis", "direct", "aov", "moment", "ptracer", "stokes", "depth",
+                       "prb", "prbvolpath_basic", "direct_projective", "prb_projective"):
+                raise NotImplementedError(f"integrator plugin '{t}' is outside the hot path (path, volpath, prbvolpath)")
         if not hasattr(self, "_sensor_dict"):
             raise ValueError("scene has no 'perspective' sensor")
         self._build_sensor(self._sensor_dict)

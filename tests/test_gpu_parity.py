@@ -352,3 +352,30 @@ def test_liver_bumpmap_surface_dda_matches_reference_order():
     img = mi.render(mi.load_dict(d), spp=64, seed=1); ref = orc.OracleScene(sc).render(seed=2, spp=64)
     assert np.isfinite(img).all()
     assert abs(img[..., :3].mean() - ref[..., :3].mean()) / ref[..., :3].mean() < 3e-2
+
+
+def test_bumpmap_prbvolpath_primal_and_adjoint():
+    """The same bump-mapped scene through `prbvolpath`: primal lanes against the oracle, and the grid gradient of a
+    heterogeneous medium behind a bump-mapped rough boundary against the oracle adjoint (same streams)."""
+    nb = {"type": "roughdielectric", "int_ior": 1.38, "ext_ior": 1.0, "alpha": 0.15}
+    sc = mi.load_dict(_bump_scene(nb, spp=8, res=32, integrator="prbvolpath")); n = 32 * 32 * 8
+    gpu = mi.Context(0).upload(sc).sample_lanes(0, 8, 0, n); cpu = orc.OracleScene(sc).sample_lanes(0, 8, 0, n)
+    assert path_match_fraction(gpu, cpu, 1e-3) > 0.985
+    d = scenes.sphere_liver_inverse(res=16, spp=4, grid_res=8)
+    d["sphere"]["interior"]["sigma_t"]["max_value"] = 0.5
+    d["sphere"]["bsdf"] = {"type": "bumpmap", "scale": 0.01, "tex": {"type": "bitmap", "bitmap": scenes.tissue_texture(64), "raw": True},
+                           "nested": dict(d["sphere"]["bsdf"])}
+    sc = mi.load_dict(d); ctx = mi.Context(0).upload(sc); o = orc.OracleScene(sc)
+    g = np.ones((16, 16, 3), dtype=np.float32); n = 16 * 16 * 4; chunk = 8; good = 0; total = 0
+    # The detached-sampling gradient is heavy-tailed (1/sigma_n weights): one path that takes another branch after an ulp
+    # difference in the perturbed frame can dominate the norm of the whole sum.  Same streams => same gradient is therefore
+    # checked per lane range: all but a few 8-lane ranges must agree tightly (tools/dbg_bump_prb.py: 2 of 1024 primal lanes
+    # differ on this scene; with the bump scale at 0 the full gradient agrees to 1e-6).
+    for b in range(0, n, chunk):
+        ctx.grid_grad_zero(0); ctx.render_backward(g, seed=1, spp=4, begin=b, end=b + chunk); ggpu = ctx.grid_grad_read(0).copy()
+        o.grid_grad_zero(0); o.render_backward(g, seed=1, spp=4, begin=b, end=b + chunk); gcpu = o.grid_grad_read(0)
+        assert np.isfinite(ggpu).all()
+        if np.linalg.norm(gcpu) == 0 and np.linalg.norm(ggpu) == 0:
+            continue
+        total += 1; good += np.linalg.norm(ggpu - gcpu) <= 1e-3 * max(np.linalg.norm(gcpu), 1e-12)
+    assert total >= 16 and good >= 0.85 * total, (good, total)

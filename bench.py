@@ -27,8 +27,15 @@ import time
 
 import numpy as np
 
-# stdout carries exactly one JSON line: NCCL's own banner / debug lines (printed when the box sets NCCL_DEBUG) go to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+# stdout carries exactly one JSON line: file descriptor 1 is pointed at stderr for the whole run (NCCL prints its banner /
+# debug lines straight to fd 1 when the box sets NCCL_DEBUG) and the line is written to the saved descriptor at the end.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
@@ -170,7 +177,7 @@ def run_reference(args):
                              "sample": f"{args.steps} x ({W}x{H} at {spp_cpu} spp) through oracle/liborc.so on {cores} threads"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "mrays_per_s": st["rays"] / dt / 1e6, "collisions_per_s": st["collisions"] / dt, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -398,7 +405,7 @@ def main():
                 "collisions_per_sample": R["colls"] / max(R["samples"], 1), "rays_per_sample": R["rays"] / max(R["samples"], 1),
                 "e2e": e2e, "gpu_launches": int(R["tot"]["launches"]), "clocks": R["clk"], "roofline": R["roofline"], "cpu_baseline": cpu, "prb": prb,
                 "reference_order_tracking": R["ref_order"], "bumpmap_surface": R["bump"]}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if R["world"] > 1:
         R["dist"].destroy_process_group()
 

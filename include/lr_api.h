@@ -270,6 +270,16 @@ typedef struct lr_stats {
     uint64_t tracking_launches;
 } lr_stats;
 
+/* Per-stage device time of the wavefront `volpath` (lr_profile_enable): CUDA events around every stage launch of a render
+   that keeps ONE batch in flight, so the intervals do not overlap (reference counterpart: the ProfilerPhase scopes of
+   include/mitsuba/core/profiler.h:20-49).  Stage names: lr_stage_name(i), i < n_stages.                                   */
+#define LR_MAX_STAGES 16
+typedef struct lr_stage_profile {
+    uint32_t n_stages, reserved;
+    double   ms[LR_MAX_STAGES];
+    uint64_t launches[LR_MAX_STAGES];
+} lr_stage_profile;
+
 typedef struct lr_ctx lr_ctx;
 
 /* ---- lifecycle ---------------------------------------------------------- */
@@ -333,6 +343,10 @@ int  lr_ray_intersect(lr_ctx *ctx, const float *rays, uint64_t n, float *hits);
 int  lr_cancel(lr_ctx *ctx);                    /* async-signal-safe             */
 int  lr_stats_get(lr_ctx *ctx, lr_stats *out);
 int  lr_set_stream(lr_ctx *ctx, void *cuda_stream);  /* run on the caller's stream (torch current stream) */
+/* profile mode (off by default): the next renders time every stage launch; lr_profile_get returns the sums since enable */
+int  lr_profile_enable(lr_ctx *ctx, int on);
+int  lr_profile_get(lr_ctx *ctx, lr_stage_profile *out);
+const char *lr_stage_name(uint32_t stage);
 
 #ifdef __cplusplus
 }

@@ -106,12 +106,17 @@ class lr_stats(C.Structure):
                 ("tracking_launches", C.c_uint64)]
 
 
+class lr_stage_profile(C.Structure):
+    _fields_ = [("n_stages", C.c_uint32), ("reserved", C.c_uint32), ("ms", C.c_double * 16), ("launches", C.c_uint64 * 16)]
+
+
 # every symbol include/lr_api.h declares (tests check the library exports all of them)
 API_SYMBOLS = [
     "lr_api_version", "lr_create", "lr_destroy", "lr_last_error", "lr_scene_upload", "lr_render", "lr_film_clear",
     "lr_render_lanes", "lr_film_channels", "lr_film_read", "lr_film_write", "lr_film_develop", "lr_film_device_ptr",
     "lr_sample_lanes", "lr_render_backward", "lr_grid_update", "lr_grid_grad_zero", "lr_grid_grad_read",
     "lr_grid_grad_device_ptr", "lr_grid_size", "lr_ray_intersect", "lr_cancel", "lr_stats_get", "lr_set_stream",
+    "lr_profile_enable", "lr_profile_get", "lr_stage_name",
 ]
 
 _LIB = None
@@ -153,6 +158,9 @@ def load_library(path: str | None = None):
     lib.lr_cancel.argtypes = [vp]; lib.lr_cancel.restype = C.c_int
     lib.lr_stats_get.argtypes = [vp, C.POINTER(lr_stats)]; lib.lr_stats_get.restype = C.c_int
     lib.lr_set_stream.argtypes = [vp, vp]; lib.lr_set_stream.restype = C.c_int
+    lib.lr_profile_enable.argtypes = [vp, C.c_int]; lib.lr_profile_enable.restype = C.c_int
+    lib.lr_profile_get.argtypes = [vp, C.POINTER(lr_stage_profile)]; lib.lr_profile_get.restype = C.c_int
+    lib.lr_stage_name.argtypes = [C.c_uint32]; lib.lr_stage_name.restype = C.c_char_p
     if path is None:
         _LIB = lib
     return lib

@@ -132,6 +132,14 @@ class Context:
     def cancel(self):
         self.lib.lr_cancel(self.ctx)
 
+    def profile(self, on: bool = True):
+        """Per-stage timing mode of the wavefront volpath (one batch in flight, CUDA events around every stage launch)."""
+        self._chk(self.lib.lr_profile_enable(self.ctx, 1 if on else 0), "lr_profile_enable")
+
+    def stage_profile(self) -> dict:
+        p = K.lr_stage_profile(); self._chk(self.lib.lr_profile_get(self.ctx, C.byref(p)), "lr_profile_get")
+        return {self.lib.lr_stage_name(i).decode(): {"ms": p.ms[i], "launches": int(p.launches[i])} for i in range(p.n_stages)}
+
     def stats(self) -> dict:
         s = K.lr_stats(); self._chk(self.lib.lr_stats_get(self.ctx, C.byref(s)), "lr_stats_get")
         return {k: getattr(s, k) for k, _ in K.lr_stats._fields_}

@@ -37,6 +37,15 @@ struct WavefrontBuffers {
     }
 };
 
+// forward wavefront pool (lr_wavefront.cuh): SoA state planes + index queues + counters, and the mapped pinned ring the
+// iterations write their live counts to
+struct WVRing { uint32_t live; uint32_t pad; unsigned long long lane_next; };
+struct WVPool {
+    DevBuf planes, queues, counters; uint32_t cap = 0;
+    WVRing *ring_host = nullptr, *ring_dev = nullptr; std::vector<cudaEvent_t> ring_ev;
+    ~WVPool() { if (ring_host) cudaFreeHost(ring_host); for (auto e : ring_ev) cudaEventDestroy(e); }
+};
+
 struct lr_ctx {
     int device = 0; cudaStream_t stream = nullptr; bool own_stream = false;
     std::string err; bool has_scene = false;
@@ -55,7 +64,10 @@ struct lr_ctx {
     lr_stats st{};
     int blocks_per_sm[8] = {0}; int n_sm = 148;
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
-    WavefrontBuffers *wf = nullptr, *wf_more[3] = {nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // further batches in flight
+    WavefrontBuffers *wf = nullptr;                                    // prbvolpath pool
+    WVPool *wv[4] = {nullptr, nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // forward pools: batches in flight
+    DevBuf lane_cursor;                                                // device-side lane cursor shared by the batches of one render
+    bool profile_on = false; std::vector<cudaEvent_t> prof_ev; double prof_ms[16] = {0}; uint64_t prof_launches[16] = {0};
     cudaEvent_t fork_ev = nullptr; int wf_runs = 3, wf_grid_mult = LR_WF_OCC, wf_grid_mult128 = LR_WF_OCC_SURF;   // one resident wave of CTAs per stage launch (profiles/r1_ab_register_budgets.txt)
     uint64_t wf_pool_slots = 1ull << 25; uint32_t surf_bucket_mask = 0; bool use_wavefront = true, all_media_dda = false;
     uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;
@@ -109,7 +121,10 @@ void lr_destroy(lr_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     c->free_scene(); delete c->wf; c->wf = nullptr;
-    for (int k = 0; k < 3; ++k) { delete c->wf_more[k]; c->wf_more[k] = nullptr; if (c->stream_more[k]) { cudaStreamDestroy(c->stream_more[k]); c->stream_more[k] = nullptr; } }
+    for (int k = 0; k < 4; ++k) { delete c->wv[k]; c->wv[k] = nullptr; }
+    for (int k = 0; k < 3; ++k) if (c->stream_more[k]) { cudaStreamDestroy(c->stream_more[k]); c->stream_more[k] = nullptr; }
+    for (auto e : c->prof_ev) cudaEventDestroy(e);
+    c->prof_ev.clear();
     if (c->fork_ev) { cudaEventDestroy(c->fork_ev); c->fork_ev = nullptr; }
     if (c->cancel_host) cudaFreeHost(c->cancel_host);
     if (c->ev0) cudaEventDestroy(c->ev0); if (c->ev1) cudaEventDestroy(c->ev1);
@@ -231,12 +246,15 @@ static int refresh_grid_derived(lr_ctx *c, uint32_t gi) {
     return LR_OK;
 }
 
+static int finish_bvh4(lr_ctx *c, const std::vector<DNode> &bin, const std::vector<DTri> &sorted);
+
 static int build_lbvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi) {
     uint32_t n = (uint32_t) tris.size(); DScene &sc = c->sc;
     c->tris_gid = c->newbuf(); if (int r = upload(c, c->tris_gid, tris.data(), n)) return r;
     DevBuf *sorted = c->newbuf(), *nodes = c->newbuf();
     LR_CUDA(c, sorted->alloc(std::max<uint32_t>(n, 1) * sizeof(DTri))); LR_CUDA(c, nodes->alloc(std::max<uint32_t>(n, 2) * sizeof(DNode)));
     sc.tris = sorted->as<DTri>(); sc.nodes = nodes->as<DNode>(); sc.n_tris = n;
+    sc.nodes4 = nullptr; sc.bvh4_stack = 1;
     if (n == 0) return LR_OK;
     DevBuf keys, keys2, vals, vals2, children, par_i, par_l, blo, bhi, flags, tmp;
     LR_CUDA(c, keys.alloc(n * 8)); LR_CUDA(c, keys2.alloc(n * 8)); LR_CUDA(c, vals.alloc(n * 4)); LR_CUDA(c, vals2.alloc(n * 4));
@@ -258,7 +276,11 @@ static int build_lbvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi) {
     }
     LR_CUDA(c, cudaGetLastError());
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
-    return LR_OK;
+    // the 4-wide tree of the TRACE kernels is collapsed on the host from the device-built two-wide tree
+    std::vector<DNode> bin(n >= 2 ? n - 1 : 0); std::vector<DTri> srt(n);
+    if (n >= 2) LR_CUDA(c, cudaMemcpy(bin.data(), nodes->p, (size_t) (n - 1) * sizeof(DNode), cudaMemcpyDeviceToHost));
+    LR_CUDA(c, cudaMemcpy(srt.data(), sorted->p, (size_t) n * sizeof(DTri), cudaMemcpyDeviceToHost));
+    return finish_bvh4(c, bin, srt);
 }
 
 #include "lr_bvh_host.inl"

@@ -35,7 +35,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         d.tri_offset = (uint32_t) tris.size(); d.n_faces = m.n_faces;
         d.flags = ((m.interior_medium >= 0 || m.exterior_medium >= 0) ? 1u : 0u) | (m.flip_normals ? 2u : 0u);
         bool is_null = s->bsdfs[m.bsdf].kind == LR_BSDF_NULL; if (is_null) sc.any_null_bsdf = 1;
-        { uint32_t k = s->bsdfs[m.bsdf].kind; surf_mask |= 1u << (k == LR_BSDF_ROUGHDIELECTRIC ? 1 : (k == LR_BSDF_PRINCIPLED ? 2 : 0)); }
+        uint32_t bucket; { uint32_t k = s->bsdfs[m.bsdf].kind; bucket = k == LR_BSDF_ROUGHDIELECTRIC ? 1u : (k == LR_BSDF_PRINCIPLED ? 2u : 0u); surf_mask |= 1u << bucket; }
         std::vector<float> cdf(m.n_faces); float area = 0.f;
         for (uint32_t f = 0; f < m.n_faces; ++f) {
             const uint32_t *ix = m.indices + 3 * (size_t) f;
@@ -43,7 +43,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
             const float *a = m.positions + 3 * (size_t) ix[0], *b = m.positions + 3 * (size_t) ix[1], *cc = m.positions + 3 * (size_t) ix[2];
             DTri t; uint32_t gid = (uint32_t) tris.size();
             t.v0 = make_float4(a[0], a[1], a[2], 0.f); t.v1 = make_float4(b[0], b[1], b[2], 0.f); t.v2 = make_float4(cc[0], cc[1], cc[2], 0.f);
-            memcpy(&t.v0.w, &gid, 4); memcpy(&t.v1.w, &i, 4); uint32_t fl = is_null ? 1u : 0u; memcpy(&t.v2.w, &fl, 4);
+            memcpy(&t.v0.w, &gid, 4); memcpy(&t.v1.w, &i, 4); uint32_t fl = (is_null ? 1u : 0u) | (bucket << 1); memcpy(&t.v2.w, &fl, 4);
             tris.push_back(t);
             for (const float *p : {a, b, cc}) { lo.x = std::min(lo.x, p[0]); lo.y = std::min(lo.y, p[1]); lo.z = std::min(lo.z, p[2]);
                                                 hi.x = std::max(hi.x, p[0]); hi.y = std::max(hi.y, p[1]); hi.z = std::max(hi.z, p[2]); }
@@ -64,6 +64,13 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     { DevBuf *b = c->newbuf(); if (int r = upload(c, b, s->bsdfs, s->n_bsdfs)) return r; sc.bsdfs = b->as<lr_bsdf>(); }
     if (int r = build_bvh(c, tris, lo, hi)) return r;
     sc.tris_gid = c->tris_gid ? c->tris_gid->as<DTri>() : nullptr;
+    {   // the trace kernels keep their traversal stack in dynamic shared memory: bvh4_stack entries per thread
+        const size_t smem = (size_t) sc.bvh4_stack * 256 * sizeof(int);
+        if (smem > 200 * 1024) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: acceleration structure too deep (%u stack entries)", sc.bvh4_stack);
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    }
 
     // ---- bitmap textures (reflectance / bump maps) ----
     {
@@ -207,7 +214,7 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
     a.lane_begin = begin; a.lane_end = end; a.seed = seed; a.spp_per_pass = p.spp_per_pass; a.n_passes = p.n_passes; a.total_spp = spp;
     a.work_counter = c->work_counter.as<unsigned long long>(); a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev;
     if (begin == end) return LR_OK;
-    c->wf_launches = 0;
+    c->wf_launches = 0; c->wf_tracking_ms = 0; c->wf_tracking_launches = 0;
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_PRBVOLPATH) {        // primal prbvolpath (INTEGRATOR_MAPPING renders)
         if (int r = wf_prepare(c, (end - begin))) return r;
         c->wf_tracking_ms = 0; c->wf_tracking_launches = 0; WFPrbArgs pa{};
@@ -216,7 +223,7 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
         return c->film_channels == 5 ? wavefront_prb_pass<5, true, false>(c, a, pa) : wavefront_prb_pass<4, true, false>(c, a, pa);
     }
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATH) {
-        if (int r = wf_prepare(c, (end - begin), true)) return r;
+        if (int r = wv_prepare(c, (end - begin))) return r;
         if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false>(c, a) : wavefront_render_t<4, false>(c, a);
         return c->film_channels == 5 ? wavefront_render_t<5, true>(c, a) : wavefront_render_t<4, true>(c, a);
     }
@@ -350,5 +357,18 @@ int lr_ray_intersect(lr_ctx *c, const float *rays, uint64_t n, float *hits) {
 }
 
 int lr_stats_get(lr_ctx *c, lr_stats *out) { if (!c || !out) return LR_ERR_INVALID_ARG; *out = c->st; return LR_OK; }
+
+int lr_profile_enable(lr_ctx *c, int on) {
+    if (!c) return LR_ERR_INVALID_ARG;
+    c->profile_on = on != 0; memset(c->prof_ms, 0, sizeof c->prof_ms); memset(c->prof_launches, 0, sizeof c->prof_launches);
+    return LR_OK;
+}
+int lr_profile_get(lr_ctx *c, lr_stage_profile *out) {
+    if (!c || !out) return LR_ERR_INVALID_ARG;
+    memset(out, 0, sizeof *out); out->n_stages = ST_COUNT;
+    for (int k = 0; k < ST_COUNT; ++k) { out->ms[k] = c->prof_ms[k]; out->launches[k] = c->prof_launches[k]; }
+    return LR_OK;
+}
+const char *lr_stage_name(uint32_t stage) { return stage < ST_COUNT ? kStageNames[stage] : ""; }
 
 } // extern "C"

@@ -121,6 +121,78 @@ struct Builder {
 
 }  // namespace sah
 
+// ---------------------------------------------------------------------------------------------
+// 4-wide tree for the wavefront TRACE kernels: the two-wide tree collapsed top-down (the inner child with the largest
+// surface area is replaced by its two children until the node holds four), depth-first order, root = node 0.  Child boxes
+// are the ones the two-wide nodes already carry, so both trees bound the same triangles with the same (padded) boxes.
+// Returns the worst-case number of stack entries a depth-first traversal that pushes every hit inner sibling can hold.
+// ---------------------------------------------------------------------------------------------
+namespace bvh4 {
+
+struct Child { int code; float lo[3], hi[3]; };
+
+static void children_of(const DNode &n, Child &l, Child &r) {
+    l.lo[0] = n.a.x; l.lo[1] = n.a.y; l.lo[2] = n.a.z; l.hi[0] = n.a.w; l.hi[1] = n.b.x; l.hi[2] = n.b.y;
+    r.lo[0] = n.b.z; r.lo[1] = n.b.w; r.lo[2] = n.c.x; r.hi[0] = n.c.y; r.hi[1] = n.c.z; r.hi[2] = n.c.w;
+    memcpy(&l.code, &n.d.x, 4); memcpy(&r.code, &n.d.y, 4);
+}
+static float half_area(const Child &c) {
+    float dx = c.hi[0] - c.lo[0], dy = c.hi[1] - c.lo[1], dz = c.hi[2] - c.lo[2]; return dx * dy + dy * dz + dz * dx;
+}
+
+struct Collapser {
+    const std::vector<DNode> &bin; std::vector<DNode4> out;
+    explicit Collapser(const std::vector<DNode> &b) : bin(b) { out.reserve(b.size() / 2 + 2); }
+    // emits the 4-wide node for two-wide node `node`; returns its index, `need` = stack entries below it
+    int emit(int node, uint32_t &need) {
+        Child ch[4]; int n = 2; children_of(bin[node], ch[0], ch[1]);
+        while (n < 4) {
+            int best = -1; float best_area = -1.f;
+            for (int i = 0; i < n; ++i) if (ch[i].code >= 0) { float a = half_area(ch[i]); if (a > best_area) { best_area = a; best = i; } }
+            if (best < 0) break;
+            Child l, r; children_of(bin[ch[best].code], l, r); ch[best] = l; ch[n++] = r;
+        }
+        int self = (int) out.size(); out.push_back(DNode4{});
+        DNode4 nd; float *lo[3] = { &nd.lox.x, &nd.loy.x, &nd.loz.x }, *hi[3] = { &nd.hix.x, &nd.hiy.x, &nd.hiz.x }; int *cc = &nd.child.x;
+        uint32_t inner = 0, below = 0;
+        for (int i = 0; i < 4; ++i) {
+            if (i < n) {
+                int code = ch[i].code;
+                if (code >= 0) { uint32_t nb = 0; code = emit(code, nb); below = std::max(below, nb); ++inner; }
+                for (int k = 0; k < 3; ++k) { lo[k][i] = ch[i].lo[k]; hi[k][i] = ch[i].hi[k]; }
+                cc[i] = code;
+            } else {
+                for (int k = 0; k < 3; ++k) { lo[k][i] = INFINITY; hi[k][i] = INFINITY; }      // both planes at +inf: the slab test fails for every ray
+                cc[i] = 0x7fffffff;
+            }
+        }
+        nd.pad = make_int4(0, 0, 0, 0);
+        out[self] = nd;
+        need = inner ? (inner - 1) + below : 0;
+        return self;
+    }
+};
+
+}  // namespace bvh4
+
+// `bin`: the two-wide nodes (host copy); uploads the collapsed tree and records it in the scene
+static int finish_bvh4(lr_ctx *c, const std::vector<DNode> &bin, const std::vector<DTri> &sorted) {
+    DScene &sc = c->sc; uint32_t n = (uint32_t) sorted.size();
+    sc.nodes4 = nullptr; sc.bvh4_stack = 1;
+    if (n == 0) return LR_OK;
+    std::vector<DNode4> nodes4; uint32_t need = 0;
+    if (n == 1) {                                             // a single triangle: one node with one leaf child
+        DNode4 nd; float *lo[3] = { &nd.lox.x, &nd.loy.x, &nd.loz.x }, *hi[3] = { &nd.hix.x, &nd.hiy.x, &nd.hiz.x }; int *cc = &nd.child.x;
+        for (int i = 0; i < 4; ++i) { for (int k = 0; k < 3; ++k) { lo[k][i] = i ? INFINITY : -INFINITY; hi[k][i] = INFINITY; } cc[i] = i ? 0x7fffffff : ~0; }
+        nd.pad = make_int4(0, 0, 0, 0); nodes4.push_back(nd);
+    } else {
+        bvh4::Collapser col(bin); col.emit(0, need); nodes4.swap(col.out);
+    }
+    DevBuf *dn = c->newbuf(); if (int r = upload(c, dn, nodes4.data(), nodes4.size())) return r;
+    sc.nodes4 = dn->as<DNode4>(); sc.bvh4_stack = need + 1;
+    return LR_OK;
+}
+
 static int build_sah_bvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi) {
     uint32_t n = (uint32_t) tris.size(); DScene &sc = c->sc;
     V3 ext = hi - lo; float pad = 1e-6f * std::max(ext.x, std::max(ext.y, ext.z)) + 1e-30f;
@@ -132,5 +204,5 @@ static int build_sah_bvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi)
     if (int r = upload(c, ds, sorted.data(), n)) return r;
     if (int r = upload(c, dn, bld.nodes.data(), bld.nodes.size())) return r;
     sc.tris = ds->as<DTri>(); sc.nodes = dn->as<DNode>(); sc.n_tris = n;
-    return LR_OK;
+    return finish_bvh4(c, bld.nodes, sorted);
 }

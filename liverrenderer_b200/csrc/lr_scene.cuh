@@ -13,8 +13,12 @@
 
 namespace lr {
 
-struct DTri { float4 v0, v1, v2; };
+struct DTri { float4 v0, v1, v2; };   // .w lanes: v0 = global primitive id, v1 = mesh id, v2 = bit 0 null-BSDF mesh, bits 1-2 surface bucket
 struct DNode { float4 a, b, c, d; };
+// 4-wide node walked by the wavefront TRACE kernels (lr_trace.cuh): the boxes of up to four children, one float4 per
+// plane (component i = child i), so a visit is six LDG.128 of box planes + one of child links.  Links: >= 0 inner node,
+// < 0 => ~k = k-th triangle of `tris`; an unused child has both planes at +inf (never hit).  128 B, cache-line aligned.
+struct __align__(16) DNode4 { float4 lox, loy, loz, hix, hiy, hiz; int4 child; int4 pad; };
 
 struct DMesh {
     const float *pos, *nrm, *uv; const uint32_t *idx; const float *area_cdf;
@@ -51,6 +55,7 @@ struct DEmitter {
 // so every field is a uniform constant-bank load.
 struct DScene {
     const DNode *nodes; const DTri *tris; const DMesh *meshes;
+    const DNode4 *nodes4; uint32_t bvh4_stack;      // 4-wide tree over the same `tris`; worst-case traversal stack depth (entries)
     const DTri *tris_gid;             // triangles by global primitive id (tris is in BVH order)
     const DTex *textures;
     const lr_bsdf *bsdfs; const DMedium *media; const DGrid *grids; const DEmitter *emitters;
@@ -110,7 +115,7 @@ LR_DEV Hit bvh_trace(const DScene &sc, const Ray &ray) {
         return false;
     };
     if (sc.n_tris == 1) { leaf(0); return h; }
-    int stack[48]; int sp = 0; int node = 0;
+    int stack[64]; int sp = 0; int node = 0;
     while (true) {
         const DNode n = sc.nodes[node];
         // slab test of both children; bounds are padded at build time, far side scaled by 1+4ulp
@@ -132,7 +137,7 @@ LR_DEV Hit bvh_trace(const DScene &sc, const Ray &ray) {
         if (h0 && h1) {
             bool swap = n1 < n0;
             int nearc = swap ? c1 : c0, farc = swap ? c0 : c1;
-            if (sp < 48) stack[sp++] = farc;
+            if (sp < 64) stack[sp++] = farc;
             node = nearc;
         } else if (h0) node = c0;
         else if (h1) node = c1;

@@ -1,197 +1,351 @@
-// lr_wavefront.cuh -- wavefront `volpath`: the same per-lane algorithm as sample_volpath()
-// (lr_integrators.cuh; reference src/integrators/volpath.cpp:93-554), cut at the points where lanes diverge
-// into stage kernels that exchange path state through HBM:
+// lr_wavefront.cuh -- wavefront `volpath` (reference: src/integrators/volpath.cpp:93-554), the production forward path.
+// The per-lane loop of sample_volpath() (lr_integrators.cuh) is cut where lanes diverge; the pieces are stage kernels over
+// index queues, and ray queries are a stage of their own (lr_trace.cuh):
 //
-//   GEN      seed / continue a lane, camera ray, primary closest hit                 (regen queue)
-//   TRACK    russian roulette + delta-tracking loop (null collisions stay in registers) until an EVENT:
-//            real scatter -> scatter queue | surface / escape -> surface queue | end of path -> regen queue
-//   SHADE_A  scatter: NEE set-up through the phase function; surface: emitter hit + MIS, NEE set-up through the BSDF
-//   NEE      ratio-tracking transmittance walk of the shadow segment (volpath.cpp:454-551)
-//   SHADE_B  phase / BSDF sampling, next ray + closest hit, medium transition -> next active queue
+//   GEN       lane hand-out, TEA/PCG32 seeding, camera ray, primary hit.  A primary ray that leaves the scene is finished
+//             right here (environment lookup + film splat, no path state is ever written for it)
+//   TRACK     free-flight sampling in the current medium (null collisions stay in registers) until an EVENT:
+//             real scatter -> scatter queue | boundary reached -> surface bucket / escape queue | depth limit -> film
+//   SHADE_A   scatter: emitter sample + phase value; surface: emitter hit + MIS, emitter sample + BSDF value.  Writes the
+//             shadow ray, pushes the slot to the shadow queue
+//   ESCAPE    rays that left the scene: environment radiance + MIS, film splat
+//   TRACE_S   occlusion of the shadow rays (persistent, 4-wide BVH); unoccluded segments outside any medium are added to
+//             the path's radiance at once, the others go to the NEE queue
+//   NEE       ratio-tracking transmittance walk along the shadow segment (volpath.cpp:454-551)
+//   SHADE_B   phase / BSDF sampling, medium transition, then the russian-roulette + depth test that opens the reference's
+//             NEXT loop iteration (volpath.cpp:160-178; no draw lies between the two, so the stream order is the
+//             reference's): a path that dies never costs a ray.  Survivors go to the trace queue
+//   TRACE_C   closest hit of the new rays (persistent, 4-wide BVH); routes each path by what comes next:
+//             inside a medium -> TRACK queue, surface -> bucket of its BSDF class, nothing hit -> escape queue
 //
-// Every lane keeps its own PCG32 stream (keyed by the GLOBAL lane index) and draws in exactly the order of the
-// reference, so a wavefront render is lane-for-lane identical to the per-lane kernel and to the oracle.
-// Queues are index arrays compacted with warp ballots (one atomicAdd per warp); surface events are bucketed
-// by BSDF class so a warp shades one material model.
+// Path state lives in SoA planes of 16-byte records indexed by slot (WVPlanes): a stage touches only the planes it needs
+// (TRACE: 32 B in / 16 B out), and consecutive queue entries -- queues are compacted with warp ballots in lane order --
+// share sectors.  Every lane keeps its own PCG32 stream (keyed by the GLOBAL lane index) and draws in exactly the order
+// of the reference, so a wavefront render is lane-for-lane identical to the per-lane kernel and to the oracle.
 #pragma once
-#include "lr_integrators.cuh"
+#include "lr_wf_common.cuh"
+#include "lr_trace.cuh"
 
-// resident 256-thread blocks per SM the stage kernels are compiled for (register cap = 65536 / (256 * LR_WF_OCC))
-#ifndef LR_WF_OCC
-#define LR_WF_OCC 4
-#endif
-// resident 128-thread blocks per SM of the two surface-shading kernels (register cap = 65536 / (128 * LR_WF_OCC_SURF))
-#ifndef LR_WF_OCC_SURF
-#define LR_WF_OCC_SURF (2 * LR_WF_OCC)
+#ifndef LR_TRACE_OCC
+#define LR_TRACE_OCC 4               // resident 256-thread blocks per SM of the trace kernels
 #endif
 
 namespace lr {
 
-enum : uint32_t {
-    WF_CHANNEL_MASK = 3u, WF_VALID_RAY = 1u << 2, WF_SPEC_CHAIN = 1u << 3, WF_NEE_ACTIVE = 1u << 4, WF_DEAD = 1u << 5,
-    WF_NEE_NEEDS_ISECT = 1u << 6, WF_HAS_LANE = 1u << 7,
-    WF_MEDIUM_SHIFT = 8, WF_MEDIUM_MASK = 0xffu << 8,          // 0xff: no medium
-    WF_PASS_SHIFT = 16                                          // pass index of a multi-pass render (integrator.cpp:279-293)
+struct WVPlanes {
+    ulonglong2 *rng;     // PCG32 state, inc
+    float4 *o;           // ray.o, ray.maxt
+    float4 *d;           // ray.d, flags (bits)
+    float4 *thr;         // throughput, depth (bits)
+    float4 *hit;         // t, prim (bits), u, v of the closest hit along the current ray
+    float4 *res;         // radiance so far, eta
+    float4 *lsp;         // last_scatter_p, last_scatter_direction_pdf
+    float4 *lane;        // lane lo/hi (bits), film sample position
+    // NEE (volpath.cpp:400-554)
+    float4 *no;          // shadow ray origin, max_dist
+    float4 *nd;          // shadow ray direction, ds.dist
+    float4 *nw;          // throughput * (phase | bsdf) value * MIS weight * emitter value, walk medium (bits)
+    float4 *nhit;        // closest hit along the shadow ray (only when the walk needs it)
 };
-#define WF_N_SURF 3                                             // surface buckets: 0 diffuse/null/dielectric, 1 roughdielectric, 2 principled
+#define WV_N_PLANES 12
 
-// One path slot, 256 B, 16-byte fields: a thread moves its slot with 128-bit loads/stores (full 32 B sectors).
-struct __align__(16) WState {
-    unsigned long long rng_state, rng_inc;
-    float4 o_maxt;          // ray.o, ray.maxt
-    float4 d_eta;           // ray.d, eta
-    float4 thr_lpdf;        // throughput, last_scatter_direction_pdf
-    float4 res_depth;       // result, depth (bits)
-    float4 hit;             // t, prim (bits), u, v of the closest hit along the current ray
-    float4 lsp_flags;       // last_scatter_p, flags (bits)
-    float4 lane_pos;        // lane lo/hi (bits), film sample position
-    // ---- NEE walk (volpath.cpp:400-554) ----
-    float4 no_maxd;         // shadow ray origin, max_dist
-    float4 nd_total;        // ds.d, total_dist
-    float4 ntr_mis;         // transmittance, MIS weight
-    float4 nw_med;          // throughput * (phase | bsdf) value, walk medium (bits)
-    float4 ne_dist;         // emitter_val, ds.dist
-    float4 nhit;            // closest hit along the shadow ray
-    float4 pad0, pad1;
+struct WVQueues {                      // device-side counters of one pool
+    uint32_t n_trace, n_track, n_scatter, n_escape, n_shadow, n_nee, n_regen;
+    uint32_t n_surf[WF_N_SURF]; uint32_t cursor[3];                    // work cursors of TRACE_C, TRACK, TRACE_S
+    uint32_t n_alloc, live, pad[3];
 };
-static_assert(sizeof(WState) == 256, "WState layout");
+#define WV_N_QUEUES (7 + WF_N_SURF)
 
-struct WQueues {                       // device-side counters, one 64-byte block
-    uint32_t n_active[2]; uint32_t n_scatter; uint32_t n_surf[WF_N_SURF]; uint32_t n_regen; uint32_t live;
-    unsigned long long lane_next; uint32_t n_nee; uint32_t cursor; uint32_t pad[4];   // cursor: work cursor of k_wf_track_dda
-};
-
-struct WFArgs {
-    WState *st; WQueues *q; uint32_t *q_active[2]; uint32_t *q_scatter; uint32_t *q_surf[WF_N_SURF]; uint32_t *q_regen; uint32_t *q_nee;   // q_nee: slots whose NEE walk is live
-    uint32_t cap; int cur;            // slots; index of the input active queue
-    const DTri *tris_gid; float *film; float *lanes_out;
-    uint64_t lane_begin, lane_end; uint32_t seed, spp_per_pass, n_passes;
+struct WVArgs {
+    WVPlanes p; WVQueues *q;
+    uint32_t *q_trace, *q_track, *q_scatter, *q_escape, *q_shadow, *q_nee, *q_regen, *q_surf[WF_N_SURF];
+    uint32_t cap, slack;                                               // slots; GEN stops handing out lanes at cap - slack
+    float *film; float *lanes_out;
+    uint64_t lane_begin, lane_end; unsigned long long *lane_next;      // lane cursor shared by all batches of one render call
+    uint32_t seed, spp_per_pass, n_passes;
     unsigned long long *stats;
 };
 
-// ---- queue push: ballot + popc, one atomic per warp; call at a point where the whole warp is converged ----
-LR_DEV void wf_push(uint32_t *queue, uint32_t *count, uint32_t slot, bool pred) {
-    unsigned m = __ballot_sync(0xffffffffu, pred);
-    if (m == 0) return;
-    unsigned lane = threadIdx.x & 31; uint32_t base = 0;
-    if (lane == (unsigned) (__ffs(m) - 1)) base = atomicAdd(count, (uint32_t) __popc(m));
-    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-    if (pred) queue[base + __popc(m & ((1u << lane) - 1u))] = slot;
+LR_DEV Sampler wv_rng(const WVPlanes &p, uint32_t s) { const ulonglong2 r = p.rng[s]; Sampler m; m.state = r.x; m.inc = r.y; return m; }
+LR_DEV void wv_rng_store(const WVPlanes &p, uint32_t s, const Sampler &m) { p.rng[s] = make_ulonglong2(m.state, m.inc); }
+LR_DEV uint32_t wv_bucket(const DScene &sc, const Hit &h) { return (__float_as_uint(sc.tris_gid[h.prim].v2.w) >> 1) & 3u; }
+
+// volpath.cpp:160-178: the russian-roulette + depth test at the top of a loop iteration
+LR_DEV bool wv_rr(const DScene &sc, Sampler &smp, V3 &thr, float eta, uint32_t depth) {
+    bool active = any_nonzero(thr);
+    const float q = fminf(hmax(thr) * sqr(eta), .95f);
+    const bool perform_rr = depth > (uint32_t) sc.rr_depth;
+    if (active) { const float u = smp.next_1d(); active &= (u < q) || !perform_rr; }
+    if (perform_rr) thr *= 1.f / q;
+    active &= depth < sc.max_depth;
+    return active;
 }
 
-LR_DEV uint32_t wf_flags(const WState &S) { return __float_as_uint(S.lsp_flags.w); }
-LR_DEV int wf_medium(uint32_t f) { uint32_t m = (f & WF_MEDIUM_MASK) >> WF_MEDIUM_SHIFT; return m == 0xffu ? -1 : (int) m; }
-LR_DEV uint32_t wf_set_medium(uint32_t f, int m) { return (f & ~WF_MEDIUM_MASK) | (((uint32_t) (m < 0 ? 0xff : m)) << WF_MEDIUM_SHIFT); }
-LR_DEV Hit wf_hit(float4 h) { Hit r; r.t = h.x; r.prim = __float_as_uint(h.y); r.u = h.z; r.v = h.w; return r; }
-LR_DEV float4 wf_hit4(const Hit &h) { return make_float4(h.t, __uint_as_float(h.prim), h.u, h.v); }
-LR_DEV int wf_surf_bucket(const DScene &sc, const DTri *tris_gid, const Hit &h) {
-    if (!hit_valid(h)) return 0;
-    uint32_t k = sc.bsdfs[sc.meshes[__float_as_uint(tris_gid[h.prim].v1.w)].bsdf].kind;
-    return k == LR_BSDF_ROUGHDIELECTRIC ? 1 : (k == LR_BSDF_PRINCIPLED ? 2 : 0);
-}
-
-// end of a path: splat (ImageBlock::put) or per-lane output
+// End of a path: ImageBlock::put or the per-lane output.  Call where the warp is converged; `pred`: this lane finishes.
+// Box filter: lanes of one pixel are neighbours in the queues (lane = pixel * spp + sample), so a warp that finishes samples of a
+// single pixel adds them up with shuffles and issues one set of atomics instead of 32 to the same address.
 template <int C, bool TO_FILM>
-LR_DEV void wf_finish(const DScene &sc, const WFArgs &a, const WState &S, V3 L, uint32_t flags) {
-    bool valid = (flags & WF_VALID_RAY) != 0;
-    if (TO_FILM) {
-        float aovs[C]; aovs[0] = L.x; aovs[1] = L.y; aovs[2] = L.z;
-        if (C == 5) { aovs[3] = valid ? 1.f : 0.f; aovs[4] = 1.f; } else aovs[3] = 1.f;
-        film_put<C>(sc, a.film, mk2(S.lane_pos.z, S.lane_pos.w), aovs, a.spp_per_pass >= 4);
-    } else {
-        uint64_t lane = ((uint64_t) __float_as_uint(S.lane_pos.y) << 32) | __float_as_uint(S.lane_pos.x);
-        uint32_t pass = flags >> WF_PASS_SHIFT;
-        reinterpret_cast<float4 *>(a.lanes_out)[(lane - a.lane_begin) * a.n_passes + pass] = make_float4(L.x, L.y, L.z, valid ? 1.f : 0.f);
+LR_DEV void wv_finish(const DScene &sc, const WVArgs &a, bool pred, float4 lane_pos, V3 L, uint32_t flags) {
+    const bool valid = (flags & WF_VALID_RAY) != 0;
+    if (!TO_FILM) {
+        if (pred) {
+            const uint64_t lane = ((uint64_t) __float_as_uint(lane_pos.y) << 32) | __float_as_uint(lane_pos.x);
+            const uint32_t pass = flags >> WF_PASS_SHIFT;
+            reinterpret_cast<float4 *>(a.lanes_out)[(lane - a.lane_begin) * a.n_passes + pass] = make_float4(L.x, L.y, L.z, valid ? 1.f : 0.f);
+        }
+        return;
     }
+    float aovs[C]; aovs[0] = L.x; aovs[1] = L.y; aovs[2] = L.z;
+    if (C == 5) { aovs[3] = valid ? 1.f : 0.f; aovs[4] = 1.f; } else aovs[3] = 1.f;
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (m == 0) return;
+    if (sc.sensor.rfilter == LR_RFILTER_BOX && __popc(m) > 1) {
+        const int W = (int) sc.sensor.film_width, H = (int) sc.sensor.film_height;
+        const int x = (int) floorf(lane_pos.z), y = (int) floorf(lane_pos.w);
+        const int pix = (pred && x >= 0 && y >= 0 && x < W && y < H) ? y * W + x : -1;
+        const int leader = __ffs(m) - 1, pix0 = __shfl_sync(0xffffffffu, pix, leader);
+        if (__all_sync(0xffffffffu, !pred || pix == pix0)) {
+            if (pix0 < 0) return;
+#pragma unroll
+            for (int k = 0; k < C; ++k) {
+                float v = pred ? aovs[k] : 0.f;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if ((int) (threadIdx.x & 31u) == leader) atomicAdd(a.film + (size_t) pix0 * C + k, v);
+            }
+            return;
+        }
+    }
+    if (pred) film_put<C>(sc, a.film, mk2(lane_pos.z, lane_pos.w), aovs, a.spp_per_pass >= 4);
 }
 
-#define WF_FOR_QUEUE(COUNT)                                                                             \
-    const uint32_t _n = (COUNT);                                                                        \
-    const uint32_t _stride = gridDim.x * blockDim.x;                                                    \
-    for (uint32_t _base = (blockIdx.x * blockDim.x + threadIdx.x) & ~31u; _base < _n; _base += _stride) \
-        if (const uint32_t qi = _base + (threadIdx.x & 31u); true)
+// a finished path whose lane has further passes to render (integrator.cpp:347-356: the stream simply continues)
+LR_DEV bool wv_more_passes(const WVArgs &a, uint32_t flags) { return a.n_passes > 1 && (flags >> WF_PASS_SHIFT) + 1 < a.n_passes; }
+
+// where a path with a fresh closest hit goes next
+LR_DEV void wv_route(const DScene &sc, const WVArgs &a, uint32_t slot, bool pred, uint32_t flags, const Hit &h) {
+    const bool in_medium = pred && wf_medium(flags) >= 0, esc = pred && !in_medium && !hit_valid(h);
+    const uint32_t b = (pred && !in_medium && !esc) ? wv_bucket(sc, h) : 0xffu;
+    wf_push(a.q_track, &a.q->n_track, slot, in_medium);
+    wf_push(a.q_escape, &a.q->n_escape, slot, esc);
+#pragma unroll
+    for (uint32_t k = 0; k < WF_N_SURF; ++k) wf_push(a.q_surf[k], &a.q->n_surf[k], slot, b == k);
+}
 
 // ------------------------------------------------------------------------------------------
-// GEN: every free slot takes the next pass of its lane or the next global lane (integrator.cpp:321-356)
+// GEN (integrator.cpp:321-356, perspective.cpp:239-279, volpath.cpp:93-178): starts lanes.  `own_slot`: the lane already owns
+// `slot` (a later pass of a multi-pass render); otherwise a slot is allocated only if the path survives its first segment.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_gen(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
-    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; unsigned long long nsamples = 0;
-    uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
-    WF_FOR_QUEUE(a.q->n_regen) {
-        bool item = qi < _n; uint32_t slot = item ? a.q_regen[qi] : 0; bool live = false;
-        WState *S = a.st + slot;
-        Sampler smp; uint64_t lane = 0; uint32_t pass = 0; bool need_lane = item;
-        if (item) {
-            uint32_t f = wf_flags(*S);
-            if ((f & WF_HAS_LANE) && (f >> WF_PASS_SHIFT) + 1 < a.n_passes) {          // same lane, next pass: the stream continues
-                need_lane = false; live = true; pass = (f >> WF_PASS_SHIFT) + 1;
-                smp.state = S->rng_state; smp.inc = S->rng_inc; smp.advance(a.spp_per_pass);
-                lane = ((uint64_t) __float_as_uint(S->lane_pos.y) << 32) | __float_as_uint(S->lane_pos.x);
-            }
-        }
-        {   // hand out fresh global lanes, one atomic per warp
-            unsigned m = __ballot_sync(0xffffffffu, need_lane); unsigned l = threadIdx.x & 31; unsigned long long base = 0;
-            if (m) {
-                if (l == (unsigned) (__ffs(m) - 1)) base = atomicAdd(&a.q->lane_next, (unsigned long long) __popc(m));
-                base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-                if (need_lane) {
-                    lane = a.lane_begin + base + __popc(m & ((1u << l) - 1u));
-                    if (lane < a.lane_end) { live = true; seed_sampler(sc, smp, a.seed, lane, a.spp_per_pass, a.n_passes); }
-                }
-            }
-        }
-        if (item && !live) { S->lsp_flags.w = __uint_as_float(WF_DEAD); }
-        if (live) {
-            LaneSetup L; L.smp = smp; lane_begin_sample(sc, L, lane, a.spp_per_pass); lane_next_ray(sc, L);
-            uint32_t channel = (uint32_t) fminf(L.smp.next_1d() * 3.f, 2.f);                // volpath.cpp:117-120
-            uint32_t f = channel | WF_HAS_LANE | (pass << WF_PASS_SHIFT);
-            if (!sc.hide_emitters && sc.env >= 0) f |= WF_VALID_RAY;                         // :103
-            if (!sc.hide_emitters) f |= WF_SPEC_CHAIN;                                       // :114
+template <int C, bool TO_FILM>
+LR_DEV void wv_start_paths(const DScene &sc, const WVArgs &a, bool have, uint64_t lane, uint32_t pass, Sampler smp, bool own_slot, uint32_t slot,
+                           Counters &cnt, unsigned long long &nsamples) {
+    LaneSetup L; L.smp = smp; L.pos = mk2(0.f, 0.f); L.sample_pos = L.pos; L.ray.o = L.ray.d = mk3(0.f); L.ray.maxt = 0.f;
+    if (have) lane_begin_sample(sc, L, lane, a.spp_per_pass);
+    const bool box = sc.sensor.rfilter == LR_RFILTER_BOX;
+    bool working = have, keep = false; Hit h; h.t = LR_INF; h.prim = 0xffffffffu; h.u = h.v = 0.f; uint32_t f = 0; V3 thr = mk3(1.f);
+    while (__any_sync(0xffffffffu, working)) {
+        bool fin = false; V3 Lr = mk3(0.f);
+        if (working) {
+            lane_next_ray(sc, L);
+            const uint32_t channel = (uint32_t) fminf(L.smp.next_1d() * 3.f, 2.f);           // volpath.cpp:117-120
+            f = channel | WF_HAS_LANE | (pass << WF_PASS_SHIFT);
+            if (!sc.hide_emitters && sc.env >= 0) f |= WF_VALID_RAY;                          // :103
+            if (!sc.hide_emitters) f |= WF_SPEC_CHAIN;                                        // :114
             f = wf_set_medium(f, sc.sensor.medium);
-            cnt.rays++; Hit h = bvh_trace<false, false>(sc, L.ray); nsamples++;
-            bool box = sc.sensor.rfilter == LR_RFILTER_BOX; V2 fp = box ? L.pos : L.sample_pos;
-            S->rng_state = L.smp.state; S->rng_inc = L.smp.inc;
-            S->o_maxt = make_float4(L.ray.o.x, L.ray.o.y, L.ray.o.z, L.ray.maxt); S->d_eta = make_float4(L.ray.d.x, L.ray.d.y, L.ray.d.z, 1.f);
-            S->thr_lpdf = make_float4(1.f, 1.f, 1.f, 1.f); S->res_depth = make_float4(0.f, 0.f, 0.f, __uint_as_float(0u));
-            S->hit = wf_hit4(h); S->lsp_flags = make_float4(0.f, 0.f, 0.f, __uint_as_float(f));
-            S->lane_pos = make_float4(__uint_as_float((uint32_t) lane), __uint_as_float((uint32_t) (lane >> 32)), fp.x, fp.y);
+            nsamples++; thr = mk3(1.f);
+            const bool alive = wv_rr(sc, L.smp, thr, 1.f, 0u);                                // :160-178 of the first iteration
+            if (alive) { cnt.rays++; h = bvh_trace<false, false>(sc, L.ray); }
+            if (!alive) fin = true;
+            else if (!hit_valid(h) && sc.sensor.medium < 0) {                                 // left the scene: :326-345 with an invalid si
+                fin = true;
+                if (sc.env >= 0 && !sc.hide_emitters) Lr = thr * emitter_eval(sc, sc.env, -L.ray.d.z, L.ray.d);
+            } else { keep = true; working = false; }
         }
-        wf_push(q_out, n_out, slot, live);
+        const V2 fp = box ? L.pos : L.sample_pos;
+        wv_finish<C, TO_FILM>(sc, a, fin, make_float4(__uint_as_float((uint32_t) lane), __uint_as_float((uint32_t) (lane >> 32)), fp.x, fp.y), Lr, f);
+        if (fin) { ++pass; if (pass < a.n_passes) L.smp.advance(a.spp_per_pass); else working = false; }
+    }
+    if (!own_slot) {                                                                          // one atomic per warp
+        const unsigned m = __ballot_sync(0xffffffffu, keep), l = threadIdx.x & 31u; uint32_t base = 0;
+        if (m) {
+            if (l == (unsigned) (__ffs(m) - 1)) base = atomicAdd(&a.q->n_alloc, (uint32_t) __popc(m));
+            base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+            slot = base + __popc(m & ((1u << l) - 1u));
+        }
+    }
+    if (keep) {
+        const WVPlanes &p = a.p; const V2 fp = box ? L.pos : L.sample_pos;
+        wv_rng_store(p, slot, L.smp);
+        p.o[slot] = make_float4(L.ray.o.x, L.ray.o.y, L.ray.o.z, L.ray.maxt);
+        p.d[slot] = make_float4(L.ray.d.x, L.ray.d.y, L.ray.d.z, __uint_as_float(f));
+        p.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(0u));
+        p.hit[slot] = wf_hit4(h);
+        p.res[slot] = make_float4(0.f, 0.f, 0.f, 1.f);
+        p.lsp[slot] = make_float4(0.f, 0.f, 0.f, 1.f);
+        p.lane[slot] = make_float4(__uint_as_float((uint32_t) lane), __uint_as_float((uint32_t) (lane >> 32)), fp.x, fp.y);
+    }
+    wv_route(sc, a, slot, keep, f, h);
+}
+
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_gen(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; unsigned long long nsamples = 0;
+    const unsigned l = threadIdx.x & 31u; const uint64_t n_total = a.lane_end - a.lane_begin;
+    for (;;) {
+        unsigned long long base = ~0ull;
+        if (l == 0) {
+            const uint32_t used = *(volatile uint32_t *) &a.q->n_alloc;
+            if (used + a.slack <= a.cap && *(volatile unsigned long long *) a.lane_next < n_total) base = atomicAdd(a.lane_next, 32ull);
+        }
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base == ~0ull || base >= n_total) break;
+        const bool have = base + l < n_total; const uint64_t lane = a.lane_begin + base + l;
+        Sampler smp; smp.state = smp.inc = 0;
+        if (have) seed_sampler(sc, smp, a.seed, lane, a.spp_per_pass, a.n_passes);
+        wv_start_paths<C, TO_FILM>(sc, a, have, lane, 0u, smp, false, 0u, cnt, nsamples);
+    }
+    flush_counters(cnt, nsamples, a.stats);
+}
+
+// later passes of lanes whose path has ended (multi-pass renders only)
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_regen(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; unsigned long long nsamples = 0;
+    WF_FOR_QUEUE(a.q->n_regen) {
+        const bool item = qi < _n; const uint32_t slot = item ? a.q_regen[qi] : 0;
+        Sampler smp; smp.state = smp.inc = 0; uint64_t lane = 0; uint32_t pass = 0;
+        if (item) {
+            smp = wv_rng(a.p, slot); smp.advance(a.spp_per_pass);
+            const float4 lp = a.p.lane[slot]; lane = ((uint64_t) __float_as_uint(lp.y) << 32) | __float_as_uint(lp.x);
+            pass = (__float_as_uint(a.p.d[slot].w) >> WF_PASS_SHIFT) + 1u;
+        }
+        wv_start_paths<C, TO_FILM>(sc, a, item, lane, pass, smp, true, slot, cnt, nsamples);
     }
     flush_counters(cnt, nsamples, a.stats);
 }
 
 // ------------------------------------------------------------------------------------------
-// TRACK: volpath.cpp:160-253 -- russian roulette, free-flight sampling, null collisions in registers
+// TRACE: persistent ray queries over a queue of slots (lr_trace.cuh).
+//   MODE 0  closest hit of the path's next ray, then routing (wv_route)
+//   MODE 1  shadow ray, any hit decides (production tracking, no index-matched boundaries in the scene)
+//   MODE 2  shadow ray, closest hit kept for the NEE walk (reference-order tracking / scenes with null boundaries)
+// ------------------------------------------------------------------------------------------
+template <int MODE>
+__global__ void __launch_bounds__(256, LR_TRACE_OCC) k_wv_trace(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    extern __shared__ int s_stack[];                                  // [bvh4_stack][256]
+    int *stack = s_stack + threadIdx.x; const int stride = 256;
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+    const uint32_t *q_in = MODE == 0 ? a.q_trace : a.q_shadow;
+    const uint32_t n_items = MODE == 0 ? a.q->n_trace : a.q->n_shadow;
+    uint32_t *cursor = &a.q->cursor[MODE == 0 ? 0 : 2];
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    TraceRay r; r.node = -2; r.sp = 0; r.tmax = 0.f; r.o = r.d = r.inv = r.ood = mk3(0.f); r.h.t = LR_INF; r.h.prim = 0xffffffffu; r.h.u = r.h.v = 0.f;
+    uint32_t slot = 0; bool exhausted = false;
+    for (;;) {
+        const unsigned walking = __ballot_sync(0xffffffffu, r.node >= 0);
+        if (__popc(walking) <= 32 - LR_TRACE_REFILL || (exhausted && __any_sync(0xffffffffu, r.node == -1))) {
+            // ---- parked lanes: write the result out, hand the path to its next stage ----
+            const bool done = r.node == -1;
+            if (MODE == 0) {
+                uint32_t f = 0;
+                if (done) { a.p.hit[slot] = wf_hit4(r.h); f = __float_as_uint(a.p.d[slot].w); }
+                wv_route(sc, a, slot, done, f, r.h);
+            } else {
+                bool walk = false;
+                if (done) {
+                    bool blocked = false;
+                    if (MODE == 1) blocked = hit_valid(r.h);
+                    else if (sc.integ.tracking == LR_TRACKING_DDA && hit_valid(r.h)) {
+                        // production tracking: a non-null surface anywhere on the segment makes the transmittance exactly 0
+                        // (eval_null_transmission, volpath.cpp:528-543), so the walk is skipped; only the RNG consumption differs
+                        blocked = true;
+                        if (sc.any_null_bsdf) {
+                            const float4 o4 = a.p.no[slot], d4 = a.p.nd[slot]; Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
+                            cnt.rays++; blocked = hit_valid(bvh_trace<true, true>(sc, ray));
+                        }
+                    }
+                    if (!blocked) {
+                        const float4 w = a.p.nw[slot];
+                        if (__float_as_int(w.w) < 0 && !hit_valid(r.h)) {      // nothing but vacuum up to the emitter: transmittance 1
+                            float4 r4 = a.p.res[slot]; r4.x += w.x; r4.y += w.y; r4.z += w.z; a.p.res[slot] = r4;
+                        } else { walk = true; if (MODE == 2) a.p.nhit[slot] = wf_hit4(r.h); }
+                    }
+                }
+                wf_push(a.q_nee, &a.q->n_nee, slot, walk);
+            }
+            if (done) r.node = -2;
+            // ---- refill ----
+            if (!exhausted) {
+                const unsigned idle = ~walking; uint32_t base = 0;
+                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(cursor, (uint32_t) __popc(idle));
+                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+                exhausted = base + (uint32_t) __popc(idle) >= n_items;
+                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+                if ((idle >> lane) & 1u) {
+                    if (qi < n_items) {
+                        slot = q_in[qi];
+                        const float4 o4 = MODE == 0 ? a.p.o[slot] : a.p.no[slot], d4 = MODE == 0 ? a.p.d[slot] : a.p.nd[slot];
+                        trace_begin(sc, r, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w); cnt.rays++;
+                    }
+                }
+            }
+        }
+        if (r.node >= 0) trace_step<MODE == 1, false>(sc, r, stack, stride);
+        if (exhausted && !__any_sync(0xffffffffu, r.node != -2)) break;
+    }
+    flush_counters(cnt, 0, a.stats);
+}
+
+// ------------------------------------------------------------------------------------------
+// TRACK: volpath.cpp:160-253 for paths inside a medium.  The russian roulette that opens the iteration was drawn by the
+// stage that spawned the ray; further loop iterations of the reference (after a null collision) draw theirs here.
+// Events: 0 end of path, 1 real scatter, 2 boundary / escape.
 // ------------------------------------------------------------------------------------------
 template <int C, bool TO_FILM>
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+LR_DEV void wv_track_out(const DScene &sc, const WVArgs &a, uint32_t slot, int event, const Sampler &smp, const Ray &ray, V3 thr, uint32_t depth, float hit_t,
+                         uint32_t f, const Hit &h0) {
+    const WVPlanes &p = a.p;
+    const bool fin = event == 0; float4 lp = make_float4(0.f, 0.f, 0.f, 0.f); V3 L = mk3(0.f);
+    if (event >= 0) wv_rng_store(p, slot, smp);
+    if (fin) { lp = p.lane[slot]; const float4 r4 = p.res[slot]; L = mk3(r4.x, r4.y, r4.z); }
+    wv_finish<C, TO_FILM>(sc, a, fin, lp, L, f);
+    if (event > 0) {
+        p.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+        p.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
+        p.hit[slot].x = hit_t;
+    }
+    const bool esc = event == 2 && !hit_valid(h0);
+    const uint32_t b = (event == 2 && !esc) ? wv_bucket(sc, h0) : 0xffu;
+    wf_push(a.q_regen, &a.q->n_regen, slot, fin && wv_more_passes(a, f));
+    wf_push(a.q_scatter, &a.q->n_scatter, slot, event == 1);
+    wf_push(a.q_escape, &a.q->n_escape, slot, esc);
+#pragma unroll
+    for (uint32_t k = 0; k < WF_N_SURF; ++k) wf_push(a.q_surf[k], &a.q->n_surf[k], slot, b == k);
+}
+
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
-    const uint32_t *q_in = a.q_active[a.cur];
-    WF_FOR_QUEUE(a.q->n_active[a.cur]) {
-        bool item = qi < _n; uint32_t slot = item ? q_in[qi] : 0; WState *S = a.st + slot;
-        int event = -1;                                   // -1 none, 0 end of path, 1 scatter, 2.. surface bucket
+    const WVPlanes &p = a.p;
+    WF_FOR_QUEUE(a.q->n_track) {
+        const bool item = qi < _n; const uint32_t slot = item ? a.q_track[qi] : 0;
+        int event = -1; Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f; V3 thr = mk3(0.f);
+        uint32_t depth = 0, f = 0; float hit_t = 0.f; Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
         if (item) {
-            Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
-            float4 t4 = S->o_maxt; Ray ray; ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
-            t4 = S->d_eta; ray.d = mk3(t4.x, t4.y, t4.z); float eta = t4.w;
-            t4 = S->thr_lpdf; V3 thr = mk3(t4.x, t4.y, t4.z); float lpdf = t4.w;
-            float4 h4 = S->hit; float hit_t = h4.x;
-            float4 lf = S->lsp_flags; uint32_t f = __float_as_uint(lf.w); V3 lsp = mk3(lf.x, lf.y, lf.z);
-            uint32_t depth = __float_as_uint(S->res_depth.w);
+            smp = wv_rng(p, slot);
+            float4 t4 = p.o[slot]; ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+            t4 = p.d[slot]; ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
+            t4 = p.thr[slot]; thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
+            h0 = wf_hit(p.hit[slot]); hit_t = h0.t;
+            const float eta = p.res[slot].w;
             const uint32_t channel = f & WF_CHANNEL_MASK; const int medium = wf_medium(f);
-            for (;;) {
-                bool active = any_nonzero(thr);
-                float q = fminf(hmax(thr) * sqr(eta), .95f);
-                bool perform_rr = depth > (uint32_t) sc.rr_depth;
-                if (active) { float u = smp.next_1d(); active &= (u < q) || !perform_rr; }
-                if (perform_rr) thr *= 1.f / q;
-                active &= depth < sc.max_depth;
-                if (!active) { event = 0; break; }
-                if (medium >= 0 && medium_uses_dda(sc, sc.media[medium])) {
+            const DMedium &m = sc.media[medium];
+            for (bool first = true;; first = false) {
+                if (!first && !wv_rr(sc, smp, thr, eta, depth)) { event = 0; break; }
+                if (medium_uses_dda(sc, m)) {
                     // production tracking: delta tracking against the local majorants of the super-grid.  The majorant is one
                     // scalar for all channels (heterogeneous.cpp:163), so Tr/pdf reduces to 1/mu at a collision and 1 at a surface.
-                    const DMedium &m = sc.media[medium]; const DGrid &g = sc.grids[m.m.sigma_t_grid];
+                    const DGrid &g = sc.grids[m.m.sigma_t_grid];
                     float mint, maxt;
                     if (medium_clip(g, ray, mint, maxt)) {
                         const float t_end = fminf(maxt, hit_t);
@@ -199,74 +353,56 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track(const __grid_consta
                             DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
                             while (dda_walk(g, m.m.scale, dd, t, tau, t_end, mu)) {
                                 cnt.collisions++;
-                                V3 p = ray_at(ray, t);
-                                V3 st = grid_eval<false>(g, p, nullptr) * m.m.scale, sn = mk3(mu) - st;
+                                V3 pt = ray_at(ray, t);
+                                V3 st = grid_eval<false>(g, pt, nullptr) * m.m.scale, sn = mk3(mu) - st;
                                 float pn = hmean(sn / mu);
                                 if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); continue; }
-                                depth += 1; lsp = p; cnt.real_scatters++;
+                                depth += 1; cnt.real_scatters++; p.lsp[slot] = make_float4(pt.x, pt.y, pt.z, p.lsp[slot].w);
                                 if (!(depth < sc.max_depth)) { event = 0; break; }
-                                thr *= (st * medium_albedo(sc, m, p)) / (mu * hmean(st / mu));
-                                ray.o = p; hit_t = hit_t - t; event = 1; break;
+                                thr *= (st * medium_albedo(sc, m, pt)) / (mu * hmean(st / mu));
+                                ray.o = pt; hit_t = hit_t - t; event = 1; break;
                             }
                         }
                     }
                     if (event < 0) event = 2;
                     break;
                 }
-                if (medium >= 0) {
-                    const DMedium &m = sc.media[medium];
-                    MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
-                    if (hit_t < mei.t) mei.t = LR_INF;
-                    const bool is_spectral = m.m.has_spectral_extinction != 0;
-                    if (is_spectral) {
-                        float t = fminf(mei.t, hit_t) - mei.mint;
-                        V3 tr = exp3(mei.combined_extinction * (-t));
-                        V3 pdf = hit_t < mei.t ? tr : tr * mei.combined_extinction;
-                        float tr_pdf = idx3(pdf, channel);
-                        thr *= tr_pdf > 0.f ? tr / tr_pdf : mk3(0.f);
-                    }
-                    if (mei_valid(mei)) {
-                        float null_scatter_prob = hmean(mei.sigma_n / mei.combined_extinction);
-                        if (smp.next_1d() < null_scatter_prob) {                       // null collision: stay in the loop
-                            if (is_spectral) thr *= mei.sigma_n / null_scatter_prob;
-                            ray.o = mei.p; hit_t = hit_t - mei.t;
-                            continue;
-                        }
-                        depth += 1; lsp = mei.p; cnt.real_scatters++;
-                        if (!(depth < sc.max_depth)) { event = 0; break; }
-                        if (is_spectral) thr *= mei.sigma_s / hmean(mei.sigma_t / mei.combined_extinction);
-                        else thr *= mei.sigma_s / mei.sigma_t;
-                        ray.o = mei.p; event = 1; break;
-                    }
+                MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
+                if (hit_t < mei.t) mei.t = LR_INF;
+                const bool is_spectral = m.m.has_spectral_extinction != 0;
+                if (is_spectral) {
+                    float t = fminf(mei.t, hit_t) - mei.mint;
+                    V3 tr = exp3(mei.combined_extinction * (-t));
+                    V3 pdf = hit_t < mei.t ? tr : tr * mei.combined_extinction;
+                    float tr_pdf = idx3(pdf, channel);
+                    thr *= tr_pdf > 0.f ? tr / tr_pdf : mk3(0.f);
                 }
-                event = 2; break;                          // surface interaction or escape (bucket chosen below)
-            }
-            if (event == 0) {
-                float4 r4 = S->res_depth; wf_finish<C, TO_FILM>(sc, a, *S, mk3(r4.x, r4.y, r4.z), f);
-                S->rng_state = smp.state; S->rng_inc = smp.inc;        // a later pass of this lane continues the stream
-            } else {
-                if (event == 2) event = 2 + wf_surf_bucket(sc, a.tris_gid, wf_hit(h4));
-                S->rng_state = smp.state; S->rng_inc = smp.inc;
-                S->o_maxt = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
-                S->thr_lpdf = make_float4(thr.x, thr.y, thr.z, lpdf);
-                S->hit.x = hit_t; S->res_depth.w = __uint_as_float(depth);
-                S->lsp_flags = make_float4(lsp.x, lsp.y, lsp.z, __uint_as_float(f));
+                if (mei_valid(mei)) {
+                    float null_scatter_prob = hmean(mei.sigma_n / mei.combined_extinction);
+                    if (smp.next_1d() < null_scatter_prob) {                       // null collision: next loop iteration of the reference
+                        if (is_spectral) thr *= mei.sigma_n / null_scatter_prob;
+                        ray.o = mei.p; hit_t = hit_t - mei.t;
+                        continue;
+                    }
+                    depth += 1; cnt.real_scatters++; p.lsp[slot] = make_float4(mei.p.x, mei.p.y, mei.p.z, p.lsp[slot].w);
+                    if (!(depth < sc.max_depth)) { event = 0; break; }
+                    if (is_spectral) thr *= mei.sigma_s / hmean(mei.sigma_t / mei.combined_extinction);
+                    else thr *= mei.sigma_s / mei.sigma_t;
+                    ray.o = mei.p; event = 1; break;
+                }
+                event = 2; break;
             }
         }
-        wf_push(a.q_regen, &a.q->n_regen, slot, event == 0);
-        wf_push(a.q_scatter, &a.q->n_scatter, slot, event == 1);
-#pragma unroll
-        for (int b = 0; b < WF_N_SURF; ++b) wf_push(a.q_surf[b], &a.q->n_surf[b], slot, event == 2 + b);
+        wv_track_out<C, TO_FILM>(sc, a, slot, event, smp, ray, thr, depth, hit_t, f, h0);
     }
     flush_counters(cnt, 0, a.stats);
 }
 
-// TRACK for scenes whose media all use the majorant-DDA (production mode): the same per-item work as k_wf_track, run as a
+// TRACK for scenes whose media all use the majorant DDA (production mode): the same per-item work as k_wv_track, run as a
 // persistent "while-while" loop.  The number of super-voxels a free flight crosses is roughly exponentially distributed, so a
-// warp that waits for its longest walk keeps 4-5 of 32 lanes busy (ncu source view of k_wf_track: lr_medium.cuh:101-118 at 4.5
-// threads per instruction).  Here a lane that has finished its item writes it out and, once half of the warp is idle, the idle
-// lanes pull the next queue entries (one atomicAdd on q->cursor per refill), so the walk loop stays populated.  Per-lane RNG
-// draw order is unchanged: RR, first optical depth, then (null test, next optical depth) per tentative collision.
+// warp that waits for its longest walk keeps 4-5 of 32 lanes busy; here a lane that has finished its item parks, and once
+// half of the warp is parked the parked lanes are written out and pull the next queue entries (one atomicAdd on the cursor
+// per refill).  Per-lane RNG draw order is unchanged: first optical depth, then (null test, next optical depth) per collision.
 #ifndef LR_TRACK_REFILL
 #define LR_TRACK_REFILL 16            // refill when at most this many lanes of the warp are still walking
 #endif
@@ -274,40 +410,39 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track(const __grid_consta
 #define LR_TRACK_STEPS 6              // super-voxel steps per lane between two converged points
 #endif
 template <int C, bool TO_FILM>
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
-    const uint32_t *q_in = a.q_active[a.cur]; const uint32_t n_items = a.q->n_active[a.cur];
+    const WVPlanes &p = a.p;
+    const uint32_t n_items = a.q->n_track;
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    uint32_t slot = 0, depth = 0, f = 0; int event = -2;                  // -2 idle, -1 walking, 0 end of path, 1 scatter, 2 surface
+    uint32_t slot = 0, depth = 0, f = 0; int event = -2;                  // -2 idle, -1 walking, 0 end of path, 1 scatter, 2 boundary
     Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f; V3 thr = mk3(0.f);
     float hit_t = 0.f, t = 0.f, tau = 0.f, t_end = 0.f, mu_scale = 0.f; int grid_id = 0; DDA dd{};
+    Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
     bool exhausted = false;
     for (;;) {
         const unsigned walking = __ballot_sync(0xffffffffu, event == -1);
-        if (!exhausted && __popc(walking) <= LR_TRACK_REFILL) {
-            const unsigned idle = ~walking; uint32_t base = 0;
-            if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor, (uint32_t) __popc(idle));
-            base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
-            exhausted = base + (uint32_t) __popc(idle) >= n_items;
-            const uint32_t qi = base + (uint32_t) __popc(idle & lt);
-            if (event == -2 && qi < n_items) {
-                slot = q_in[qi]; const WState *S = a.st + slot;
-                smp.state = S->rng_state; smp.inc = S->rng_inc;
-                float4 t4 = S->o_maxt; ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
-                t4 = S->d_eta; ray.d = mk3(t4.x, t4.y, t4.z); const float eta = t4.w;
-                t4 = S->thr_lpdf; thr = mk3(t4.x, t4.y, t4.z);
-                hit_t = S->hit.x; f = __float_as_uint(S->lsp_flags.w); depth = __float_as_uint(S->res_depth.w);
-                const int medium = wf_medium(f);
-                // volpath.cpp:160-178: russian roulette, depth test
-                bool active = any_nonzero(thr);
-                float q = fminf(hmax(thr) * sqr(eta), .95f);
-                bool perform_rr = depth > (uint32_t) sc.rr_depth;
-                if (active) { float u = smp.next_1d(); active &= (u < q) || !perform_rr; }
-                if (perform_rr) thr *= 1.f / q;
-                active &= depth < sc.max_depth;
-                event = active ? 2 : 0;
-                if (active && medium >= 0) {
-                    const DMedium &m = sc.media[medium]; grid_id = m.m.sigma_t_grid; mu_scale = m.m.scale; const DGrid &g = sc.grids[grid_id];
+        if (__popc(walking) <= LR_TRACK_REFILL) {
+            // ---- write finished items out and queue them (converged: the pushes use warp ballots) ----
+            if (__any_sync(0xffffffffu, event >= 0)) {
+                wv_track_out<C, TO_FILM>(sc, a, slot, event >= 0 ? event : -1, smp, ray, thr, depth, hit_t, f, h0);
+                if (event >= 0) event = -2;
+            }
+            if (!exhausted) {
+                const unsigned idle = ~walking; uint32_t base = 0;
+                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor[1], (uint32_t) __popc(idle));
+                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+                exhausted = base + (uint32_t) __popc(idle) >= n_items;
+                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+                if (event == -2 && qi < n_items) {
+                    slot = a.q_track[qi];
+                    smp = wv_rng(p, slot);
+                    float4 t4 = p.o[slot]; ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+                    t4 = p.d[slot]; ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
+                    t4 = p.thr[slot]; thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
+                    h0 = wf_hit(p.hit[slot]); hit_t = h0.t;
+                    const DMedium &m = sc.media[wf_medium(f)]; grid_id = m.m.sigma_t_grid; mu_scale = m.m.scale; const DGrid &g = sc.grids[grid_id];
+                    event = 2;
                     float mint, maxt;
                     if (medium_clip(g, ray, mint, maxt)) {
                         t_end = fminf(maxt, hit_t);
@@ -335,325 +470,338 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_track_dda(const __grid_co
         if (collide) {
             const DGrid &g = sc.grids[grid_id]; const DMedium &m = sc.media[wf_medium(f)];
             cnt.collisions++;
-            V3 p = ray_at(ray, t);
-            V3 st = grid_eval<false>(g, p, nullptr) * mu_scale, sn = mk3(mu) - st;
+            V3 pt = ray_at(ray, t);
+            V3 st = grid_eval<false>(g, pt, nullptr) * mu_scale, sn = mk3(mu) - st;
             float pn = hmean(sn / mu);
             if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); }
             else {
                 depth += 1; cnt.real_scatters++;
-                WState *S = a.st + slot; S->lsp_flags.x = p.x; S->lsp_flags.y = p.y; S->lsp_flags.z = p.z;
+                float *lp = reinterpret_cast<float *>(p.lsp + slot); lp[0] = pt.x; lp[1] = pt.y; lp[2] = pt.z;
                 if (!(depth < sc.max_depth)) event = 0;
-                else { thr *= (st * medium_albedo(sc, m, p)) / (mu * hmean(st / mu)); ray.o = p; hit_t = hit_t - t; event = 1; }
+                else { thr *= (st * medium_albedo(sc, m, pt)) / (mu * hmean(st / mu)); ray.o = pt; hit_t = hit_t - t; event = 1; }
             }
         }
-        // ---- write finished items out and queue them (converged: wf_push uses warp ballots) ----
-        const bool fin = event >= 0;
-        if (__any_sync(0xffffffffu, fin)) {
-            WState *S = a.st + slot;
-            if (fin) {
-                S->rng_state = smp.state; S->rng_inc = smp.inc;            // a later pass of this lane continues the stream
-                if (event == 0) { float4 r4 = S->res_depth; wf_finish<C, TO_FILM>(sc, a, *S, mk3(r4.x, r4.y, r4.z), f); }
-                else {
-                    if (event == 2) event = 2 + wf_surf_bucket(sc, a.tris_gid, wf_hit(S->hit));
-                    S->o_maxt = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
-                    S->thr_lpdf.x = thr.x; S->thr_lpdf.y = thr.y; S->thr_lpdf.z = thr.z;
-                    S->hit.x = hit_t; S->res_depth.w = __uint_as_float(depth);
-                }
-            }
-            wf_push(a.q_regen, &a.q->n_regen, slot, event == 0);
-            wf_push(a.q_scatter, &a.q->n_scatter, slot, event == 1);
-#pragma unroll
-            for (int b = 0; b < WF_N_SURF; ++b) wf_push(a.q_surf[b], &a.q->n_surf[b], slot, event == 2 + b);
-            if (fin) event = -2;
-        }
-        if (exhausted && !__any_sync(0xffffffffu, event == -1)) break;
+        if (exhausted && !__any_sync(0xffffffffu, event != -2)) break;
     }
     flush_counters(cnt, 0, a.stats);
 }
 
-// NEE set-up shared by both SHADE_A kernels: Scene::sample_emitter_direction + the first lines of
-// VolumetricPathIntegrator::sample_emitter (volpath.cpp:400-452), plus the shadow ray's closest hit.
-LR_DEV bool wf_nee_setup(const DScene &sc, const WFArgs &a, WState *S, Sampler &smp, V3 ref_p, V3 ref_n, const SurfaceInteraction *ref_si,
-                         int medium, DirectionSample &ds, Counters &cnt) {
-    V3 emitter_val; ds = sample_emitter_direction(sc, ref_p, smp.next_2d(), emitter_val);
+// ------------------------------------------------------------------------------------------
+// SHADE_A: emitter sampling (Scene::sample_emitter_direction + the first lines of VolumetricPathIntegrator::sample_emitter,
+// volpath.cpp:400-452).  The shadow ray is written to the NEE planes; TRACE_S / NEE finish the estimate.
+// ------------------------------------------------------------------------------------------
+LR_DEV bool wv_nee_setup(const DScene &sc, const WVArgs &a, uint32_t slot, Sampler &smp, V3 ref_p, V3 ref_n, const SurfaceInteraction *ref_si,
+                         int &medium, DirectionSample &ds, V3 &emitter_val) {
+    ds = sample_emitter_direction(sc, ref_p, smp.next_2d(), emitter_val);
     if (ds.pdf == 0.f) return false;
-    Ray ray = spawn_ray_to(ref_p, ref_n, ds.p);
+    const Ray ray = spawn_ray_to(ref_p, ref_n, ds.p);
     if (ref_si && mesh_is_transition(sc, ref_si->mesh)) medium = target_medium(sc, *ref_si, ray.d);
-    cnt.rays++; Hit h;
-    // production mode without index-matched boundaries: every surface blocks a shadow ray, so the first accepted triangle decides
-    // (any-hit query, no closest hit needed); a miss leaves the whole segment to the medium walk
-    if (sc.integ.tracking == LR_TRACKING_DDA && !sc.any_null_bsdf) { h = bvh_trace<true, false>(sc, ray); if (hit_valid(h)) return false; }
-    else h = bvh_trace<false, false>(sc, ray);
-    if (sc.integ.tracking == LR_TRACKING_DDA && hit_valid(h)) {
-        // production mode: opaque-occluder pre-test.  A non-null surface anywhere on the shadow segment makes the transmittance
-        // exactly 0 (eval_null_transmission), so the ratio-tracking walk is skipped; only the RNG consumption differs.
-        bool blocked = true;
-        if (sc.any_null_bsdf) { cnt.rays++; blocked = hit_valid(bvh_trace<true, true>(sc, ray)); }
-        if (blocked) return false;
-    }
-    S->no_maxd = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
-    S->nd_total = make_float4(ray.d.x, ray.d.y, ray.d.z, 0.f);
-    S->ne_dist = make_float4(emitter_val.x, emitter_val.y, emitter_val.z, ds.dist);
-    S->nhit = wf_hit4(h);
-    S->nw_med.w = __int_as_float(medium);
+    a.p.no[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+    a.p.nd[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ds.dist);
     return true;
 }
 
-// SHADE_A, medium scatter (volpath.cpp:256-283)
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
-    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+// medium scatter (volpath.cpp:256-283)
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_shade_a_medium(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    const WVPlanes &p = a.p;
     WF_FOR_QUEUE(a.q->n_scatter) {
-        bool item = qi < _n, nee = false; uint32_t slot = item ? a.q_scatter[qi] : 0;
+        const bool item = qi < _n; bool nee = false; const uint32_t slot = item ? a.q_scatter[qi] : 0;
         if (item) {
-            WState *S = a.st + slot;
-            Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
-            uint32_t f = wf_flags(*S); int medium = wf_medium(f);
+            const float4 d4 = p.d[slot]; uint32_t f = __float_as_uint(d4.w); const int medium = wf_medium(f);
             const DMedium &m = sc.media[medium]; Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
-            bool sample_emitters = m.m.sample_emitters != 0;
-            f |= WF_VALID_RAY; f = sample_emitters ? (f & ~WF_SPEC_CHAIN) : (f | WF_SPEC_CHAIN); f &= ~(WF_NEE_ACTIVE | WF_DEAD);
+            const bool sample_emitters = m.m.sample_emitters != 0;
+            const uint32_t f0 = f; int walk_medium = medium;
+            f |= WF_VALID_RAY; f = sample_emitters ? (f & ~WF_SPEC_CHAIN) : (f | WF_SPEC_CHAIN);
             if (sample_emitters) {
-                float4 o = S->o_maxt, d = S->d_eta, t = S->thr_lpdf; V3 p = mk3(o.x, o.y, o.z), wi = -mk3(d.x, d.y, d.z), thr = mk3(t.x, t.y, t.z);
-                DirectionSample ds;
-                if (wf_nee_setup(sc, a, S, smp, p, mk3(0.f), nullptr, medium, ds, cnt)) {
-                    float phase_val = phase.eval_pdf(wi, ds.d); V3 w = thr * phase_val;
-                    S->ntr_mis = make_float4(1.f, 1.f, 1.f, mis_weight(ds.pdf, ds.delta ? 0.f : phase_val));
-                    S->nw_med.x = w.x; S->nw_med.y = w.y; S->nw_med.z = w.z;
-                    f |= WF_NEE_ACTIVE;
+                Sampler smp = wv_rng(p, slot);
+                const float4 o4 = p.o[slot], t4 = p.thr[slot]; const V3 pt = mk3(o4.x, o4.y, o4.z), wi = -mk3(d4.x, d4.y, d4.z), thr = mk3(t4.x, t4.y, t4.z);
+                DirectionSample ds; V3 ev;
+                if (wv_nee_setup(sc, a, slot, smp, pt, mk3(0.f), nullptr, walk_medium, ds, ev)) {
+                    const float phase_val = phase.eval_pdf(wi, ds.d);
+                    const V3 w = thr * phase_val * mis_weight(ds.pdf, ds.delta ? 0.f : phase_val) * ev;
+                    p.nw[slot] = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
+                    nee = true;
                 }
-                S->rng_state = smp.state; S->rng_inc = smp.inc;
+                wv_rng_store(p, slot, smp);
             }
-            S->lsp_flags.w = __uint_as_float(f); nee = (f & WF_NEE_ACTIVE) != 0;
+            if (f != f0) reinterpret_cast<float *>(p.d + slot)[3] = __uint_as_float(f);
         }
-        wf_push(a.q_nee, &a.q->n_nee, slot, nee);
+        wf_push(a.q_shadow, &a.q->n_shadow, slot, nee);
     }
-    flush_counters(cnt, 0, a.stats);
 }
 
-// SHADE_A, surface / escape (volpath.cpp:300-362)
+// surface (volpath.cpp:300-362); every item has a valid hit (escaped rays have their own queue)
 template <int C, bool TO_FILM>
-__global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wf_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
+__global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_a_surface(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a, int bucket) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+    const WVPlanes &p = a.p;
     WF_FOR_QUEUE(a.q->n_surf[bucket]) {
-        bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool dead = false, nee = false;
+        const bool item = qi < _n; const uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool nee = false, gone = false; uint32_t f = 0;
         if (item) {
-            WState *S = a.st + slot;
-            Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
-            uint32_t f = wf_flags(*S) & ~(WF_NEE_ACTIVE | WF_DEAD); int medium = wf_medium(f);
-            float4 o = S->o_maxt, d = S->d_eta, t = S->thr_lpdf, r4 = S->res_depth;
-            Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
-            V3 thr = mk3(t.x, t.y, t.z), result = mk3(r4.x, r4.y, r4.z); uint32_t depth = __float_as_uint(r4.w);
-            Hit h = wf_hit(S->hit);
-            SurfaceInteraction si = compute_si(sc, ray, h, a.tris_gid);
+            Sampler smp = wv_rng(p, slot);
+            const float4 o4 = p.o[slot], d4 = p.d[slot], t4 = p.thr[slot];
+            f = __float_as_uint(d4.w); const uint32_t depth = __float_as_uint(t4.w); const int medium = wf_medium(f);
+            Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
+            const V3 thr = mk3(t4.x, t4.y, t4.z);
+            Hit h = wf_hit(p.hit[slot]);
+            SurfaceInteraction si = compute_si(sc, ray, h, sc.tris_gid);
             // the segment started outside any medium <=> the reference intersected in this very iteration (`intersect`, :301-303)
-            if (sc.hide_emitters && medium < 0 && depth == 0u && si_valid(si) && sc.meshes[si.mesh].emitter >= 0) {        // :307-323
-                Ray r2 = spawn_ray(si.p, si.n, ray.d); Hit pi = skip_area_emitters(sc, a.tris_gid, r2, cnt);
-                si = compute_si(sc, r2, pi, a.tris_gid); h = pi; S->hit = wf_hit4(h);
-                S->o_maxt = make_float4(r2.o.x, r2.o.y, r2.o.z, r2.maxt);       // SHADE_B recomputes si from (ray, hit): keep them consistent
+            if (sc.hide_emitters && medium < 0 && depth == 0u && sc.meshes[si.mesh].emitter >= 0) {                     // :307-323
+                Ray r2 = spawn_ray(si.p, si.n, ray.d); Hit pi = skip_area_emitters(sc, sc.tris_gid, r2, cnt);
+                si = compute_si(sc, r2, pi, sc.tris_gid); h = pi; p.hit[slot] = wf_hit4(h);
+                p.o[slot] = make_float4(r2.o.x, r2.o.y, r2.o.z, r2.maxt);         // SHADE_B recomputes si from (ray, hit): keep them consistent
             }
-            bool count_direct = depth == 0u || (f & WF_SPEC_CHAIN);
-            int emitter = emitter_of(sc, si);
+            const bool count_direct = depth == 0u || (f & WF_SPEC_CHAIN);
+            const int emitter = emitter_of(sc, si);
             if (emitter >= 0 && !(depth == 0u && sc.hide_emitters)) {                                                     // :326-345
+                const float4 l4 = p.lsp[slot];
                 float emitter_pdf = 1.f;
-                if (!count_direct) { float4 l = S->lsp_flags; DirectionSample ds = ds_from_si(sc, si, mk3(l.x, l.y, l.z)); emitter_pdf = pdf_emitter_direction(sc, ds); }
-                V3 emitted = eval_emitter_at(sc, emitter, si);
-                result += count_direct ? thr * emitted : thr * mis_weight(t.w, emitter_pdf) * emitted;
+                if (!count_direct) { DirectionSample ds = ds_from_si(sc, si, mk3(l4.x, l4.y, l4.z)); emitter_pdf = pdf_emitter_direction(sc, ds); }
+                const V3 emitted = eval_emitter_at(sc, emitter, si);
+                const V3 c = count_direct ? thr * emitted : thr * mis_weight(l4.w, emitter_pdf) * emitted;
+                float4 r4 = p.res[slot]; r4.x += c.x; r4.y += c.y; r4.z += c.z; p.res[slot] = r4;
             }
-            if (!si_valid(si)) {                                   // escaped to the environment: the path ends here
-                dead = true; f |= WF_DEAD; wf_finish<C, TO_FILM>(sc, a, *S, result, f);
+            if (!si_valid(si)) {                                   // only after the hidden-emitter skip above: nothing behind the emitter
+                gone = true; f |= WF_DEAD; reinterpret_cast<float *>(p.d + slot)[3] = __uint_as_float(f);
             } else {
                 BSDF bsdf(sc, si);
                 if ((bsdf.flags() & F_SMOOTH) && (depth + 1 < sc.max_depth)) {                                           // :350-362
-                    DirectionSample ds;
-                    if (wf_nee_setup(sc, a, S, smp, si.p, si.n, &si, medium, ds, cnt)) {
-                        V3 wo = si.sh.to_local(ds.d); float bsdf_pdf; V3 bsdf_val = bsdf.eval_pdf(si.wi, wo, bsdf_pdf);
-                        V3 w = thr * bsdf_val;
-                        S->ntr_mis = make_float4(1.f, 1.f, 1.f, mis_weight(ds.pdf, ds.delta ? 0.f : bsdf_pdf));
-                        S->nw_med.x = w.x; S->nw_med.y = w.y; S->nw_med.z = w.z;
-                        f |= WF_NEE_ACTIVE;
+                    DirectionSample ds; V3 ev; int walk_medium = medium;
+                    if (wv_nee_setup(sc, a, slot, smp, si.p, si.n, &si, walk_medium, ds, ev)) {
+                        const V3 wo = si.sh.to_local(ds.d); float bsdf_pdf; const V3 bsdf_val = bsdf.eval_pdf(si.wi, wo, bsdf_pdf);
+                        const V3 w = thr * bsdf_val * mis_weight(ds.pdf, ds.delta ? 0.f : bsdf_pdf) * ev;
+                        p.nw[slot] = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
+                        nee = true;
                     }
+                    wv_rng_store(p, slot, smp);
                 }
             }
-            S->rng_state = smp.state; S->rng_inc = smp.inc;
-            S->res_depth = make_float4(result.x, result.y, result.z, r4.w);
-            S->lsp_flags.w = __uint_as_float(f); nee = (f & WF_NEE_ACTIVE) != 0;
         }
-        wf_push(a.q_regen, &a.q->n_regen, slot, dead);
-        wf_push(a.q_nee, &a.q->n_nee, slot, nee);
+        {
+            float4 lp = make_float4(0.f, 0.f, 0.f, 0.f); V3 L = mk3(0.f);
+            if (gone) { lp = p.lane[slot]; const float4 r4 = p.res[slot]; L = mk3(r4.x, r4.y, r4.z); }
+            wv_finish<C, TO_FILM>(sc, a, gone, lp, L, f);
+        }
+        wf_push(a.q_regen, &a.q->n_regen, slot, gone && wv_more_passes(a, f));
+        wf_push(a.q_shadow, &a.q->n_shadow, slot, nee);
     }
     flush_counters(cnt, 0, a.stats);
 }
 
+// rays that left the scene (volpath.cpp:326-345 with an invalid si): environment radiance + MIS, then the path ends
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_escape(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    const WVPlanes &p = a.p;
+    WF_FOR_QUEUE(a.q->n_escape) {
+        const bool item = qi < _n; const uint32_t slot = item ? a.q_escape[qi] : 0;
+        V3 L = mk3(0.f); uint32_t f = 0; float4 lp = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (item) {
+            const float4 d4 = p.d[slot], t4 = p.thr[slot], r4 = p.res[slot]; lp = p.lane[slot];
+            f = __float_as_uint(d4.w); const uint32_t depth = __float_as_uint(t4.w);
+            L = mk3(r4.x, r4.y, r4.z);
+            if (sc.env >= 0 && !(depth == 0u && sc.hide_emitters)) {
+                const V3 dir = mk3(d4.x, d4.y, d4.z), thr = mk3(t4.x, t4.y, t4.z);
+                const bool count_direct = depth == 0u || (f & WF_SPEC_CHAIN);
+                const V3 emitted = emitter_eval(sc, sc.env, -dir.z, dir);
+                if (count_direct) L += thr * emitted;
+                else {
+                    DirectionSample ds; ds.d = dir; ds.emitter = sc.env; ds.dist = 0.f; ds.n = ds.p = mk3(0.f); ds.uv = mk2(0.f, 0.f); ds.pdf = 0.f; ds.delta = false;
+                    L += thr * mis_weight(p.lsp[slot].w, pdf_emitter_direction(sc, ds)) * emitted;
+                }
+            }
+        }
+        wv_finish<C, TO_FILM>(sc, a, item, lp, L, f);
+        wf_push(a.q_regen, &a.q->n_regen, slot, item && wv_more_passes(a, f));
+    }
+}
+
 // ------------------------------------------------------------------------------------------
-// NEE: transmittance along the shadow segment (volpath.cpp:454-551), ratio tracking through media and
-// index-matched (null) boundaries.  Runs over the NEE queue the SHADE_A kernels fill.
+// NEE: transmittance along the shadow segment (volpath.cpp:454-551), ratio tracking through media and index-matched
+// (null) boundaries, over the slots TRACE_S let through.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_nee(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, uint32_t surf_mask) {
-    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; (void) surf_mask;
-    {
-    const uint32_t *queue = a.q_nee;
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_nee(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a, int have_nhit) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+    const WVPlanes &p = a.p;
     WF_FOR_QUEUE(a.q->n_nee) {
         if (qi < _n) {
-            WState *S = a.st + queue[qi]; uint32_t f = wf_flags(*S);
-            if ((f & WF_NEE_ACTIVE) && !(f & WF_DEAD)) {
-                Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
-                const uint32_t channel = f & WF_CHANNEL_MASK;
-                float4 o = S->no_maxd, d = S->nd_total; Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z);
-                const float max_dist = o.w, ds_dist = S->ne_dist.w; float total_dist = 0.f;
-                int medium = __float_as_int(S->nw_med.w);
-                Hit h = wf_hit(S->nhit); float si_t = h.t; bool needs_intersection = false, active = true;
-                V3 transmittance = mk3(1.f);
-                while (active) {
-                    float remaining_dist = max_dist - total_dist; ray.maxt = remaining_dist;
-                    active &= remaining_dist > 0.f;
-                    if (!active) break;
-                    bool escaped_medium = false, active_medium = medium >= 0, active_surface = !active_medium; float mei_t = LR_INF;
-                    if (active_medium && medium_uses_dda(sc, sc.media[medium])) {
-                        // ratio tracking over the whole medium segment against the local majorants: T *= sigma_n / mu per tentative collision
-                        const DMedium &m = sc.media[medium]; const DGrid &g = sc.grids[m.m.sigma_t_grid];
-                        if (needs_intersection) { cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false; }
-                        float mint, maxt;
-                        if (medium_clip(g, ray, mint, maxt)) {
-                            const float t_end = fminf(maxt, si_t);
-                            if (mint < t_end) {
-                                DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
-                                while (dda_walk(g, m.m.scale, dd, t, tau, t_end, mu)) {
-                                    cnt.collisions++;
-                                    V3 st = grid_eval<false>(g, ray_at(ray, t), nullptr) * m.m.scale;
-                                    transmittance *= (mk3(mu) - st) / mu;
-                                    if (!any_nonzero(transmittance)) break;
-                                    tau = -logf(1.f - smp.next_1d());
-                                }
+            const uint32_t slot = a.q_nee[qi];
+            Sampler smp = wv_rng(p, slot);
+            const uint32_t channel = __float_as_uint(p.d[slot].w) & WF_CHANNEL_MASK;
+            const float4 o4 = p.no[slot], d4 = p.nd[slot], w4 = p.nw[slot];
+            Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z);
+            const float max_dist = o4.w, ds_dist = d4.w; float total_dist = 0.f;
+            int medium = __float_as_int(w4.w);
+            Hit h; h.t = LR_INF; h.prim = 0xffffffffu; h.u = h.v = 0.f;
+            if (have_nhit) h = wf_hit(p.nhit[slot]);
+            float si_t = h.t; bool needs_intersection = false, active = true;
+            V3 transmittance = mk3(1.f);
+            while (active) {
+                float remaining_dist = max_dist - total_dist; ray.maxt = remaining_dist;
+                active &= remaining_dist > 0.f;
+                if (!active) break;
+                bool escaped_medium = false, active_medium = medium >= 0, active_surface = !active_medium;
+                if (active_medium && medium_uses_dda(sc, sc.media[medium])) {
+                    // ratio tracking over the whole medium segment against the local majorants: T *= sigma_n / mu per tentative collision
+                    const DMedium &m = sc.media[medium]; const DGrid &g = sc.grids[m.m.sigma_t_grid];
+                    if (needs_intersection) { cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false; }
+                    float mint, maxt;
+                    if (medium_clip(g, ray, mint, maxt)) {
+                        const float t_end = fminf(maxt, si_t);
+                        if (mint < t_end) {
+                            DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
+                            while (dda_walk(g, m.m.scale, dd, t, tau, t_end, mu)) {
+                                cnt.collisions++;
+                                V3 st = grid_eval<false>(g, ray_at(ray, t), nullptr) * m.m.scale;
+                                transmittance *= (mk3(mu) - st) / mu;
+                                if (!any_nonzero(transmittance)) break;
+                                tau = -logf(1.f - smp.next_1d());
                             }
                         }
-                        if (si_t > remaining_dist) total_dist = ds_dist;        // nothing but medium up to the emitter (volpath.cpp:494-496)
-                        escaped_medium = true; active_medium = false;
-                    } else if (active_medium) {
-                        const DMedium &m = sc.media[medium];
-                        MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
-                        if (needs_intersection) {
-                            if (m.m.kind == LR_MEDIUM_HOMOGENEOUS && mei_valid(mei)) ray.maxt = fminf(mei.t, remaining_dist);
-                            cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false;
-                        }
-                        if (si_t < mei.t) mei.t = LR_INF;
-                        const bool is_spectral = m.m.has_spectral_extinction != 0;
-                        if (is_spectral) {
-                            float t = fminf(remaining_dist, fminf(mei.t, si_t)) - mei.mint;
-                            V3 tr = exp3(mei.combined_extinction * (-t));
-                            V3 ffp = (si_t < mei.t || mei.t > remaining_dist) ? tr : tr * mei.combined_extinction;
-                            float tr_pdf = idx3(ffp, channel);
-                            transmittance *= tr_pdf > 0.f ? tr / tr_pdf : mk3(0.f);
-                        }
-                        if (mei.t > remaining_dist && mei_valid(mei)) total_dist = ds_dist;
-                        if (mei.t > remaining_dist) mei.t = LR_INF;
-                        escaped_medium = !mei_valid(mei); active_medium = mei_valid(mei);
-                        if (active_medium) {
-                            total_dist += mei.t; ray.o = mei.p; si_t = si_t - mei.t;
-                            if (is_spectral) transmittance *= mei.sigma_n; else transmittance *= mei.sigma_n / mei.combined_extinction;
-                        }
-                        mei_t = mei.t;
                     }
-                    if (active_surface && needs_intersection) { cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false; }
-                    active_surface |= escaped_medium;
-                    if (active_surface) total_dist += si_t;
-                    active_surface &= (si_t != LR_INF) && !active_medium;
-                    SurfaceInteraction si;
-                    if (active_surface) {
-                        h.t = si_t; si = compute_si(sc, ray, h, a.tris_gid);
-                        BSDF bsdf(sc, si);
-                        transmittance *= bsdf.eval_null_transmission();
-                        Ray r2 = spawn_ray(si.p, si.n, ray.d); ray.o = r2.o;
+                    if (si_t > remaining_dist) total_dist = ds_dist;        // nothing but medium up to the emitter (volpath.cpp:494-496)
+                    escaped_medium = true; active_medium = false;
+                } else if (active_medium) {
+                    const DMedium &m = sc.media[medium];
+                    MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
+                    if (needs_intersection) {
+                        if (m.m.kind == LR_MEDIUM_HOMOGENEOUS && mei_valid(mei)) ray.maxt = fminf(mei.t, remaining_dist);
+                        cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false;
                     }
-                    ray.maxt = remaining_dist;
-                    needs_intersection |= active_surface;
-                    active &= (active_medium || active_surface) && any_nonzero(transmittance);
-                    if (active_surface && mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
-                    (void) mei_t;
+                    if (si_t < mei.t) mei.t = LR_INF;
+                    const bool is_spectral = m.m.has_spectral_extinction != 0;
+                    if (is_spectral) {
+                        float t = fminf(remaining_dist, fminf(mei.t, si_t)) - mei.mint;
+                        V3 tr = exp3(mei.combined_extinction * (-t));
+                        V3 ffp = (si_t < mei.t || mei.t > remaining_dist) ? tr : tr * mei.combined_extinction;
+                        float tr_pdf = idx3(ffp, channel);
+                        transmittance *= tr_pdf > 0.f ? tr / tr_pdf : mk3(0.f);
+                    }
+                    if (mei.t > remaining_dist && mei_valid(mei)) total_dist = ds_dist;
+                    if (mei.t > remaining_dist) mei.t = LR_INF;
+                    escaped_medium = !mei_valid(mei); active_medium = mei_valid(mei);
+                    if (active_medium) {
+                        total_dist += mei.t; ray.o = mei.p; si_t = si_t - mei.t;
+                        if (is_spectral) transmittance *= mei.sigma_n; else transmittance *= mei.sigma_n / mei.combined_extinction;
+                    }
                 }
-                // result += throughput * (phase | bsdf) value * mis * (transmittance * emitter_val)     (:279-283, :356-361)
-                float4 w = S->nw_med, e = S->ne_dist, r4 = S->res_depth; float mis = S->ntr_mis.w;
-                V3 emitted = transmittance * mk3(e.x, e.y, e.z);
-                V3 res = mk3(r4.x, r4.y, r4.z) + mk3(w.x, w.y, w.z) * mis * emitted;
-                S->res_depth = make_float4(res.x, res.y, res.z, r4.w);
-                S->rng_state = smp.state; S->rng_inc = smp.inc;
+                if (active_surface && needs_intersection) { cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false; }
+                active_surface |= escaped_medium;
+                if (active_surface) total_dist += si_t;
+                active_surface &= (si_t != LR_INF) && !active_medium;
+                SurfaceInteraction si;
+                if (active_surface) {
+                    h.t = si_t; si = compute_si(sc, ray, h, sc.tris_gid);
+                    BSDF bsdf(sc, si);
+                    transmittance *= bsdf.eval_null_transmission();
+                    Ray r2 = spawn_ray(si.p, si.n, ray.d); ray.o = r2.o;
+                }
+                ray.maxt = remaining_dist;
+                needs_intersection |= active_surface;
+                active &= (active_medium || active_surface) && any_nonzero(transmittance);
+                if (active_surface && mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
             }
+            // result += throughput * (phase | bsdf) value * mis * emitter_val * transmittance     (:279-283, :356-361)
+            float4 r4 = p.res[slot];
+            r4.x = fmaf(w4.x, transmittance.x, r4.x); r4.y = fmaf(w4.y, transmittance.y, r4.y); r4.z = fmaf(w4.z, transmittance.z, r4.z);
+            p.res[slot] = r4;
+            wv_rng_store(p, slot, smp);
         }
-    }
     }
     flush_counters(cnt, 0, a.stats);
 }
 
-// SHADE_B, medium scatter: phase-function sampling (volpath.cpp:285-297) + closest hit of the new ray
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wf_shade_b_medium(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a) {
-    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
-    uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
+// ------------------------------------------------------------------------------------------
+// SHADE_B: direction sampling, then the russian roulette + depth test of the next loop iteration.
+// ------------------------------------------------------------------------------------------
+// medium scatter: phase-function sampling (volpath.cpp:285-297)
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_shade_b_medium(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    const WVPlanes &p = a.p;
+    uint32_t *q_out = a.q_trace, *n_out = &a.q->n_trace;
     WF_FOR_QUEUE(a.q->n_scatter) {
-        bool item = qi < _n; uint32_t slot = item ? a.q_scatter[qi] : 0;
+        const bool item = qi < _n; const uint32_t slot = item ? a.q_scatter[qi] : 0;
+        bool alive = false; uint32_t f = 0; V3 L = mk3(0.f); float4 lp = make_float4(0.f, 0.f, 0.f, 0.f);
         if (item) {
-            WState *S = a.st + slot;
-            Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
-            const DMedium &m = sc.media[wf_medium(wf_flags(*S))]; Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
-            float4 o = S->o_maxt, d = S->d_eta;
-            (void) smp.next_1d(); V2 s2 = smp.next_2d();
-            float phase_pdf; V3 wo = phase.sample(-mk3(d.x, d.y, d.z), s2, phase_pdf);
-            Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
-            if (phase_pdf > 0.f) { ray.d = wo; ray.maxt = LR_LARGEST; S->thr_lpdf.w = phase_pdf; }
-            cnt.rays++; Hit h = bvh_trace<false, false>(sc, ray);
-            S->rng_state = smp.state; S->rng_inc = smp.inc;
-            S->o_maxt.w = ray.maxt; S->d_eta = make_float4(ray.d.x, ray.d.y, ray.d.z, d.w); S->hit = wf_hit4(h);
-        }
-        wf_push(q_out, n_out, slot, item);
-    }
-    flush_counters(cnt, 0, a.stats);
-}
-
-// SHADE_B, surface: BSDF sampling, next ray, medium transition (volpath.cpp:364-389)
-__global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wf_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WFArgs a, int bucket) {
-    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
-    uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
-    WF_FOR_QUEUE(a.q->n_surf[bucket]) {
-        bool item = qi < _n; uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool live = false;
-        if (item) {
-            WState *S = a.st + slot; uint32_t f = wf_flags(*S);
-            if (!(f & WF_DEAD)) {
-                live = true;
-                Sampler smp; smp.state = S->rng_state; smp.inc = S->rng_inc;
-                float4 o = S->o_maxt, d = S->d_eta, t = S->thr_lpdf;
-                Ray ray; ray.o = mk3(o.x, o.y, o.z); ray.d = mk3(d.x, d.y, d.z); ray.maxt = o.w;
-                SurfaceInteraction si = compute_si(sc, ray, wf_hit(S->hit), a.tris_gid);
-                BSDF bsdf(sc, si);
-                float s1 = smp.next_1d(); V2 s2 = smp.next_2d();
-                V3 bsdf_val; BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_val);
-                V3 thr = mk3(t.x, t.y, t.z) * bsdf_val; float eta = d.w * bs.eta, lpdf = t.w;
-                ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
-                bool non_null = !(bs.sampled_type & F_NULL);
-                if (non_null) {
-                    S->res_depth.w = __uint_as_float(__float_as_uint(S->res_depth.w) + 1u);
-                    S->lsp_flags.x = si.p.x; S->lsp_flags.y = si.p.y; S->lsp_flags.z = si.p.z; lpdf = bs.pdf; f |= WF_VALID_RAY;
+            Sampler smp = wv_rng(p, slot);
+            const float4 d4 = p.d[slot], t4 = p.thr[slot], r4 = p.res[slot]; f = __float_as_uint(d4.w);
+            const DMedium &m = sc.media[wf_medium(f)]; Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
+            (void) smp.next_1d(); const V2 s2 = smp.next_2d();
+            float phase_pdf; const V3 wo = phase.sample(-mk3(d4.x, d4.y, d4.z), s2, phase_pdf);
+            V3 thr = mk3(t4.x, t4.y, t4.z); const uint32_t depth = __float_as_uint(t4.w);
+            alive = wv_rr(sc, smp, thr, r4.w, depth);
+            wv_rng_store(p, slot, smp);
+            if (alive) {
+                if (phase_pdf > 0.f) {
+                    p.d[slot] = make_float4(wo.x, wo.y, wo.z, d4.w);
+                    reinterpret_cast<float *>(p.o + slot)[3] = LR_LARGEST; reinterpret_cast<float *>(p.lsp + slot)[3] = phase_pdf;
                 }
-                bool spec = (f & WF_SPEC_CHAIN) != 0;
-                spec |= non_null && (bs.sampled_type & F_DELTA); spec &= !(bs.sampled_type & F_SMOOTH);
-                f = spec ? (f | WF_SPEC_CHAIN) : (f & ~WF_SPEC_CHAIN);
-                if (mesh_is_transition(sc, si.mesh)) f = wf_set_medium(f, target_medium(sc, si, ray.d));
-                cnt.rays++; Hit h = bvh_trace<false, false>(sc, ray);
-                S->rng_state = smp.state; S->rng_inc = smp.inc;
-                S->o_maxt = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt); S->d_eta = make_float4(ray.d.x, ray.d.y, ray.d.z, eta);
-                S->thr_lpdf = make_float4(thr.x, thr.y, thr.z, lpdf); S->hit = wf_hit4(h);
-                S->lsp_flags.w = __uint_as_float(f);
-            }
+                p.thr[slot] = make_float4(thr.x, thr.y, thr.z, t4.w);
+            } else { L = mk3(r4.x, r4.y, r4.z); lp = p.lane[slot]; }
         }
-        wf_push(q_out, n_out, slot, live);
+        wv_finish<C, TO_FILM>(sc, a, item && !alive, lp, L, f);
+        wf_push(q_out, n_out, slot, alive);
+        wf_push(a.q_regen, &a.q->n_regen, slot, item && !alive && wv_more_passes(a, f));
     }
-    flush_counters(cnt, 0, a.stats);
 }
 
-__global__ void k_wf_begin_iteration(WQueues *q, int cur) {     // counters of the queues this iteration fills
-    q->n_active[cur ^ 1] = 0; q->n_scatter = 0; q->n_regen = 0; q->n_nee = 0; q->cursor = 0;
-    for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
+// surface: BSDF sampling, next ray, medium transition (volpath.cpp:364-389)
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_b_surface(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a, int bucket) {
+    const WVPlanes &p = a.p;
+    uint32_t *q_out = a.q_trace, *n_out = &a.q->n_trace;
+    WF_FOR_QUEUE(a.q->n_surf[bucket]) {
+        bool item = qi < _n; const uint32_t slot = item ? a.q_surf[bucket][qi] : 0;
+        bool alive = false; uint32_t f = 0; V3 L = mk3(0.f); float4 lp = make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 d4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (item) { d4 = p.d[slot]; f = __float_as_uint(d4.w); item = !(f & WF_DEAD); }        // WF_DEAD: finished by SHADE_A (hidden-emitter skip)
+        if (item) {
+            Sampler smp = wv_rng(p, slot);
+            const float4 o4 = p.o[slot], t4 = p.thr[slot], r4 = p.res[slot];
+            Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
+            const SurfaceInteraction si = compute_si(sc, ray, wf_hit(p.hit[slot]), sc.tris_gid);
+            BSDF bsdf(sc, si);
+            const float s1 = smp.next_1d(); const V2 s2 = smp.next_2d();
+            V3 bsdf_val; const BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_val);
+            V3 thr = mk3(t4.x, t4.y, t4.z) * bsdf_val; const float eta = r4.w * bs.eta; uint32_t depth = __float_as_uint(t4.w);
+            ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
+            const bool non_null = !(bs.sampled_type & F_NULL);
+            if (non_null) { depth += 1u; p.lsp[slot] = make_float4(si.p.x, si.p.y, si.p.z, bs.pdf); f |= WF_VALID_RAY; }
+            bool spec = (f & WF_SPEC_CHAIN) != 0;
+            spec |= non_null && (bs.sampled_type & F_DELTA); spec &= !(bs.sampled_type & F_SMOOTH);
+            f = spec ? (f | WF_SPEC_CHAIN) : (f & ~WF_SPEC_CHAIN);
+            if (mesh_is_transition(sc, si.mesh)) f = wf_set_medium(f, target_medium(sc, si, ray.d));
+            alive = wv_rr(sc, smp, thr, eta, depth);
+            wv_rng_store(p, slot, smp);
+            if (alive) {
+                p.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+                p.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(f));
+                p.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
+                if (eta != r4.w) reinterpret_cast<float *>(p.res + slot)[3] = eta;
+            } else { L = mk3(r4.x, r4.y, r4.z); lp = p.lane[slot]; }
+        }
+        wv_finish<C, TO_FILM>(sc, a, item && !alive, lp, L, f);
+        wf_push(q_out, n_out, slot, alive);
+        wf_push(a.q_regen, &a.q->n_regen, slot, item && !alive && wv_more_passes(a, f));
+    }
 }
-__global__ void k_wf_init(WQueues *q, uint32_t *q_regen, uint32_t cap, WState *st) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i == 0) { q->n_active[0] = q->n_active[1] = 0; q->n_scatter = 0; q->n_regen = cap; q->lane_next = 0; q->n_nee = 0; q->cursor = 0; for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0; }
-    if (i < cap) { q_regen[i] = i; st[i].lsp_flags.w = __uint_as_float(0u); }
+
+// counters of the queues the second half of an iteration fills (after SHADE_B has consumed the scatter / surface queues)
+__global__ void k_wv_mid_iteration(WVQueues *q) {
+    q->n_track = 0; q->n_scatter = 0; q->n_escape = 0; q->n_shadow = 0; q->n_nee = 0;
+    for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
+    q->cursor[0] = q->cursor[1] = q->cursor[2] = 0;
+}
+// end of an iteration: what is still alive; the consumed trace / regen queues are emptied
+__global__ void k_wv_end_iteration(WVQueues *q, uint32_t *live_out, const unsigned long long *lane_next, unsigned long long *lane_next_out) {
+    uint32_t live = q->n_track + q->n_escape;
+    for (int b = 0; b < WF_N_SURF; ++b) live += q->n_surf[b];
+    q->live = live; q->n_trace = 0; q->n_regen = 0;
+    *live_out = live; *lane_next_out = *lane_next;
+}
+__global__ void k_wv_init(WVQueues *q) {
+    q->n_trace = 0; q->n_track = q->n_scatter = q->n_escape = q->n_shadow = q->n_nee = q->n_regen = 0;
+    for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
+    q->cursor[0] = q->cursor[1] = q->cursor[2] = 0; q->n_alloc = 0; q->live = 0;
 }
 
 } // namespace lr

@@ -1,11 +1,11 @@
-// lr_wavefront_host.inl -- host driver of the wavefront `volpath` (kernels: lr_wavefront.cuh).
-// Included by lr_backend_api.inl.  One render = GEN, then iterations of
-//   TRACK -> SHADE_A (medium, surface buckets) -> NEE -> SHADE_B (medium, surface buckets) -> GEN
-// until the active queue stays empty.  The host never waits for an iteration it has just enqueued: the live
-// count of iteration i is read back asynchronously and checked three iterations later, so the stream stays full.
+// lr_wavefront_host.inl -- host drivers of the wavefront `volpath` (kernels: lr_wavefront.cuh) and `prbvolpath`
+// (lr_wavefront_prb.cuh).  Included by lr_backend_api.inl.  One forward batch = GEN, then iterations of
+//   TRACK -> SHADE_A (medium, surface buckets) -> ESCAPE -> TRACE_S -> NEE -> SHADE_B (medium, surface buckets) -> TRACE_C [-> REGEN]
+// until nothing is alive.  The host never waits for an iteration it has just enqueued.
 
 static const int WF_RING = 8, WF_LAG = 3;
 
+// ---- legacy AoS pool of the wavefront prbvolpath ----
 static int wf_alloc(lr_ctx *c, WavefrontBuffers *&wp, uint64_t want) {
     if (!wp) wp = new WavefrontBuffers();
     WavefrontBuffers &w = *wp;
@@ -22,23 +22,11 @@ static int wf_alloc(lr_ctx *c, WavefrontBuffers *&wp, uint64_t want) {
     }
     return LR_OK;
 }
-
-// `two_runs`: also set up the second pool + stream used when a lane range is rendered as overlapped batches
-static int wf_prepare(lr_ctx *c, uint64_t n_lanes, bool two_runs = false) {
+static int wf_prepare(lr_ctx *c, uint64_t n_lanes) {
     uint64_t want = std::min<uint64_t>(c->wf_pool_slots, (n_lanes + 31) & ~31ull);
     want = std::max<uint64_t>(want, 1024);
-    if (int r = wf_alloc(c, c->wf, want)) return r;
-    if (two_runs && n_lanes > c->wf->cap) {
-        uint64_t batches = (n_lanes + c->wf->cap - 1) / c->wf->cap;
-        for (int k = 0; k + 1 < c->wf_runs && (uint64_t) (k + 1) < batches; ++k) {
-            if (int r = wf_alloc(c, c->wf_more[k], c->wf->cap)) return r;
-            if (!c->stream_more[k]) LR_CUDA(c, cudaStreamCreateWithFlags(&c->stream_more[k], cudaStreamNonBlocking));
-        }
-        if (!c->fork_ev) LR_CUDA(c, cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
-    }
-    return LR_OK;
+    return wf_alloc(c, c->wf, want);
 }
-
 static void wf_bind(WFArgs &a, WavefrontBuffers &w) {
     a.st = w.states.as<WState>(); a.q = w.counters.as<WQueues>(); a.cap = w.cap;
     uint32_t *qb = w.queues.as<uint32_t>();
@@ -47,90 +35,172 @@ static void wf_bind(WFArgs &a, WavefrontBuffers &w) {
     a.q_nee = qb + (4 + WF_N_SURF) * (size_t) w.cap;
 }
 
+// ---------------------------------------------------------------------------------------------
+// forward wavefront (kernels: lr_wavefront.cuh)
+// ---------------------------------------------------------------------------------------------
+// stage kinds of the per-stage profile (lr_profile_get)
+enum { ST_GEN = 0, ST_TRACE_C, ST_TRACK, ST_SHADE_A_MED, ST_SHADE_A_SURF, ST_ESCAPE, ST_TRACE_S, ST_NEE, ST_SHADE_B_MED, ST_SHADE_B_SURF, ST_REGEN, ST_OTHER, ST_COUNT };
+static const char *const kStageNames[ST_COUNT] = { "gen", "trace_closest", "track", "shade_a_medium", "shade_a_surface", "escape", "trace_shadow", "nee",
+                                                  "shade_b_medium", "shade_b_surface", "regen", "other" };
+
+static int wv_alloc(lr_ctx *c, WVPool *&wp, uint64_t want) {
+    if (!wp) wp = new WVPool();
+    WVPool &w = *wp;
+    if (w.cap < want) {
+        w.cap = (uint32_t) want;
+        LR_CUDA(c, w.planes.alloc((size_t) w.cap * 16 * WV_N_PLANES));
+        LR_CUDA(c, w.queues.alloc((size_t) w.cap * 4 * WV_N_QUEUES));
+        LR_CUDA(c, w.counters.alloc(sizeof(WVQueues)));
+    }
+    if (!w.ring_host) {
+        LR_CUDA(c, cudaHostAlloc((void **) &w.ring_host, WF_RING * sizeof(WVRing), cudaHostAllocMapped));
+        LR_CUDA(c, cudaHostGetDevicePointer((void **) &w.ring_dev, w.ring_host, 0));
+        w.ring_ev.resize(WF_RING);
+        for (auto &e : w.ring_ev) LR_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    return LR_OK;
+}
+
+// pools for a render of `n_lanes` lanes: one pool of min(wf_pool_slots, n_lanes) slots, further ones when the lanes cannot all be
+// resident at once (they may: primary rays that leave the scene never take a slot)
+static int wv_prepare(lr_ctx *c, uint64_t n_lanes) {
+    uint64_t want = std::min<uint64_t>(c->wf_pool_slots, (n_lanes + 31) & ~31ull);
+    want = std::max<uint64_t>(want, 1024);
+    if (int r = wv_alloc(c, c->wv[0], want)) return r;
+    const int runs = c->profile_on ? 1 : c->wf_runs;
+    if (n_lanes > c->wv[0]->cap) {
+        uint64_t batches = (n_lanes + c->wv[0]->cap - 1) / c->wv[0]->cap;
+        for (int k = 1; k < runs && (uint64_t) k < batches; ++k) {
+            if (int r = wv_alloc(c, c->wv[k], c->wv[0]->cap)) return r;
+            if (!c->stream_more[k - 1]) LR_CUDA(c, cudaStreamCreateWithFlags(&c->stream_more[k - 1], cudaStreamNonBlocking));
+        }
+        if (!c->fork_ev) LR_CUDA(c, cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
+    }
+    if (!c->lane_cursor.p) LR_CUDA(c, c->lane_cursor.alloc(8));
+    return LR_OK;
+}
+
+static void wv_bind(WVArgs &a, WVPool &w) {
+    char *pb = (char *) w.planes.p; const size_t ps = (size_t) w.cap * 16;
+    a.p.rng = (ulonglong2 *) pb; float4 **pl[] = { &a.p.o, &a.p.d, &a.p.thr, &a.p.hit, &a.p.res, &a.p.lsp, &a.p.lane, &a.p.no, &a.p.nd, &a.p.nw, &a.p.nhit };
+    for (int k = 0; k < WV_N_PLANES - 1; ++k) *pl[k] = (float4 *) (pb + ps * (k + 1));
+    a.q = w.counters.as<WVQueues>(); a.cap = w.cap;
+    uint32_t *qb = w.queues.as<uint32_t>(); const size_t qs = w.cap;
+    a.q_trace = qb; a.q_track = qb + qs; a.q_scatter = qb + 2 * qs; a.q_escape = qb + 3 * qs; a.q_shadow = qb + 4 * qs; a.q_nee = qb + 5 * qs; a.q_regen = qb + 6 * qs;
+    for (int b = 0; b < WF_N_SURF; ++b) a.q_surf[b] = qb + (7 + b) * qs;
+}
+
 // One batch of lanes in flight on one pool + stream.
-struct WfRun {
-    WavefrontBuffers *w = nullptr; cudaStream_t s = nullptr; WFArgs a{}; uint64_t iter = 0; bool busy = false;
-    size_t kev_used = 0; std::vector<int> kev_kind;
+struct WvRun {
+    WVPool *w = nullptr; cudaStream_t s = nullptr; WVArgs a{}; uint64_t iter = 0; bool busy = false; int gen_grid = 1;
 };
 
-// The lane range is cut into batches of one pool each.  A batch runs in lock step -- every lane of it starts in the same GEN
-// launch, so iteration k holds the k-th vertex of paths whose queue order is still lane (= pixel) order: warps stay spatially
-// coherent, which is worth 15-20 % over a steady-state pool that keeps refilling freed slots with unrelated lanes.  The price
-// is the thin tail of a batch; two (LR_WF_RUNS, up to four) batches are kept in flight on separate streams so that the tail iterations (and the tail of
-// every single launch) are filled by the other batch.  Lanes are independent, so results do not depend on the batching.
+// A render is a sequence of lock-step batches.  GEN fills one pool with the lanes whose primary ray hits something (or starts
+// inside a medium) -- the others are finished inside GEN -- so iteration k of a batch holds the k-th vertex of paths whose queue
+// order is still lane (= pixel) order: warps stay spatially coherent.  The price is the thin tail of a batch, so up to wf_runs
+// batches are kept in flight on separate streams and pools: the tail iterations of one batch (and the tail of every single launch)
+// are filled by the others.  All batches draw their lanes from one device-side cursor; lanes are independent, so results do not
+// depend on the batching.  The host never waits for an iteration it has just enqueued: the live count of iteration i is written
+// to mapped pinned memory by the iteration itself and checked WF_LAG iterations later.
 template <int C, bool TO_FILM>
 static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
-    const uint64_t cap = c->wf->cap, n_lanes = ra.lane_end - ra.lane_begin;
-    WfRun runs[4]; runs[0].w = c->wf; runs[0].s = c->stream; int n_runs = 1;
-    if (n_lanes > cap) {
-        const uint64_t batches = (n_lanes + cap - 1) / cap;
-        for (int k = 0; k < 3 && n_runs < c->wf_runs && (uint64_t) n_runs < batches && c->wf_more[k] && c->wf_more[k]->cap >= cap; ++k) {
-            runs[n_runs].w = c->wf_more[k]; runs[n_runs].s = c->stream_more[k]; ++n_runs; }
+    const uint64_t cap = c->wv[0]->cap, n_lanes = ra.lane_end - ra.lane_begin;
+    const bool prof = c->profile_on;
+    WvRun runs[4]; int n_runs = 0;
+    for (int k = 0; k < (prof ? 1 : c->wf_runs) && k < 4; ++k) {
+        if (!c->wv[k] || c->wv[k]->cap < cap) break;
+        if (k > 0 && n_lanes <= cap) break;
+        runs[k].w = c->wv[k]; runs[k].s = k == 0 ? c->stream : c->stream_more[k - 1]; ++n_runs;
     }
     if (n_runs > 1) {                                                  // the extra streams start after whatever is queued on the caller's stream
         LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream));
         for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0));
     }
-    const uint32_t surf_mask = 1u | c->surf_bucket_mask;             // surface buckets present in this scene (bucket 0 also takes escaped rays)
-    const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128;   // blocks per SM handed to the grid-stride stage kernels (LR_WF_GRID / LR_WF_GRID128)
-    uint64_t launches = 0, next = ra.lane_begin;
-    auto timed = [&](WfRun &r, int kind) -> cudaEvent_t * {           // {start, stop} events for a TRACK (0) / NEE (1) launch
-        auto &kev = r.w->kev;
-        if (r.kev_used + 2 > kev.size()) { size_t n0 = kev.size(); kev.resize(n0 + 512); for (size_t i = n0; i < kev.size(); ++i) cudaEventCreate(&kev[i]); }
-        r.kev_kind.push_back(kind); r.kev_used += 2; return &kev[r.kev_used - 2];
+    LR_CUDA(c, cudaMemsetAsync(c->lane_cursor.p, 0, 8, c->stream));
+    if (n_runs > 1) { LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream)); for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0)); }
+    const uint32_t surf_mask = c->surf_bucket_mask;                    // surface buckets present in this scene
+    const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128, grid_tr = c->n_sm * LR_TRACE_OCC;
+    const size_t smem_tr = (size_t) c->sc.bvh4_stack * 256 * sizeof(int);
+    const bool multipass = ra.n_passes > 1;
+    const int shadow_mode = (c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf) ? 1 : 2;
+    uint64_t launches = 0; bool lanes_done = false; const bool dbg_sync = getenv("LR_WF_SYNC") != nullptr;
+    // per-stage CUDA events (profile mode: one batch in flight, so the intervals do not overlap)
+    std::vector<cudaEvent_t> &kev = c->prof_ev; size_t kev_used = 0; std::vector<int> kev_kind;
+    auto launch = [&](WvRun &r, int kind, auto &&fn) {
+        cudaEvent_t *e = nullptr;
+        if (prof) {
+            if (kev_used + 2 > kev.size()) { size_t n0 = kev.size(); kev.resize(n0 + 1024); for (size_t i = n0; i < kev.size(); ++i) cudaEventCreate(&kev[i]); }
+            e = &kev[kev_used]; kev_used += 2; kev_kind.push_back(kind); cudaEventRecord(e[0], r.s);
+        }
+        fn(); ++launches;
+        if (prof) cudaEventRecord(e[1], r.s);
+        if (dbg_sync) {                                                // LR_WF_SYNC=1: find the stage a device fault comes from
+            cudaError_t err = cudaStreamSynchronize(r.s);
+            if (err != cudaSuccess) { fprintf(stderr, "[lr] stage %s (iteration %llu): %s\n", kStageNames[kind], (unsigned long long) r.iter, cudaGetErrorString(err)); }
+        }
     };
-    auto start = [&](WfRun &r) -> int {                                // 1: a batch was started, 0: no lanes left
-        if (next >= ra.lane_end) return 0;
-        WFArgs &a = r.a; a = WFArgs{}; wf_bind(a, *r.w);
-        a.tris_gid = ra.tris_gid; a.film = ra.film; a.seed = ra.seed; a.spp_per_pass = ra.spp_per_pass; a.n_passes = ra.n_passes; a.stats = ra.stats;
-        a.lane_begin = next; a.lane_end = std::min<uint64_t>(ra.lane_end, next + cap); next = a.lane_end;
-        a.lanes_out = ra.lanes_out ? ra.lanes_out + (a.lane_begin - ra.lane_begin) * ra.n_passes * 4 : nullptr;
-        k_wf_init<<<(r.w->cap + 255) / 256, 256, 0, r.s>>>(a.q, a.q_regen, r.w->cap, a.st);
-        a.cur = 0; k_wf_gen<<<grid, 256, 0, r.s>>>(c->sc, a); a.cur = 1; launches += 2;
+    auto readback = [&](WvRun &r) -> int {                             // live count + lane cursor of the work enqueued so far -> ring slot
+        WVPool &w = *r.w; int slot = (int) (r.iter % WF_RING);
+        k_wv_end_iteration<<<1, 1, 0, r.s>>>(r.a.q, &w.ring_dev[slot].live, (const unsigned long long *) c->lane_cursor.p, &w.ring_dev[slot].lane_next);
+        if (cudaEventRecord(w.ring_ev[slot], r.s) != cudaSuccess) return -1;
+        ++r.iter; ++launches;
+        return cudaGetLastError() == cudaSuccess ? 0 : -1;
+    };
+    auto start = [&](WvRun &r) -> int {                                // a new batch on this pool
+        WVArgs &a = r.a; a = WVArgs{}; wv_bind(a, *r.w);
+        a.film = ra.film; a.lanes_out = ra.lanes_out; a.seed = ra.seed; a.spp_per_pass = ra.spp_per_pass; a.n_passes = ra.n_passes; a.stats = ra.stats;
+        a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end; a.lane_next = (unsigned long long *) c->lane_cursor.p;
+        // GEN hands out lanes while n_alloc + slack <= cap; slack = 32 slots per resident warp of the GEN grid bounds the overshoot
+        r.gen_grid = (int) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) grid, a.cap / 512)); a.slack = (uint32_t) r.gen_grid * 256u;
+        k_wv_init<<<1, 1, 0, r.s>>>(a.q); ++launches;
+        launch(r, ST_GEN, [&] { k_wv_gen<C, TO_FILM><<<r.gen_grid, 256, 0, r.s>>>(c->sc, a); });
         r.iter = 0; r.busy = true;
-        return 1;
+        return readback(r);
     };
-    auto step = [&](WfRun &r) -> int {                                 // enqueue one iteration; 1: the batch has drained
-        WFArgs &a = r.a; cudaStream_t s = r.s; WavefrontBuffers &w = *r.w;
+    auto step = [&](WvRun &r) -> int {                                 // enqueue one iteration; 1: the batch has drained
+        WVArgs &a = r.a; cudaStream_t s = r.s; WVPool &w = *r.w;
         if (r.iter >= (uint64_t) WF_LAG) {
             int slot = (int) ((r.iter - WF_LAG) % WF_RING);
             if (cudaEventSynchronize(w.ring_ev[slot]) != cudaSuccess) return -1;
-            if (w.live_host[slot] == 0 || *c->cancel_host) { r.busy = false; return 1; }
+            if (w.ring_host[slot].lane_next >= n_lanes) lanes_done = true;
+            if (w.ring_host[slot].live == 0 || *c->cancel_host) { r.busy = false; return 1; }
         }
-        k_wf_begin_iteration<<<1, 1, 0, s>>>(a.q, a.cur);
-        { cudaEvent_t *e = timed(r, 0); cudaEventRecord(e[0], s); if (c->all_media_dda) k_wf_track_dda<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wf_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); cudaEventRecord(e[1], s); }
-        k_wf_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); launches += 3;
-        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) { k_wf_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); ++launches; }
-        { cudaEvent_t *e = timed(r, 1); cudaEventRecord(e[0], s); k_wf_nee<<<grid, 256, 0, s>>>(c->sc, a, surf_mask); cudaEventRecord(e[1], s); }
-        k_wf_shade_b_medium<<<grid, 256, 0, s>>>(c->sc, a); launches += 2;
-        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) { k_wf_shade_b_surface<<<grid128, 128, 0, s>>>(c->sc, a, b); ++launches; }
-        k_wf_gen<<<grid, 256, 0, s>>>(c->sc, a); ++launches;
-        a.cur ^= 1;
-        int slot = (int) (r.iter % WF_RING);
-        if (cudaMemcpyAsync(&w.live_host[slot], &a.q->n_active[a.cur], 4, cudaMemcpyDeviceToHost, s) != cudaSuccess) return -1;
-        if (cudaEventRecord(w.ring_ev[slot], s) != cudaSuccess) return -1;
-        ++r.iter;
-        return cudaGetLastError() == cudaSuccess ? 0 : -1;
+        launch(r, ST_TRACK, [&] { if (c->all_media_dda) k_wv_track_dda<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+        launch(r, ST_SHADE_A_MED, [&] { k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); });
+        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] { k_wv_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); });
+        launch(r, ST_ESCAPE, [&] { k_wv_escape<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+        launch(r, ST_TRACE_S, [&] { if (shadow_mode == 1) k_wv_trace<1><<<grid_tr, 256, smem_tr, s>>>(c->sc, a); else k_wv_trace<2><<<grid_tr, 256, smem_tr, s>>>(c->sc, a); });
+        launch(r, ST_NEE, [&] { k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });
+        launch(r, ST_SHADE_B_MED, [&] { k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_B_SURF, [&] { k_wv_shade_b_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); });
+        k_wv_mid_iteration<<<1, 1, 0, s>>>(a.q); ++launches;
+        launch(r, ST_TRACE_C, [&] { k_wv_trace<0><<<grid_tr, 256, smem_tr, s>>>(c->sc, a); });
+        if (multipass) launch(r, ST_REGEN, [&] { k_wv_regen<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+        return readback(r);
     };
     for (bool any = true; any;) {
         any = false;
         for (int k = 0; k < n_runs; ++k) {
-            WfRun &r = runs[k];
-            if (!r.busy && (*c->cancel_host || !start(r))) continue;
+            WvRun &r = runs[k];
+            if (!r.busy) {
+                if (*c->cancel_host || lanes_done) continue;
+                if (start(r) < 0) { LR_CUDA(c, cudaGetLastError()); LR_CUDA(c, cudaDeviceSynchronize()); c->err = "wavefront batch start failed"; return LR_ERR_CUDA; }
+            }
             any = true;
             if (step(r) < 0) { LR_CUDA(c, cudaGetLastError()); LR_CUDA(c, cudaDeviceSynchronize()); c->err = "wavefront iteration failed"; return LR_ERR_CUDA; }
         }
     }
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
     for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamSynchronize(runs[k].s));
-    double ms_track = 0, ms_nee = 0; uint64_t n_track = 0, n_nee = 0;
-    for (int k = 0; k < n_runs; ++k)
-        for (size_t i = 0; i < runs[k].kev_kind.size(); ++i) {
-            float ms = 0.f; if (cudaEventElapsedTime(&ms, runs[k].w->kev[2 * i], runs[k].w->kev[2 * i + 1]) != cudaSuccess) continue;
-            if (runs[k].kev_kind[i] == 0) { ms_track += ms; ++n_track; } else { ms_nee += ms; ++n_nee; }
+    LR_CUDA(c, cudaGetLastError());
+    if (prof) {
+        for (size_t i = 0; i < kev_kind.size(); ++i) {
+            float ms = 0.f; if (cudaEventElapsedTime(&ms, kev[2 * i], kev[2 * i + 1]) != cudaSuccess) continue;
+            c->prof_ms[kev_kind[i]] += ms; c->prof_launches[kev_kind[i]] += 1;
         }
-    c->wf_launches = launches; c->wf_tracking_ms = ms_track + ms_nee; c->wf_tracking_launches = n_track + n_nee;
-    c->wf_track_ms = ms_track; c->wf_nee_ms = ms_nee;
+        c->wf_tracking_ms = c->prof_ms[ST_TRACK] + c->prof_ms[ST_NEE]; c->wf_tracking_launches = c->prof_launches[ST_TRACK] + c->prof_launches[ST_NEE];
+    }
+    c->wf_launches = launches;
     return LR_OK;
 }
 

@@ -41,7 +41,7 @@ struct WavefrontBuffers {
 // iterations write their live counts to
 struct WVRing { uint32_t live; uint32_t pad; unsigned long long lane_next; };
 struct WVPool {
-    DevBuf planes, queues, counters; uint32_t cap = 0;
+    DevBuf planes, queues, counters, trace_ovf; uint32_t cap = 0;
     WVRing *ring_host = nullptr, *ring_dev = nullptr; std::vector<cudaEvent_t> ring_ev;
     ~WVPool() { if (ring_host) cudaFreeHost(ring_host); for (auto e : ring_ev) cudaEventDestroy(e); }
 };
@@ -66,6 +66,7 @@ struct lr_ctx {
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
     WavefrontBuffers *wf = nullptr;                                    // prbvolpath pool
     WVPool *wv[4] = {nullptr, nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // forward pools: batches in flight
+    uint32_t bvh4_nodes = 0; bool bvh4_small = false; uint32_t trace_n_smem = 0, trace_sd = 1; size_t trace_smem = 0;   // trace-kernel shared-memory plan
     DevBuf lane_cursor;                                                // device-side lane cursor shared by the batches of one render
     bool profile_on = false; std::vector<cudaEvent_t> prof_ev; double prof_ms[16] = {0}; uint64_t prof_launches[16] = {0};
     cudaEvent_t fork_ev = nullptr; int wf_runs = 3, wf_grid_mult = LR_WF_OCC, wf_grid_mult128 = LR_WF_OCC_SURF;   // one resident wave of CTAs per stage launch (profiles/r1_ab_register_budgets.txt)

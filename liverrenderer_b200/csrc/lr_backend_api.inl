@@ -64,12 +64,21 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     { DevBuf *b = c->newbuf(); if (int r = upload(c, b, s->bsdfs, s->n_bsdfs)) return r; sc.bsdfs = b->as<lr_bsdf>(); }
     if (int r = build_bvh(c, tris, lo, hi)) return r;
     sc.tris_gid = c->tris_gid ? c->tris_gid->as<DTri>() : nullptr;
-    {   // the trace kernels keep their traversal stack in dynamic shared memory: bvh4_stack entries per thread
-        const size_t smem = (size_t) sc.bvh4_stack * 256 * sizeof(int);
-        if (smem > 200 * 1024) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: acceleration structure too deep (%u stack entries)", sc.bvh4_stack);
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    {   // shared-memory plan of the trace kernels (lr_trace.cuh): staged rays + the top of the tree + the first entries of every lane's stack
+        c->bvh4_small = c->bvh4_nodes < 32000 && sc.n_tris <= 32000;
+        const size_t esz = c->bvh4_small ? sizeof(short) : sizeof(int), budget = 200 * 1024;
+        c->trace_sd = std::min<uint32_t>(std::max<uint32_t>(sc.bvh4_stack, 1u), LR_TRACE_SD);
+        const size_t fixed = (size_t) 2 * LR_TRACE_THREADS * 16 + (size_t) c->trace_sd * LR_TRACE_THREADS * esz;
+        c->trace_n_smem = (uint32_t) std::min<size_t>(c->bvh4_nodes, (budget - fixed) / sizeof(DNodeQ));
+        c->trace_smem = fixed + (size_t) c->trace_n_smem * sizeof(DNodeQ);
+        if (getenv("LR_VERBOSE")) fprintf(stderr, "[lr] bvh4: %u nodes (%u in shared memory), worst-case stack %u entries (%u in shared memory), %zu B of shared memory per block\n",
+                                          c->bvh4_nodes, c->trace_n_smem, sc.bvh4_stack, c->trace_sd, c->trace_smem);
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
+        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
     }
 
     // ---- bitmap textures (reflectance / bump maps) ----

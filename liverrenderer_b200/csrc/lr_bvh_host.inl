@@ -123,13 +123,15 @@ struct Builder {
 
 // ---------------------------------------------------------------------------------------------
 // 4-wide tree for the wavefront TRACE kernels: the two-wide tree collapsed top-down (the inner child with the largest
-// surface area is replaced by its two children until the node holds four), depth-first order, root = node 0.  Child boxes
-// are the ones the two-wide nodes already carry, so both trees bound the same triangles with the same (padded) boxes.
-// Returns the worst-case number of stack entries a depth-first traversal that pushes every hit inner sibling can hold.
+// surface area is replaced by its two children until the node holds four), re-ordered breadth-first and quantized to DNodeQ
+// (lr_scene.cuh).  Child boxes are the ones the two-wide nodes already carry, rounded outward to the node's 7-bit grid, so
+// every box still contains its triangles (hits are decided by the exact triangle test, never by a box).
+// Also computes the worst-case number of stack entries of a depth-first traversal that pushes every hit sibling.
 // ---------------------------------------------------------------------------------------------
 namespace bvh4 {
 
 struct Child { int code; float lo[3], hi[3]; };
+struct Wide { Child ch[4]; int n; };                          // one collapsed node; child codes >= 0 index `wide`
 
 static void children_of(const DNode &n, Child &l, Child &r) {
     l.lo[0] = n.a.x; l.lo[1] = n.a.y; l.lo[2] = n.a.z; l.hi[0] = n.a.w; l.hi[1] = n.b.x; l.hi[2] = n.b.y;
@@ -141,55 +143,82 @@ static float half_area(const Child &c) {
 }
 
 struct Collapser {
-    const std::vector<DNode> &bin; std::vector<DNode4> out;
-    explicit Collapser(const std::vector<DNode> &b) : bin(b) { out.reserve(b.size() / 2 + 2); }
+    const std::vector<DNode> &bin; std::vector<Wide> wide;
+    explicit Collapser(const std::vector<DNode> &b) : bin(b) { wide.reserve(b.size() / 2 + 2); }
     // emits the 4-wide node for two-wide node `node`; returns its index, `need` = stack entries below it
     int emit(int node, uint32_t &need) {
-        Child ch[4]; int n = 2; children_of(bin[node], ch[0], ch[1]);
-        while (n < 4) {
+        Wide w; w.n = 2; children_of(bin[node], w.ch[0], w.ch[1]);
+        while (w.n < 4) {
             int best = -1; float best_area = -1.f;
-            for (int i = 0; i < n; ++i) if (ch[i].code >= 0) { float a = half_area(ch[i]); if (a > best_area) { best_area = a; best = i; } }
+            for (int i = 0; i < w.n; ++i) if (w.ch[i].code >= 0) { float a = half_area(w.ch[i]); if (a > best_area) { best_area = a; best = i; } }
             if (best < 0) break;
-            Child l, r; children_of(bin[ch[best].code], l, r); ch[best] = l; ch[n++] = r;
+            Child l, r; children_of(bin[w.ch[best].code], l, r); w.ch[best] = l; w.ch[w.n++] = r;
         }
-        int self = (int) out.size(); out.push_back(DNode4{});
-        DNode4 nd; float *lo[3] = { &nd.lox.x, &nd.loy.x, &nd.loz.x }, *hi[3] = { &nd.hix.x, &nd.hiy.x, &nd.hiz.x }; int *cc = &nd.child.x;
-        uint32_t inner = 0, below = 0;
-        for (int i = 0; i < 4; ++i) {
-            if (i < n) {
-                int code = ch[i].code;
-                if (code >= 0) { uint32_t nb = 0; code = emit(code, nb); below = std::max(below, nb); ++inner; }
-                for (int k = 0; k < 3; ++k) { lo[k][i] = ch[i].lo[k]; hi[k][i] = ch[i].hi[k]; }
-                cc[i] = code;
-            } else {
-                for (int k = 0; k < 3; ++k) { lo[k][i] = INFINITY; hi[k][i] = INFINITY; }      // both planes at +inf: the slab test fails for every ray
-                cc[i] = 0x7fffffff;
-            }
-        }
-        nd.pad = make_int4(0, 0, 0, 0);
-        out[self] = nd;
-        need = inner ? (inner - 1) + below : 0;
+        int self = (int) wide.size(); wide.push_back(w);
+        uint32_t below = 0;
+        for (int i = 0; i < w.n; ++i) if (w.ch[i].code >= 0) { uint32_t nb = 0; w.ch[i].code = emit(w.ch[i].code, nb); below = std::max(below, nb); }
+        wide[self] = w;
+        need = (uint32_t) (w.n - 1) + below;                  // triangles are stack entries too (they are tested when popped)
         return self;
     }
 };
+
+// quantize one collapsed node; `remap`: collapsed index -> breadth-first index
+static DNodeQ quantize(const Wide &w, const std::vector<int> &remap) {
+    float lo[3] = { INFINITY, INFINITY, INFINITY }, hi[3] = { -INFINITY, -INFINITY, -INFINITY };
+    for (int i = 0; i < w.n; ++i) for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], w.ch[i].lo[k]); hi[k] = std::max(hi[k], w.ch[i].hi[k]); }
+    auto fin = [](float v) { return std::isfinite(v) ? v : (v > 0 ? 1e30f : -1e30f); };
+    uint32_t ebits[3]; double cell[3], org[3];
+    for (int k = 0; k < 3; ++k) {
+        if (!std::isfinite(lo[k]) || !std::isfinite(hi[k])) { lo[k] = -1e30f; hi[k] = 1e30f; }       // the single-triangle node: unbounded box
+        // cell = 2^e with 126 cells covering the extent (one cell of slack on either side for the outward rounding)
+        double ext = std::max((double) hi[k] - (double) lo[k], 1e-30); int e = (int) std::ceil(std::log2(ext / 125.0));
+        e = std::max(-100, std::min(100, e)); cell[k] = std::ldexp(1.0, e); ebits[k] = (uint32_t) (e + 127);
+        // origin: an fp32 value at or below lo - one cell's worth of slack is not needed: floor() below rounds outward
+        org[k] = (double) (float) lo[k]; if (org[k] > lo[k]) org[k] = (double) std::nextafterf((float) lo[k], -INFINITY);
+    }
+    DNodeQ q; uint32_t planes[6] = { 0, 0, 0, 0, 0, 0 }; int32_t links[4];
+    for (int i = 0; i < 4; ++i) {
+        if (i >= w.n) { links[i] = 0x7fffffff; for (int k = 0; k < 3; ++k) { planes[k] |= (0x80u | 127u) << (8 * i); planes[3 + k] |= 0x80u << (8 * i); } continue; }
+        links[i] = w.ch[i].code >= 0 ? remap[w.ch[i].code] : w.ch[i].code;
+        for (int k = 0; k < 3; ++k) {
+            // outward rounding with a margin of 1e-3 cell against the fp32 evaluation order of the device
+            int ql = (int) std::floor(((double) fin(w.ch[i].lo[k]) - org[k]) / cell[k] - 1e-3), qh = (int) std::ceil(((double) fin(w.ch[i].hi[k]) - org[k]) / cell[k] + 1e-3);
+            ql = std::max(0, std::min(127, ql)); qh = std::max(0, std::min(127, qh));
+            planes[k] |= (0x80u | (uint32_t) ql) << (8 * i); planes[3 + k] |= (0x80u | (uint32_t) qh) << (8 * i);
+        }
+    }
+    float of[3] = { (float) org[0], (float) org[1], (float) org[2] }; uint32_t ob[3]; memcpy(ob, of, 12);
+    q.c0 = make_uint4(ob[0], ob[1], ob[2], ebits[0] | (ebits[1] << 8) | (ebits[2] << 16));
+    q.c1 = make_uint4((uint32_t) links[0], (uint32_t) links[1], (uint32_t) links[2], (uint32_t) links[3]);
+    q.c2 = make_uint4(planes[0], planes[1], planes[2], planes[3]);
+    q.c3 = make_uint4(planes[4], planes[5], 0u, 0u);
+    return q;
+}
 
 }  // namespace bvh4
 
 // `bin`: the two-wide nodes (host copy); uploads the collapsed tree and records it in the scene
 static int finish_bvh4(lr_ctx *c, const std::vector<DNode> &bin, const std::vector<DTri> &sorted) {
     DScene &sc = c->sc; uint32_t n = (uint32_t) sorted.size();
-    sc.nodes4 = nullptr; sc.bvh4_stack = 1;
+    sc.nodes4 = nullptr; sc.bvh4_stack = 1; sc.n_nodes4 = 0; c->bvh4_nodes = 0;
     if (n == 0) return LR_OK;
-    std::vector<DNode4> nodes4; uint32_t need = 0;
-    if (n == 1) {                                             // a single triangle: one node with one leaf child
-        DNode4 nd; float *lo[3] = { &nd.lox.x, &nd.loy.x, &nd.loz.x }, *hi[3] = { &nd.hix.x, &nd.hiy.x, &nd.hiz.x }; int *cc = &nd.child.x;
-        for (int i = 0; i < 4; ++i) { for (int k = 0; k < 3; ++k) { lo[k][i] = i ? INFINITY : -INFINITY; hi[k][i] = INFINITY; } cc[i] = i ? 0x7fffffff : ~0; }
-        nd.pad = make_int4(0, 0, 0, 0); nodes4.push_back(nd);
+    std::vector<bvh4::Wide> wide; uint32_t need = 0;
+    if (n == 1) {                                             // a single triangle: one node with one leaf child, unbounded box
+        bvh4::Wide w; w.n = 1; w.ch[0].code = ~0; for (int k = 0; k < 3; ++k) { w.ch[0].lo[k] = -INFINITY; w.ch[0].hi[k] = INFINITY; }
+        wide.push_back(w);
     } else {
-        bvh4::Collapser col(bin); col.emit(0, need); nodes4.swap(col.out);
+        bvh4::Collapser col(bin); col.emit(0, need); wide.swap(col.wide);
     }
+    // breadth-first order: the top of the tree becomes a prefix of the array
+    std::vector<int> order; order.reserve(wide.size()); std::vector<int> remap(wide.size(), -1);
+    order.push_back(0);
+    for (size_t h = 0; h < order.size(); ++h) { const bvh4::Wide &w = wide[order[h]]; for (int i = 0; i < w.n; ++i) if (w.ch[i].code >= 0) order.push_back(w.ch[i].code); }
+    for (size_t i = 0; i < order.size(); ++i) remap[order[i]] = (int) i;
+    std::vector<DNodeQ> nodes4(order.size());
+    for (size_t i = 0; i < order.size(); ++i) nodes4[i] = bvh4::quantize(wide[order[i]], remap);
     DevBuf *dn = c->newbuf(); if (int r = upload(c, dn, nodes4.data(), nodes4.size())) return r;
-    sc.nodes4 = dn->as<DNode4>(); sc.bvh4_stack = need + 1;
+    sc.nodes4 = dn->as<DNodeQ>(); sc.bvh4_stack = need + 1; sc.n_nodes4 = (uint32_t) nodes4.size(); c->bvh4_nodes = sc.n_nodes4;
     return LR_OK;
 }
 

@@ -15,10 +15,15 @@ namespace lr {
 
 struct DTri { float4 v0, v1, v2; };   // .w lanes: v0 = global primitive id, v1 = mesh id, v2 = bit 0 null-BSDF mesh, bits 1-2 surface bucket
 struct DNode { float4 a, b, c, d; };
-// 4-wide node walked by the wavefront TRACE kernels (lr_trace.cuh): the boxes of up to four children, one float4 per
-// plane (component i = child i), so a visit is six LDG.128 of box planes + one of child links.  Links: >= 0 inner node,
-// < 0 => ~k = k-th triangle of `tris`; an unused child has both planes at +inf (never hit).  128 B, cache-line aligned.
-struct __align__(16) DNode4 { float4 lox, loy, loz, hix, hiy, hiz; int4 child; int4 pad; };
+// 4-wide quantized node walked by the wavefront TRACE kernels (lr_trace.cuh), 64 B = four 16-byte chunks:
+//   chunk 0: origin.xyz (fp32), exponents ex | ey << 8 | ez << 16 (biased, as in an fp32): cell size on axis a = 2^(e_a - 127)
+//   chunk 1: child links; >= 0 inner node, < 0 => ~k = k-th triangle of `tris`, 0x7fffffff unused
+//   chunk 2: lo.x, lo.y, lo.z, hi.x -- one byte per child, 7-bit grid coordinate with bit 7 SET (0x80 | q), so that a single
+//   chunk 3: hi.y, hi.z, -, -        PRMT turns a byte into the float 1 + q/128 (bits 0x3F000000 | byte << 16)
+// Plane position = origin + q * cell; lo planes are rounded down and hi planes up on the host, so the quantized box contains the
+// exact one.  An unused child has lo = 127, hi = 0 on every axis (never hit).  Nodes are stored in breadth-first order so the top of
+// the tree -- what the trace kernels keep in shared memory -- is a prefix of the array.
+struct __align__(16) DNodeQ { uint4 c0, c1, c2, c3; };
 
 struct DMesh {
     const float *pos, *nrm, *uv; const uint32_t *idx; const float *area_cdf;
@@ -55,7 +60,7 @@ struct DEmitter {
 // so every field is a uniform constant-bank load.
 struct DScene {
     const DNode *nodes; const DTri *tris; const DMesh *meshes;
-    const DNode4 *nodes4; uint32_t bvh4_stack;      // 4-wide tree over the same `tris`; worst-case traversal stack depth (entries)
+    const DNodeQ *nodes4; uint32_t n_nodes4, bvh4_stack;      // 4-wide tree over the same `tris`; worst-case traversal stack depth (entries)
     const DTri *tris_gid;             // triangles by global primitive id (tris is in BVH order)
     const DTex *textures;
     const lr_bsdf *bsdfs; const DMedium *media; const DGrid *grids; const DEmitter *emitters;

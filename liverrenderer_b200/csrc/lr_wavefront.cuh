@@ -25,10 +25,7 @@
 #pragma once
 #include "lr_wf_common.cuh"
 #include "lr_trace.cuh"
-
-#ifndef LR_TRACE_OCC
-#define LR_TRACE_OCC 4               // resident 256-thread blocks per SM of the trace kernels
-#endif
+#include <cuda_pipeline.h>
 
 namespace lr {
 
@@ -122,14 +119,28 @@ LR_DEV void wv_finish(const DScene &sc, const WVArgs &a, bool pred, float4 lane_
 // a finished path whose lane has further passes to render (integrator.cpp:347-356: the stream simply continues)
 LR_DEV bool wv_more_passes(const WVArgs &a, uint32_t flags) { return a.n_passes > 1 && (flags >> WF_PASS_SHIFT) + 1 < a.n_passes; }
 
-// where a path with a fresh closest hit goes next
+// where a path with a fresh closest hit goes next.  One round trip for all five queues: lane k of the warp reserves the
+// entries of queue k (TRACK, ESCAPE, surface buckets), the bases travel back by shuffle.
 LR_DEV void wv_route(const DScene &sc, const WVArgs &a, uint32_t slot, bool pred, uint32_t flags, const Hit &h) {
-    const bool in_medium = pred && wf_medium(flags) >= 0, esc = pred && !in_medium && !hit_valid(h);
-    const uint32_t b = (pred && !in_medium && !esc) ? wv_bucket(sc, h) : 0xffu;
-    wf_push(a.q_track, &a.q->n_track, slot, in_medium);
-    wf_push(a.q_escape, &a.q->n_escape, slot, esc);
+    uint32_t dest = 0xffu;                                                  // 0 TRACK, 1 ESCAPE, 2.. surface bucket
+    if (pred) dest = wf_medium(flags) >= 0 ? 0u : (!hit_valid(h) ? 1u : 2u + wv_bucket(sc, h));
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned mine = 0, m[2 + WF_N_SURF];
 #pragma unroll
-    for (uint32_t k = 0; k < WF_N_SURF; ++k) wf_push(a.q_surf[k], &a.q->n_surf[k], slot, b == k);
+    for (uint32_t k = 0; k < 2 + WF_N_SURF; ++k) { m[k] = __ballot_sync(0xffffffffu, dest == k); if (dest == k) mine = m[k]; }
+    uint32_t base = 0;
+    if (lane < 2 + WF_N_SURF) {
+        unsigned mk = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < 2 + WF_N_SURF; ++k) if (lane == k) mk = m[k];
+        uint32_t *cnt = lane == 0 ? &a.q->n_track : (lane == 1 ? &a.q->n_escape : &a.q->n_surf[lane - 2]);
+        if (mk) base = atomicAdd(cnt, (uint32_t) __popc(mk));
+    }
+    base = __shfl_sync(0xffffffffu, base, dest & 31u);
+    if (pred) {
+        uint32_t *q = dest == 0 ? a.q_track : (dest == 1 ? a.q_escape : a.q_surf[dest - 2]);
+        q[base + __popc(mine & ((1u << lane) - 1u))] = slot;
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -230,26 +241,40 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_regen(const __grid_consta
 //   MODE 1  shadow ray, any hit decides (production tracking, no index-matched boundaries in the scene)
 //   MODE 2  shadow ray, closest hit kept for the NEE walk (reference-order tracking / scenes with null boundaries)
 // ------------------------------------------------------------------------------------------
-template <int MODE>
-__global__ void __launch_bounds__(256, LR_TRACE_OCC) k_wv_trace(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
-    extern __shared__ int s_stack[];                                  // [bvh4_stack][256]
-    int *stack = s_stack + threadIdx.x; const int stride = 256;
+struct TraceCfg { uint32_t n_smem, sd; int *ovf; uint32_t ovf_stride; };   // nodes held in shared memory, shared stack depth, overflow scratch
+
+template <int MODE, typename STK>
+__global__ void __launch_bounds__(LR_TRACE_THREADS, 1) k_wv_trace(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a, const __grid_constant__ TraceCfg cfg) {
+    // dynamic shared memory: [staged next rays: 2 x T float4][nodes: n_smem x 4 uint4, chunk-rotated][stack: sd x T STK]
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    float4 *s_next = reinterpret_cast<float4 *>(s_raw);
+    uint4 *s_nodes = reinterpret_cast<uint4 *>(s_raw + (size_t) 2 * LR_TRACE_THREADS * sizeof(float4));
+    TraceStack<STK> st; st.stack = reinterpret_cast<STK *>(s_nodes + (size_t) cfg.n_smem * 4u) + threadIdx.x; st.stride = LR_TRACE_THREADS; st.sd = (int) cfg.sd;
+    st.ovf = cfg.ovf + (size_t) blockIdx.x * LR_TRACE_THREADS + threadIdx.x; st.ovf_stride = (int) cfg.ovf_stride;
+    for (uint32_t i = threadIdx.x; i < cfg.n_smem * 4u; i += LR_TRACE_THREADS) {          // chunk k of node n goes to slot (k + (n >> 1)) & 3
+        const uint32_t n = i >> 2, k = i & 3u;
+        s_nodes[n * 4u + ((k + (n >> 1)) & 3u)] = reinterpret_cast<const uint4 *>(sc.nodes4)[i];
+    }
+    __syncthreads();
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     const uint32_t *q_in = MODE == 0 ? a.q_trace : a.q_shadow;
     const uint32_t n_items = MODE == 0 ? a.q->n_trace : a.q->n_shadow;
     uint32_t *cursor = &a.q->cursor[MODE == 0 ? 0 : 2];
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
-    TraceRay r; r.node = -2; r.sp = 0; r.tmax = 0.f; r.o = r.d = r.inv = r.ood = mk3(0.f); r.h.t = LR_INF; r.h.prim = 0xffffffffu; r.h.u = r.h.v = 0.f;
+    TraceRay r; r.node = TR_IDLE; r.sp = 0; r.tmax = 0.f; r.o = r.d = r.inv = r.ood = mk3(0.f); r.h.t = LR_INF; r.h.prim = 0xffffffffu; r.h.u = r.h.v = 0.f;
     uint32_t slot = 0; bool exhausted = false;
+    // queue entries are handed out in chunks per warp: one global atomic per chunk instead of one per refill
+    const uint32_t n_warps = gridDim.x * (blockDim.x >> 5);
+    const uint32_t chunk = min(256u, max(32u, (n_items / (4u * n_warps) + 31u) & ~31u));
+    uint32_t chunk_next = 0, chunk_end = 0, slot_a = 0, slot_b = 0, flags = 0; bool have_a = false, have_b = false;
     for (;;) {
-        const unsigned walking = __ballot_sync(0xffffffffu, r.node >= 0);
-        if (__popc(walking) <= 32 - LR_TRACE_REFILL || (exhausted && __any_sync(0xffffffffu, r.node == -1))) {
+        const unsigned walking = __ballot_sync(0xffffffffu, trace_walking(r));
+        if (__popc(walking) <= 32 - LR_TRACE_REFILL || (exhausted && __any_sync(0xffffffffu, r.node == TR_DONE || (r.node == TR_IDLE && (have_a || have_b))))) {
             // ---- parked lanes: write the result out, hand the path to its next stage ----
-            const bool done = r.node == -1;
+            const bool done = r.node == TR_DONE;
             if (MODE == 0) {
-                uint32_t f = 0;
-                if (done) { a.p.hit[slot] = wf_hit4(r.h); f = __float_as_uint(a.p.d[slot].w); }
-                wv_route(sc, a, slot, done, f, r.h);
+                if (done) a.p.hit[slot] = wf_hit4(r.h);
+                wv_route(sc, a, slot, done, flags, r.h);
             } else {
                 bool walk = false;
                 if (done) {
@@ -273,25 +298,47 @@ __global__ void __launch_bounds__(256, LR_TRACE_OCC) k_wv_trace(const __grid_con
                 }
                 wf_push(a.q_nee, &a.q->n_nee, slot, walk);
             }
-            if (done) r.node = -2;
-            // ---- refill ----
+            if (done) r.node = TR_IDLE;
+            // ---- refill, a three-stage pipeline per lane so that no stage waits for DRAM:
+            //      (c) an idle lane starts the ray that was staged in shared memory by an earlier refill,
+            //      (b) a lane whose staging buffer is free starts the asynchronous copy (cp.async) of the ray of the queue entry it holds,
+            //      (a) a lane that holds no queue entry claims the next one (plain load, consumed at a later refill) ----
+            if (r.node == TR_IDLE && have_b) {
+                __pipeline_wait_prior(0);
+                const float4 o4 = s_next[threadIdx.x], d4 = s_next[LR_TRACE_THREADS + threadIdx.x];
+                slot = slot_b; have_b = false; flags = __float_as_uint(d4.w);
+                trace_begin(sc, r, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w); cnt.rays++;
+            }
+            if (!have_b && have_a) {
+                slot_b = slot_a; have_a = false; have_b = true;
+                __pipeline_memcpy_async(&s_next[threadIdx.x], MODE == 0 ? &a.p.o[slot_b] : &a.p.no[slot_b], 16);
+                __pipeline_memcpy_async(&s_next[LR_TRACE_THREADS + threadIdx.x], MODE == 0 ? &a.p.d[slot_b] : &a.p.nd[slot_b], 16);
+                __pipeline_commit();
+            }
             if (!exhausted) {
-                const unsigned idle = ~walking; uint32_t base = 0;
-                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(cursor, (uint32_t) __popc(idle));
-                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
-                exhausted = base + (uint32_t) __popc(idle) >= n_items;
-                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
-                if ((idle >> lane) & 1u) {
-                    if (qi < n_items) {
-                        slot = q_in[qi];
-                        const float4 o4 = MODE == 0 ? a.p.o[slot] : a.p.no[slot], d4 = MODE == 0 ? a.p.d[slot] : a.p.nd[slot];
-                        trace_begin(sc, r, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), o4.w); cnt.rays++;
+                const unsigned need = __ballot_sync(0xffffffffu, !have_a); const uint32_t want = (uint32_t) __popc(need);
+                if (want) {
+                    if (chunk_next == chunk_end) {
+                        uint32_t base = 0;
+                        if (lane == 0) base = atomicAdd(cursor, chunk);
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        chunk_next = base; chunk_end = base + chunk;
                     }
+                    const uint32_t take = min(want, chunk_end - chunk_next);
+                    const uint32_t rank = (uint32_t) __popc(need & lt), qi = chunk_next + rank;
+                    if (!have_a && rank < take && qi < n_items) { slot_a = q_in[qi]; have_a = true; }
+                    chunk_next += take;
+                    exhausted = chunk_next >= n_items;
                 }
             }
         }
-        if (r.node >= 0) trace_step<MODE == 1, false>(sc, r, stack, stride);
-        if (exhausted && !__any_sync(0xffffffffu, r.node != -2)) break;
+        // ---- one step: either the lanes holding a triangle test it, or the lanes at an inner node visit it ----
+        const bool at_leaf = r.node < 0;
+        const unsigned leaves = __ballot_sync(0xffffffffu, at_leaf), inner = __ballot_sync(0xffffffffu, trace_walking(r) && !at_leaf);
+        if (leaves != 0u && ((uint32_t) __popc(leaves) >= LR_TRACE_LEAF_BATCH || inner == 0u)) {
+            if (at_leaf) trace_leaf<MODE == 1, false, STK>(sc, r, st);
+        } else if ((inner >> lane) & 1u) trace_visit<MODE != 1, STK>(sc, r, s_nodes, cfg.n_smem, st);
+        if (exhausted && !__any_sync(0xffffffffu, r.node != TR_IDLE || have_a || have_b)) break;
     }
     flush_counters(cnt, 0, a.stats);
 }

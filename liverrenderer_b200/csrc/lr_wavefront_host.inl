@@ -52,6 +52,10 @@ static int wv_alloc(lr_ctx *c, WVPool *&wp, uint64_t want) {
         LR_CUDA(c, w.queues.alloc((size_t) w.cap * 4 * WV_N_QUEUES));
         LR_CUDA(c, w.counters.alloc(sizeof(WVQueues)));
     }
+    {   // stack entries beyond the shared-memory part of the trace kernels' stacks (one column per resident thread)
+        const size_t need = (size_t) c->n_sm * LR_TRACE_THREADS * std::max<uint32_t>(c->sc.bvh4_stack > c->trace_sd ? c->sc.bvh4_stack - c->trace_sd : 0u, 1u) * sizeof(int);
+        if (w.trace_ovf.bytes < need) LR_CUDA(c, w.trace_ovf.alloc(need));
+    }
     if (!w.ring_host) {
         LR_CUDA(c, cudaHostAlloc((void **) &w.ring_host, WF_RING * sizeof(WVRing), cudaHostAllocMapped));
         LR_CUDA(c, cudaHostGetDevicePointer((void **) &w.ring_dev, w.ring_host, 0));
@@ -92,7 +96,7 @@ static void wv_bind(WVArgs &a, WVPool &w) {
 
 // One batch of lanes in flight on one pool + stream.
 struct WvRun {
-    WVPool *w = nullptr; cudaStream_t s = nullptr; WVArgs a{}; uint64_t iter = 0; bool busy = false; int gen_grid = 1;
+    WVPool *w = nullptr; cudaStream_t s = nullptr; WVArgs a{}; TraceCfg tcfg{}; uint64_t iter = 0; bool busy = false; int gen_grid = 1;
 };
 
 // A render is a sequence of lock-step batches.  GEN fills one pool with the lanes whose primary ray hits something (or starts
@@ -111,6 +115,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
         if (!c->wv[k] || c->wv[k]->cap < cap) break;
         if (k > 0 && n_lanes <= cap) break;
         runs[k].w = c->wv[k]; runs[k].s = k == 0 ? c->stream : c->stream_more[k - 1]; ++n_runs;
+        runs[k].tcfg.n_smem = c->trace_n_smem; runs[k].tcfg.sd = c->trace_sd; runs[k].tcfg.ovf = c->wv[k]->trace_ovf.as<int>(); runs[k].tcfg.ovf_stride = (uint32_t) c->n_sm * LR_TRACE_THREADS;
     }
     if (n_runs > 1) {                                                  // the extra streams start after whatever is queued on the caller's stream
         LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream));
@@ -119,8 +124,8 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
     LR_CUDA(c, cudaMemsetAsync(c->lane_cursor.p, 0, 8, c->stream));
     if (n_runs > 1) { LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream)); for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0)); }
     const uint32_t surf_mask = c->surf_bucket_mask;                    // surface buckets present in this scene
-    const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128, grid_tr = c->n_sm * LR_TRACE_OCC;
-    const size_t smem_tr = (size_t) c->sc.bvh4_stack * 256 * sizeof(int);
+    const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128, grid_tr = c->n_sm;      // trace: one block of LR_TRACE_THREADS per SM
+    const bool stk16 = c->bvh4_small; const size_t smem_tr = c->trace_smem;
     const bool multipass = ra.n_passes > 1;
     const int shadow_mode = (c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf) ? 1 : 2;
     uint64_t launches = 0; bool lanes_done = false; const bool dbg_sync = getenv("LR_WF_SYNC") != nullptr;
@@ -169,12 +174,14 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
         launch(r, ST_SHADE_A_MED, [&] { k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] { k_wv_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); });
         launch(r, ST_ESCAPE, [&] { k_wv_escape<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
-        launch(r, ST_TRACE_S, [&] { if (shadow_mode == 1) k_wv_trace<1><<<grid_tr, 256, smem_tr, s>>>(c->sc, a); else k_wv_trace<2><<<grid_tr, 256, smem_tr, s>>>(c->sc, a); });
+        launch(r, ST_TRACE_S, [&] {
+            if (shadow_mode == 1) { if (stk16) k_wv_trace<1, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<1, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); }
+            else { if (stk16) k_wv_trace<2, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<2, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); } });
         launch(r, ST_NEE, [&] { k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });
         launch(r, ST_SHADE_B_MED, [&] { k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_B_SURF, [&] { k_wv_shade_b_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); });
         k_wv_mid_iteration<<<1, 1, 0, s>>>(a.q); ++launches;
-        launch(r, ST_TRACE_C, [&] { k_wv_trace<0><<<grid_tr, 256, smem_tr, s>>>(c->sc, a); });
+        launch(r, ST_TRACE_C, [&] { if (stk16) k_wv_trace<0, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<0, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); });
         if (multipass) launch(r, ST_REGEN, [&] { k_wv_regen<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         return readback(r);
     };

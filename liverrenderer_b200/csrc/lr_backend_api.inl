@@ -1,5 +1,70 @@
 // lr_backend_api.inl -- scene upload and the render / adjoint entry points (included by lr_backend.cu)
 
+// ---------------------------------------------------------------------------------------------
+// Sealed media.  In production tracking (LR_TRACKING_DDA) a shadow segment that meets a non-null surface contributes exactly 0
+// (eval_null_transmission, volpath.cpp:528-543).  When a medium can only be entered through closed, opaque (non-null BSDF)
+// surfaces and no emitter lies inside them, that is the fate of EVERY shadow ray that starts in it, so emitter sampling at its
+// scatter vertices -- and the BSDF value / shadow ray of boundary vertices whose light direction points into it -- can be
+// skipped without changing a single path.  Conditions checked here, all conservative (a `false` only costs speed):
+//   * the medium is the interior of at least one mesh, and every mesh that names it as interior is a closed, consistently
+//     oriented manifold (every directed edge has exactly one opposite; vertices welded by position) with a non-null BSDF
+//     and without an area emitter
+//   * meshes that name it as exterior (nested shells) lie inside the bounding box of one of those enclosing meshes
+//   * the sensor is not inside it, and no area emitter's bounding box touches an enclosing mesh's bounding box
+// ---------------------------------------------------------------------------------------------
+static bool mesh_is_closed(const lr_mesh &m) {
+    if (m.n_faces < 4) return false;
+    // weld vertices by position bits
+    std::vector<uint32_t> order(m.n_vertices), canon(m.n_vertices);
+    for (uint32_t i = 0; i < m.n_vertices; ++i) order[i] = i;
+    auto key = [&](uint32_t i) { return m.positions + 3 * (size_t) i; };
+    std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return memcmp(key(a), key(b), 12) < 0; });
+    for (uint32_t k = 0; k < m.n_vertices; ++k) canon[order[k]] = (k && memcmp(key(order[k]), key(order[k - 1]), 12) == 0) ? canon[order[k - 1]] : order[k];
+    std::vector<uint64_t> edges; edges.reserve((size_t) m.n_faces * 3);
+    for (uint32_t f = 0; f < m.n_faces; ++f) {
+        uint32_t v[3] = { canon[m.indices[3 * (size_t) f]], canon[m.indices[3 * (size_t) f + 1]], canon[m.indices[3 * (size_t) f + 2]] };
+        if (v[0] == v[1] || v[1] == v[2] || v[0] == v[2]) return false;                       // degenerate face
+        for (int k = 0; k < 3; ++k) edges.push_back(((uint64_t) v[k] << 32) | v[(k + 1) % 3]);
+    }
+    std::sort(edges.begin(), edges.end());
+    for (size_t i = 1; i < edges.size(); ++i) if (edges[i] == edges[i - 1]) return false;  // a directed edge used twice
+    for (uint64_t e : edges) { uint64_t opp = (e << 32) | (e >> 32); if (!std::binary_search(edges.begin(), edges.end(), opp)) return false; }
+    return true;
+}
+static void mesh_bbox(const lr_mesh &m, float lo[3], float hi[3]) {
+    for (int k = 0; k < 3; ++k) { lo[k] = INFINITY; hi[k] = -INFINITY; }
+    for (uint32_t i = 0; i < m.n_vertices; ++i) for (int k = 0; k < 3; ++k) { float v = m.positions[3 * (size_t) i + k]; lo[k] = std::min(lo[k], v); hi[k] = std::max(hi[k], v); }
+}
+static void seal_media(const lr_scene *s, std::vector<DMedium> &media) {
+    for (auto &m : media) m.sealed = 0;
+    if (getenv("LR_NO_SEAL")) return;
+    std::vector<char> closed(s->n_meshes, 0);
+    for (uint32_t j = 0; j < s->n_meshes; ++j) {
+        const lr_mesh &me = s->meshes[j];
+        if (me.interior_medium >= 0 && s->bsdfs[me.bsdf].kind != LR_BSDF_NULL && me.emitter < 0) closed[j] = mesh_is_closed(me) ? 1 : 0;
+    }
+    for (uint32_t i = 0; i < s->n_media; ++i) {
+        if (s->sensor.medium == (int) i) continue;
+        bool ok = true, any = false;
+        for (uint32_t j = 0; j < s->n_meshes && ok; ++j) if (s->meshes[j].interior_medium == (int) i) { any = true; ok = closed[j] != 0; }
+        if (!ok || !any) continue;
+        auto inside_an_encloser = [&](const float lo[3], const float hi[3], bool strictly) {
+            for (uint32_t j = 0; j < s->n_meshes; ++j) if (s->meshes[j].interior_medium == (int) i) {
+                float elo[3], ehi[3]; mesh_bbox(s->meshes[j], elo, ehi); bool in = true, touch = true;
+                for (int k = 0; k < 3; ++k) { in = in && lo[k] >= elo[k] && hi[k] <= ehi[k]; touch = touch && lo[k] <= ehi[k] && hi[k] >= elo[k]; }
+                if (strictly ? in : touch) return true;
+            }
+            return false;
+        };
+        for (uint32_t j = 0; j < s->n_meshes && ok; ++j) {
+            const lr_mesh &me = s->meshes[j]; float lo[3], hi[3]; mesh_bbox(me, lo, hi);
+            if (me.exterior_medium == (int) i && me.interior_medium != (int) i && !inside_an_encloser(lo, hi, true)) ok = false;
+            if (me.emitter >= 0 && inside_an_encloser(lo, hi, false)) ok = false;
+        }
+        if (ok) media[i].sealed = 1;
+    }
+}
+
 extern "C" {
 
 int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
@@ -127,6 +192,8 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
             LR_FAIL(c, LR_ERR_INVALID_ARG, "medium %u: heterogeneous medium needs a sigma_t grid", i);
         if (m.kind == LR_MEDIUM_HETEROGENEOUS) sc.prb_handle_null = 1; else sc.prb_nee_homogeneous = 1;
     }
+    seal_media(s, c->h_media);
+    if (getenv("LR_VERBOSE")) for (uint32_t i = 0; i < s->n_media; ++i) fprintf(stderr, "[lr] medium %u: %s\n", i, c->h_media[i].sealed ? "sealed (NEE from inside skipped in DDA mode)" : "open");
     c->d_grids = c->newbuf(); LR_CUDA(c, c->d_grids->alloc(std::max<size_t>(s->n_grids, 1) * sizeof(DGrid)));
     c->d_media = c->newbuf(); LR_CUDA(c, c->d_media->alloc(std::max<size_t>(s->n_media, 1) * sizeof(DMedium)));
     sc.grids = c->d_grids->as<DGrid>(); sc.media = c->d_media->as<DMedium>();

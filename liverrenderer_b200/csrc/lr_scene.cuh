@@ -38,7 +38,9 @@ struct DGrid {
     uint32_t differentiable;
 };
 
-struct DMedium { lr_medium m; float max_density; };
+// `sealed`: every point of the medium lies inside a closed surface with a non-null BSDF that no emitter shares (lr_backend_api.inl:
+// seal_media), so a shadow ray that starts in it always ends on an opaque surface: transmittance exactly 0 (volpath.cpp:528-543)
+struct DMedium { lr_medium m; float max_density; uint32_t sealed; };
 
 // `bitmap` texture (src/textures/bitmap.cpp); row-major [h][w][ch] floats in HBM
 struct DTex { const float *data; int w, h, ch; uint32_t filter, wrap; float to_uv[6]; };

@@ -539,10 +539,15 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
 // ------------------------------------------------------------------------------------------
 LR_DEV bool wv_nee_setup(const DScene &sc, const WVArgs &a, uint32_t slot, Sampler &smp, V3 ref_p, V3 ref_n, const SurfaceInteraction *ref_si,
                          int &medium, DirectionSample &ds, V3 &emitter_val) {
+    // production tracking: a shadow ray that starts in a sealed medium always ends on an opaque surface (DMedium::sealed) => exactly 0;
+    // the two draws of the emitter sample are consumed as usual, nothing else happens
+    const bool dda = sc.integ.tracking == LR_TRACKING_DDA;
+    if (dda && !ref_si && medium >= 0 && sc.media[medium].sealed) { (void) smp.next_2d(); ds.pdf = 0.f; return false; }
     ds = sample_emitter_direction(sc, ref_p, smp.next_2d(), emitter_val);
     if (ds.pdf == 0.f) return false;
     const Ray ray = spawn_ray_to(ref_p, ref_n, ds.p);
     if (ref_si && mesh_is_transition(sc, ref_si->mesh)) medium = target_medium(sc, *ref_si, ray.d);
+    if (dda && medium >= 0 && sc.media[medium].sealed) return false;
     a.p.no[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
     a.p.nd[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ds.dist);
     return true;

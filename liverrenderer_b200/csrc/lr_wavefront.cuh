@@ -29,22 +29,31 @@
 
 namespace lr {
 
+// Path state, indexed by slot.  Fields that are always touched together share one 32-byte record = one DRAM sector (after the
+// first bounce the queues address slots in no particular order, so every access costs whole sectors; 16-byte SoA planes would use
+// half of each):
+//   h0  { PCG32 state, inc | throughput, depth }             every stage that draws or scales
+//   h1  { ray.o, ray.maxt  | ray.d, flags }                  the ray: all TRACE needs
+//   h2  { radiance so far, eta | last_scatter_p, last_scatter_direction_pdf }   emitter hits, MIS, russian roulette beyond rr_depth
+//   hit { t, prim, u, v }   lane { lane lo/hi, film sample position }           16-byte records
+//   n0  { shadow ray origin, max_dist | shadow ray direction, ds.dist }         NEE (volpath.cpp:400-554)
+//   n1  { throughput * (phase | bsdf) value * MIS weight * emitter value, walk medium | closest hit along the shadow ray }
 struct WVPlanes {
-    ulonglong2 *rng;     // PCG32 state, inc
-    float4 *o;           // ray.o, ray.maxt
-    float4 *d;           // ray.d, flags (bits)
-    float4 *thr;         // throughput, depth (bits)
-    float4 *hit;         // t, prim (bits), u, v of the closest hit along the current ray
-    float4 *res;         // radiance so far, eta
-    float4 *lsp;         // last_scatter_p, last_scatter_direction_pdf
-    float4 *lane;        // lane lo/hi (bits), film sample position
-    // NEE (volpath.cpp:400-554)
-    float4 *no;          // shadow ray origin, max_dist
-    float4 *nd;          // shadow ray direction, ds.dist
-    float4 *nw;          // throughput * (phase | bsdf) value * MIS weight * emitter value, walk medium (bits)
-    float4 *nhit;        // closest hit along the shadow ray (only when the walk needs it)
+    float4 *h0, *h1, *h2, *hit_, *lane_, *n0, *n1;
+    LR_DEV ulonglong2 &rng(uint32_t s) const { return reinterpret_cast<ulonglong2 *>(h0)[2 * (size_t) s]; }
+    LR_DEV float4 &thr(uint32_t s) const { return h0[2 * (size_t) s + 1]; }
+    LR_DEV float4 &o(uint32_t s) const { return h1[2 * (size_t) s]; }
+    LR_DEV float4 &d(uint32_t s) const { return h1[2 * (size_t) s + 1]; }
+    LR_DEV float4 &res(uint32_t s) const { return h2[2 * (size_t) s]; }
+    LR_DEV float4 &lsp(uint32_t s) const { return h2[2 * (size_t) s + 1]; }
+    LR_DEV float4 &hit(uint32_t s) const { return hit_[s]; }
+    LR_DEV float4 &lane(uint32_t s) const { return lane_[s]; }
+    LR_DEV float4 &no(uint32_t s) const { return n0[2 * (size_t) s]; }
+    LR_DEV float4 &nd(uint32_t s) const { return n0[2 * (size_t) s + 1]; }
+    LR_DEV float4 &nw(uint32_t s) const { return n1[2 * (size_t) s]; }
+    LR_DEV float4 &nhit(uint32_t s) const { return n1[2 * (size_t) s + 1]; }
 };
-#define WV_N_PLANES 12
+#define WV_N_PLANES 12                  // 16-byte units per slot
 
 struct WVQueues {                      // device-side counters of one pool
     uint32_t n_trace, n_track, n_scatter, n_escape, n_shadow, n_nee, n_regen;
@@ -63,8 +72,8 @@ struct WVArgs {
     unsigned long long *stats;
 };
 
-LR_DEV Sampler wv_rng(const WVPlanes &p, uint32_t s) { const ulonglong2 r = p.rng[s]; Sampler m; m.state = r.x; m.inc = r.y; return m; }
-LR_DEV void wv_rng_store(const WVPlanes &p, uint32_t s, const Sampler &m) { p.rng[s] = make_ulonglong2(m.state, m.inc); }
+LR_DEV Sampler wv_rng(const WVPlanes &p, uint32_t s) { const ulonglong2 r = p.rng(s); Sampler m; m.state = r.x; m.inc = r.y; return m; }
+LR_DEV void wv_rng_store(const WVPlanes &p, uint32_t s, const Sampler &m) { p.rng(s) = make_ulonglong2(m.state, m.inc); }
 LR_DEV uint32_t wv_bucket(const DScene &sc, const Hit &h) { return (__float_as_uint(sc.tris_gid[h.prim].v2.w) >> 1) & 3u; }
 
 // volpath.cpp:160-178: the russian-roulette + depth test at the top of a loop iteration
@@ -187,13 +196,13 @@ LR_DEV void wv_start_paths(const DScene &sc, const WVArgs &a, bool have, uint64_
     if (keep) {
         const WVPlanes &p = a.p; const V2 fp = box ? L.pos : L.sample_pos;
         wv_rng_store(p, slot, L.smp);
-        p.o[slot] = make_float4(L.ray.o.x, L.ray.o.y, L.ray.o.z, L.ray.maxt);
-        p.d[slot] = make_float4(L.ray.d.x, L.ray.d.y, L.ray.d.z, __uint_as_float(f));
-        p.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(0u));
-        p.hit[slot] = wf_hit4(h);
-        p.res[slot] = make_float4(0.f, 0.f, 0.f, 1.f);
-        p.lsp[slot] = make_float4(0.f, 0.f, 0.f, 1.f);
-        p.lane[slot] = make_float4(__uint_as_float((uint32_t) lane), __uint_as_float((uint32_t) (lane >> 32)), fp.x, fp.y);
+        p.o(slot) = make_float4(L.ray.o.x, L.ray.o.y, L.ray.o.z, L.ray.maxt);
+        p.d(slot) = make_float4(L.ray.d.x, L.ray.d.y, L.ray.d.z, __uint_as_float(f));
+        p.thr(slot) = make_float4(thr.x, thr.y, thr.z, __uint_as_float(0u));
+        p.hit(slot) = wf_hit4(h);
+        p.res(slot) = make_float4(0.f, 0.f, 0.f, 1.f);
+        p.lsp(slot) = make_float4(0.f, 0.f, 0.f, 1.f);
+        p.lane(slot) = make_float4(__uint_as_float((uint32_t) lane), __uint_as_float((uint32_t) (lane >> 32)), fp.x, fp.y);
     }
     wv_route(sc, a, slot, keep, f, h);
 }
@@ -227,8 +236,8 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_regen(const __grid_consta
         Sampler smp; smp.state = smp.inc = 0; uint64_t lane = 0; uint32_t pass = 0;
         if (item) {
             smp = wv_rng(a.p, slot); smp.advance(a.spp_per_pass);
-            const float4 lp = a.p.lane[slot]; lane = ((uint64_t) __float_as_uint(lp.y) << 32) | __float_as_uint(lp.x);
-            pass = (__float_as_uint(a.p.d[slot].w) >> WF_PASS_SHIFT) + 1u;
+            const float4 lp = a.p.lane(slot); lane = ((uint64_t) __float_as_uint(lp.y) << 32) | __float_as_uint(lp.x);
+            pass = (__float_as_uint(a.p.d(slot).w) >> WF_PASS_SHIFT) + 1u;
         }
         wv_start_paths<C, TO_FILM>(sc, a, item, lane, pass, smp, true, slot, cnt, nsamples);
     }
@@ -273,7 +282,7 @@ __global__ void __launch_bounds__(LR_TRACE_THREADS, 1) k_wv_trace(const __grid_c
             // ---- parked lanes: write the result out, hand the path to its next stage ----
             const bool done = r.node == TR_DONE;
             if (MODE == 0) {
-                if (done) a.p.hit[slot] = wf_hit4(r.h);
+                if (done) a.p.hit(slot) = wf_hit4(r.h);
                 wv_route(sc, a, slot, done, flags, r.h);
             } else {
                 bool walk = false;
@@ -285,15 +294,15 @@ __global__ void __launch_bounds__(LR_TRACE_THREADS, 1) k_wv_trace(const __grid_c
                         // (eval_null_transmission, volpath.cpp:528-543), so the walk is skipped; only the RNG consumption differs
                         blocked = true;
                         if (sc.any_null_bsdf) {
-                            const float4 o4 = a.p.no[slot], d4 = a.p.nd[slot]; Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
+                            const float4 o4 = a.p.no(slot), d4 = a.p.nd(slot); Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
                             cnt.rays++; blocked = hit_valid(bvh_trace<true, true>(sc, ray));
                         }
                     }
                     if (!blocked) {
-                        const float4 w = a.p.nw[slot];
+                        const float4 w = a.p.nw(slot);
                         if (__float_as_int(w.w) < 0 && !hit_valid(r.h)) {      // nothing but vacuum up to the emitter: transmittance 1
-                            float4 r4 = a.p.res[slot]; r4.x += w.x; r4.y += w.y; r4.z += w.z; a.p.res[slot] = r4;
-                        } else { walk = true; if (MODE == 2) a.p.nhit[slot] = wf_hit4(r.h); }
+                            float4 r4 = a.p.res(slot); r4.x += w.x; r4.y += w.y; r4.z += w.z; a.p.res(slot) = r4;
+                        } else { walk = true; if (MODE == 2) a.p.nhit(slot) = wf_hit4(r.h); }
                     }
                 }
                 wf_push(a.q_nee, &a.q->n_nee, slot, walk);
@@ -311,8 +320,8 @@ __global__ void __launch_bounds__(LR_TRACE_THREADS, 1) k_wv_trace(const __grid_c
             }
             if (!have_b && have_a) {
                 slot_b = slot_a; have_a = false; have_b = true;
-                __pipeline_memcpy_async(&s_next[threadIdx.x], MODE == 0 ? &a.p.o[slot_b] : &a.p.no[slot_b], 16);
-                __pipeline_memcpy_async(&s_next[LR_TRACE_THREADS + threadIdx.x], MODE == 0 ? &a.p.d[slot_b] : &a.p.nd[slot_b], 16);
+                __pipeline_memcpy_async(&s_next[threadIdx.x], MODE == 0 ? &a.p.o(slot_b) : &a.p.no(slot_b), 16);
+                __pipeline_memcpy_async(&s_next[LR_TRACE_THREADS + threadIdx.x], MODE == 0 ? &a.p.d(slot_b) : &a.p.nd(slot_b), 16);
                 __pipeline_commit();
             }
             if (!exhausted) {
@@ -354,12 +363,12 @@ LR_DEV void wv_track_out(const DScene &sc, const WVArgs &a, uint32_t slot, int e
     const WVPlanes &p = a.p;
     const bool fin = event == 0; float4 lp = make_float4(0.f, 0.f, 0.f, 0.f); V3 L = mk3(0.f);
     if (event >= 0) wv_rng_store(p, slot, smp);
-    if (fin) { lp = p.lane[slot]; const float4 r4 = p.res[slot]; L = mk3(r4.x, r4.y, r4.z); }
+    if (fin) { lp = p.lane(slot); const float4 r4 = p.res(slot); L = mk3(r4.x, r4.y, r4.z); }
     wv_finish<C, TO_FILM>(sc, a, fin, lp, L, f);
     if (event > 0) {
-        p.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
-        p.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
-        p.hit[slot].x = hit_t;
+        p.o(slot) = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+        p.thr(slot) = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
+        p.hit(slot).x = hit_t;
     }
     const bool esc = event == 2 && !hit_valid(h0);
     const uint32_t b = (event == 2 && !esc) ? wv_bucket(sc, h0) : 0xffu;
@@ -380,11 +389,11 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
         uint32_t depth = 0, f = 0; float hit_t = 0.f; Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
         if (item) {
             smp = wv_rng(p, slot);
-            float4 t4 = p.o[slot]; ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
-            t4 = p.d[slot]; ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
-            t4 = p.thr[slot]; thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
-            h0 = wf_hit(p.hit[slot]); hit_t = h0.t;
-            const float eta = p.res[slot].w;
+            float4 t4 = p.o(slot); ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+            t4 = p.d(slot); ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
+            t4 = p.thr(slot); thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
+            h0 = wf_hit(p.hit(slot)); hit_t = h0.t;
+            const float eta = p.res(slot).w;
             const uint32_t channel = f & WF_CHANNEL_MASK; const int medium = wf_medium(f);
             const DMedium &m = sc.media[medium];
             for (bool first = true;; first = false) {
@@ -404,7 +413,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
                                 V3 st = grid_eval<false>(g, pt, nullptr) * m.m.scale, sn = mk3(mu) - st;
                                 float pn = hmean(sn / mu);
                                 if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); continue; }
-                                depth += 1; cnt.real_scatters++; p.lsp[slot] = make_float4(pt.x, pt.y, pt.z, p.lsp[slot].w);
+                                depth += 1; cnt.real_scatters++; p.lsp(slot) = make_float4(pt.x, pt.y, pt.z, p.lsp(slot).w);
                                 if (!(depth < sc.max_depth)) { event = 0; break; }
                                 thr *= (st * medium_albedo(sc, m, pt)) / (mu * hmean(st / mu));
                                 ray.o = pt; hit_t = hit_t - t; event = 1; break;
@@ -431,7 +440,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
                         ray.o = mei.p; hit_t = hit_t - mei.t;
                         continue;
                     }
-                    depth += 1; cnt.real_scatters++; p.lsp[slot] = make_float4(mei.p.x, mei.p.y, mei.p.z, p.lsp[slot].w);
+                    depth += 1; cnt.real_scatters++; p.lsp(slot) = make_float4(mei.p.x, mei.p.y, mei.p.z, p.lsp(slot).w);
                     if (!(depth < sc.max_depth)) { event = 0; break; }
                     if (is_spectral) thr *= mei.sigma_s / hmean(mei.sigma_t / mei.combined_extinction);
                     else thr *= mei.sigma_s / mei.sigma_t;
@@ -484,10 +493,10 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
                 if (event == -2 && qi < n_items) {
                     slot = a.q_track[qi];
                     smp = wv_rng(p, slot);
-                    float4 t4 = p.o[slot]; ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
-                    t4 = p.d[slot]; ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
-                    t4 = p.thr[slot]; thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
-                    h0 = wf_hit(p.hit[slot]); hit_t = h0.t;
+                    float4 t4 = p.o(slot); ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+                    t4 = p.d(slot); ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
+                    t4 = p.thr(slot); thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
+                    h0 = wf_hit(p.hit(slot)); hit_t = h0.t;
                     const DMedium &m = sc.media[wf_medium(f)]; grid_id = m.m.sigma_t_grid; mu_scale = m.m.scale; const DGrid &g = sc.grids[grid_id];
                     event = 2;
                     float mint, maxt;
@@ -523,7 +532,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
             if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); }
             else {
                 depth += 1; cnt.real_scatters++;
-                float *lp = reinterpret_cast<float *>(p.lsp + slot); lp[0] = pt.x; lp[1] = pt.y; lp[2] = pt.z;
+                float *lp = reinterpret_cast<float *>(&p.lsp(slot)); lp[0] = pt.x; lp[1] = pt.y; lp[2] = pt.z;
                 if (!(depth < sc.max_depth)) event = 0;
                 else { thr *= (st * medium_albedo(sc, m, pt)) / (mu * hmean(st / mu)); ray.o = pt; hit_t = hit_t - t; event = 1; }
             }
@@ -548,8 +557,8 @@ LR_DEV bool wv_nee_setup(const DScene &sc, const WVArgs &a, uint32_t slot, Sampl
     const Ray ray = spawn_ray_to(ref_p, ref_n, ds.p);
     if (ref_si && mesh_is_transition(sc, ref_si->mesh)) medium = target_medium(sc, *ref_si, ray.d);
     if (dda && medium >= 0 && sc.media[medium].sealed) return false;
-    a.p.no[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
-    a.p.nd[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, ds.dist);
+    a.p.no(slot) = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+    a.p.nd(slot) = make_float4(ray.d.x, ray.d.y, ray.d.z, ds.dist);
     return true;
 }
 
@@ -559,24 +568,24 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_shade_a_medium(const __gr
     WF_FOR_QUEUE(a.q->n_scatter) {
         const bool item = qi < _n; bool nee = false; const uint32_t slot = item ? a.q_scatter[qi] : 0;
         if (item) {
-            const float4 d4 = p.d[slot]; uint32_t f = __float_as_uint(d4.w); const int medium = wf_medium(f);
+            const float4 d4 = p.d(slot); uint32_t f = __float_as_uint(d4.w); const int medium = wf_medium(f);
             const DMedium &m = sc.media[medium]; Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
             const bool sample_emitters = m.m.sample_emitters != 0;
             const uint32_t f0 = f; int walk_medium = medium;
             f |= WF_VALID_RAY; f = sample_emitters ? (f & ~WF_SPEC_CHAIN) : (f | WF_SPEC_CHAIN);
             if (sample_emitters) {
                 Sampler smp = wv_rng(p, slot);
-                const float4 o4 = p.o[slot], t4 = p.thr[slot]; const V3 pt = mk3(o4.x, o4.y, o4.z), wi = -mk3(d4.x, d4.y, d4.z), thr = mk3(t4.x, t4.y, t4.z);
+                const float4 o4 = p.o(slot), t4 = p.thr(slot); const V3 pt = mk3(o4.x, o4.y, o4.z), wi = -mk3(d4.x, d4.y, d4.z), thr = mk3(t4.x, t4.y, t4.z);
                 DirectionSample ds; V3 ev;
                 if (wv_nee_setup(sc, a, slot, smp, pt, mk3(0.f), nullptr, walk_medium, ds, ev)) {
                     const float phase_val = phase.eval_pdf(wi, ds.d);
                     const V3 w = thr * phase_val * mis_weight(ds.pdf, ds.delta ? 0.f : phase_val) * ev;
-                    p.nw[slot] = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
+                    p.nw(slot) = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
                     nee = true;
                 }
                 wv_rng_store(p, slot, smp);
             }
-            if (f != f0) reinterpret_cast<float *>(p.d + slot)[3] = __uint_as_float(f);
+            if (f != f0) reinterpret_cast<float *>(&p.d(slot))[3] = __uint_as_float(f);
         }
         wf_push(a.q_shadow, &a.q->n_shadow, slot, nee);
     }
@@ -591,30 +600,30 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_a_surface(cons
         const bool item = qi < _n; const uint32_t slot = item ? a.q_surf[bucket][qi] : 0; bool nee = false, gone = false; uint32_t f = 0;
         if (item) {
             Sampler smp = wv_rng(p, slot);
-            const float4 o4 = p.o[slot], d4 = p.d[slot], t4 = p.thr[slot];
+            const float4 o4 = p.o(slot), d4 = p.d(slot), t4 = p.thr(slot);
             f = __float_as_uint(d4.w); const uint32_t depth = __float_as_uint(t4.w); const int medium = wf_medium(f);
             Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
             const V3 thr = mk3(t4.x, t4.y, t4.z);
-            Hit h = wf_hit(p.hit[slot]);
+            Hit h = wf_hit(p.hit(slot));
             SurfaceInteraction si = compute_si(sc, ray, h, sc.tris_gid);
             // the segment started outside any medium <=> the reference intersected in this very iteration (`intersect`, :301-303)
             if (sc.hide_emitters && medium < 0 && depth == 0u && sc.meshes[si.mesh].emitter >= 0) {                     // :307-323
                 Ray r2 = spawn_ray(si.p, si.n, ray.d); Hit pi = skip_area_emitters(sc, sc.tris_gid, r2, cnt);
-                si = compute_si(sc, r2, pi, sc.tris_gid); h = pi; p.hit[slot] = wf_hit4(h);
-                p.o[slot] = make_float4(r2.o.x, r2.o.y, r2.o.z, r2.maxt);         // SHADE_B recomputes si from (ray, hit): keep them consistent
+                si = compute_si(sc, r2, pi, sc.tris_gid); h = pi; p.hit(slot) = wf_hit4(h);
+                p.o(slot) = make_float4(r2.o.x, r2.o.y, r2.o.z, r2.maxt);         // SHADE_B recomputes si from (ray, hit): keep them consistent
             }
             const bool count_direct = depth == 0u || (f & WF_SPEC_CHAIN);
             const int emitter = emitter_of(sc, si);
             if (emitter >= 0 && !(depth == 0u && sc.hide_emitters)) {                                                     // :326-345
-                const float4 l4 = p.lsp[slot];
+                const float4 l4 = p.lsp(slot);
                 float emitter_pdf = 1.f;
                 if (!count_direct) { DirectionSample ds = ds_from_si(sc, si, mk3(l4.x, l4.y, l4.z)); emitter_pdf = pdf_emitter_direction(sc, ds); }
                 const V3 emitted = eval_emitter_at(sc, emitter, si);
                 const V3 c = count_direct ? thr * emitted : thr * mis_weight(l4.w, emitter_pdf) * emitted;
-                float4 r4 = p.res[slot]; r4.x += c.x; r4.y += c.y; r4.z += c.z; p.res[slot] = r4;
+                float4 r4 = p.res(slot); r4.x += c.x; r4.y += c.y; r4.z += c.z; p.res(slot) = r4;
             }
             if (!si_valid(si)) {                                   // only after the hidden-emitter skip above: nothing behind the emitter
-                gone = true; f |= WF_DEAD; reinterpret_cast<float *>(p.d + slot)[3] = __uint_as_float(f);
+                gone = true; f |= WF_DEAD; reinterpret_cast<float *>(&p.d(slot))[3] = __uint_as_float(f);
             } else {
                 BSDF bsdf(sc, si);
                 if ((bsdf.flags() & F_SMOOTH) && (depth + 1 < sc.max_depth)) {                                           // :350-362
@@ -622,7 +631,7 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_a_surface(cons
                     if (wv_nee_setup(sc, a, slot, smp, si.p, si.n, &si, walk_medium, ds, ev)) {
                         const V3 wo = si.sh.to_local(ds.d); float bsdf_pdf; const V3 bsdf_val = bsdf.eval_pdf(si.wi, wo, bsdf_pdf);
                         const V3 w = thr * bsdf_val * mis_weight(ds.pdf, ds.delta ? 0.f : bsdf_pdf) * ev;
-                        p.nw[slot] = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
+                        p.nw(slot) = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
                         nee = true;
                     }
                     wv_rng_store(p, slot, smp);
@@ -631,7 +640,7 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_a_surface(cons
         }
         {
             float4 lp = make_float4(0.f, 0.f, 0.f, 0.f); V3 L = mk3(0.f);
-            if (gone) { lp = p.lane[slot]; const float4 r4 = p.res[slot]; L = mk3(r4.x, r4.y, r4.z); }
+            if (gone) { lp = p.lane(slot); const float4 r4 = p.res(slot); L = mk3(r4.x, r4.y, r4.z); }
             wv_finish<C, TO_FILM>(sc, a, gone, lp, L, f);
         }
         wf_push(a.q_regen, &a.q->n_regen, slot, gone && wv_more_passes(a, f));
@@ -648,7 +657,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_escape(const __grid_const
         const bool item = qi < _n; const uint32_t slot = item ? a.q_escape[qi] : 0;
         V3 L = mk3(0.f); uint32_t f = 0; float4 lp = make_float4(0.f, 0.f, 0.f, 0.f);
         if (item) {
-            const float4 d4 = p.d[slot], t4 = p.thr[slot], r4 = p.res[slot]; lp = p.lane[slot];
+            const float4 d4 = p.d(slot), t4 = p.thr(slot), r4 = p.res(slot); lp = p.lane(slot);
             f = __float_as_uint(d4.w); const uint32_t depth = __float_as_uint(t4.w);
             L = mk3(r4.x, r4.y, r4.z);
             if (sc.env >= 0 && !(depth == 0u && sc.hide_emitters)) {
@@ -658,7 +667,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_escape(const __grid_const
                 if (count_direct) L += thr * emitted;
                 else {
                     DirectionSample ds; ds.d = dir; ds.emitter = sc.env; ds.dist = 0.f; ds.n = ds.p = mk3(0.f); ds.uv = mk2(0.f, 0.f); ds.pdf = 0.f; ds.delta = false;
-                    L += thr * mis_weight(p.lsp[slot].w, pdf_emitter_direction(sc, ds)) * emitted;
+                    L += thr * mis_weight(p.lsp(slot).w, pdf_emitter_direction(sc, ds)) * emitted;
                 }
             }
         }
@@ -678,13 +687,13 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_nee(const __grid_constant
         if (qi < _n) {
             const uint32_t slot = a.q_nee[qi];
             Sampler smp = wv_rng(p, slot);
-            const uint32_t channel = __float_as_uint(p.d[slot].w) & WF_CHANNEL_MASK;
-            const float4 o4 = p.no[slot], d4 = p.nd[slot], w4 = p.nw[slot];
+            const uint32_t channel = __float_as_uint(p.d(slot).w) & WF_CHANNEL_MASK;
+            const float4 o4 = p.no(slot), d4 = p.nd(slot), w4 = p.nw(slot);
             Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z);
             const float max_dist = o4.w, ds_dist = d4.w; float total_dist = 0.f;
             int medium = __float_as_int(w4.w);
             Hit h; h.t = LR_INF; h.prim = 0xffffffffu; h.u = h.v = 0.f;
-            if (have_nhit) h = wf_hit(p.nhit[slot]);
+            if (have_nhit) h = wf_hit(p.nhit(slot));
             float si_t = h.t; bool needs_intersection = false, active = true;
             V3 transmittance = mk3(1.f);
             while (active) {
@@ -753,9 +762,9 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_nee(const __grid_constant
                 if (active_surface && mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
             }
             // result += throughput * (phase | bsdf) value * mis * emitter_val * transmittance     (:279-283, :356-361)
-            float4 r4 = p.res[slot];
+            float4 r4 = p.res(slot);
             r4.x = fmaf(w4.x, transmittance.x, r4.x); r4.y = fmaf(w4.y, transmittance.y, r4.y); r4.z = fmaf(w4.z, transmittance.z, r4.z);
-            p.res[slot] = r4;
+            p.res(slot) = r4;
             wv_rng_store(p, slot, smp);
         }
     }
@@ -775,20 +784,22 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_shade_b_medium(const __gr
         bool alive = false; uint32_t f = 0; V3 L = mk3(0.f); float4 lp = make_float4(0.f, 0.f, 0.f, 0.f);
         if (item) {
             Sampler smp = wv_rng(p, slot);
-            const float4 d4 = p.d[slot], t4 = p.thr[slot], r4 = p.res[slot]; f = __float_as_uint(d4.w);
+            const float4 d4 = p.d(slot), t4 = p.thr(slot); f = __float_as_uint(d4.w);
             const DMedium &m = sc.media[wf_medium(f)]; Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
             (void) smp.next_1d(); const V2 s2 = smp.next_2d();
             float phase_pdf; const V3 wo = phase.sample(-mk3(d4.x, d4.y, d4.z), s2, phase_pdf);
             V3 thr = mk3(t4.x, t4.y, t4.z); const uint32_t depth = __float_as_uint(t4.w);
-            alive = wv_rr(sc, smp, thr, r4.w, depth);
+            // eta only enters the roulette once it is performed (depth > rr_depth): the h2 record is not touched before
+            const float eta = depth > (uint32_t) sc.rr_depth ? p.res(slot).w : 1.f;
+            alive = wv_rr(sc, smp, thr, eta, depth);
             wv_rng_store(p, slot, smp);
             if (alive) {
                 if (phase_pdf > 0.f) {
-                    p.d[slot] = make_float4(wo.x, wo.y, wo.z, d4.w);
-                    reinterpret_cast<float *>(p.o + slot)[3] = LR_LARGEST; reinterpret_cast<float *>(p.lsp + slot)[3] = phase_pdf;
+                    p.d(slot) = make_float4(wo.x, wo.y, wo.z, d4.w);
+                    reinterpret_cast<float *>(&p.o(slot))[3] = LR_LARGEST; reinterpret_cast<float *>(&p.lsp(slot))[3] = phase_pdf;
                 }
-                p.thr[slot] = make_float4(thr.x, thr.y, thr.z, t4.w);
-            } else { L = mk3(r4.x, r4.y, r4.z); lp = p.lane[slot]; }
+                p.thr(slot) = make_float4(thr.x, thr.y, thr.z, t4.w);
+            } else { const float4 r4 = p.res(slot); L = mk3(r4.x, r4.y, r4.z); lp = p.lane(slot); }
         }
         wv_finish<C, TO_FILM>(sc, a, item && !alive, lp, L, f);
         wf_push(q_out, n_out, slot, alive);
@@ -805,19 +816,19 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_b_surface(cons
         bool item = qi < _n; const uint32_t slot = item ? a.q_surf[bucket][qi] : 0;
         bool alive = false; uint32_t f = 0; V3 L = mk3(0.f); float4 lp = make_float4(0.f, 0.f, 0.f, 0.f);
         float4 d4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (item) { d4 = p.d[slot]; f = __float_as_uint(d4.w); item = !(f & WF_DEAD); }        // WF_DEAD: finished by SHADE_A (hidden-emitter skip)
+        if (item) { d4 = p.d(slot); f = __float_as_uint(d4.w); item = !(f & WF_DEAD); }        // WF_DEAD: finished by SHADE_A (hidden-emitter skip)
         if (item) {
             Sampler smp = wv_rng(p, slot);
-            const float4 o4 = p.o[slot], t4 = p.thr[slot], r4 = p.res[slot];
+            const float4 o4 = p.o(slot), t4 = p.thr(slot), r4 = p.res(slot);
             Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z); ray.maxt = o4.w;
-            const SurfaceInteraction si = compute_si(sc, ray, wf_hit(p.hit[slot]), sc.tris_gid);
+            const SurfaceInteraction si = compute_si(sc, ray, wf_hit(p.hit(slot)), sc.tris_gid);
             BSDF bsdf(sc, si);
             const float s1 = smp.next_1d(); const V2 s2 = smp.next_2d();
             V3 bsdf_val; const BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_val);
             V3 thr = mk3(t4.x, t4.y, t4.z) * bsdf_val; const float eta = r4.w * bs.eta; uint32_t depth = __float_as_uint(t4.w);
             ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
             const bool non_null = !(bs.sampled_type & F_NULL);
-            if (non_null) { depth += 1u; p.lsp[slot] = make_float4(si.p.x, si.p.y, si.p.z, bs.pdf); f |= WF_VALID_RAY; }
+            if (non_null) { depth += 1u; p.lsp(slot) = make_float4(si.p.x, si.p.y, si.p.z, bs.pdf); f |= WF_VALID_RAY; }
             bool spec = (f & WF_SPEC_CHAIN) != 0;
             spec |= non_null && (bs.sampled_type & F_DELTA); spec &= !(bs.sampled_type & F_SMOOTH);
             f = spec ? (f | WF_SPEC_CHAIN) : (f & ~WF_SPEC_CHAIN);
@@ -825,11 +836,11 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_b_surface(cons
             alive = wv_rr(sc, smp, thr, eta, depth);
             wv_rng_store(p, slot, smp);
             if (alive) {
-                p.o[slot] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
-                p.d[slot] = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(f));
-                p.thr[slot] = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
-                if (eta != r4.w) reinterpret_cast<float *>(p.res + slot)[3] = eta;
-            } else { L = mk3(r4.x, r4.y, r4.z); lp = p.lane[slot]; }
+                p.o(slot) = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+                p.d(slot) = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(f));
+                p.thr(slot) = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
+                if (eta != r4.w) reinterpret_cast<float *>(&p.res(slot))[3] = eta;
+            } else { L = mk3(r4.x, r4.y, r4.z); lp = p.lane(slot); }
         }
         wv_finish<C, TO_FILM>(sc, a, item && !alive, lp, L, f);
         wf_push(q_out, n_out, slot, alive);

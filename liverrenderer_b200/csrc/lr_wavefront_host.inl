@@ -85,9 +85,9 @@ static int wv_prepare(lr_ctx *c, uint64_t n_lanes) {
 }
 
 static void wv_bind(WVArgs &a, WVPool &w) {
-    char *pb = (char *) w.planes.p; const size_t ps = (size_t) w.cap * 16;
-    a.p.rng = (ulonglong2 *) pb; float4 **pl[] = { &a.p.o, &a.p.d, &a.p.thr, &a.p.hit, &a.p.res, &a.p.lsp, &a.p.lane, &a.p.no, &a.p.nd, &a.p.nw, &a.p.nhit };
-    for (int k = 0; k < WV_N_PLANES - 1; ++k) *pl[k] = (float4 *) (pb + ps * (k + 1));
+    char *pb = (char *) w.planes.p; const size_t u = (size_t) w.cap * 16;           // 16-byte units per slot: h0 2, h1 2, h2 2, hit 1, lane 1, n0 2, n1 2
+    a.p.h0 = (float4 *) pb; a.p.h1 = (float4 *) (pb + 2 * u); a.p.h2 = (float4 *) (pb + 4 * u); a.p.hit_ = (float4 *) (pb + 6 * u); a.p.lane_ = (float4 *) (pb + 7 * u);
+    a.p.n0 = (float4 *) (pb + 8 * u); a.p.n1 = (float4 *) (pb + 10 * u);
     a.q = w.counters.as<WVQueues>(); a.cap = w.cap;
     uint32_t *qb = w.queues.as<uint32_t>(); const size_t qs = w.cap;
     a.q_trace = qb; a.q_track = qb + qs; a.q_scatter = qb + 2 * qs; a.q_escape = qb + 3 * qs; a.q_shadow = qb + 4 * qs; a.q_nee = qb + 5 * qs; a.q_regen = qb + 6 * qs;

@@ -230,6 +230,18 @@ __global__ void k_majorant_grid(const float *data, int rx, int ry, int rz, int c
     maj[c] = m;
 }
 
+// fat-voxel copy (DGrid::fat): one thread per record
+__global__ void k_grid_fatten(const float *data, int rx, int ry, int rz, float4 *fat) {
+    const size_t n = (size_t) (rx + 1) * (ry + 1) * (rz + 1);
+    for (size_t r = (size_t) blockIdx.x * blockDim.x + threadIdx.x; r < n; r += (size_t) gridDim.x * blockDim.x) {
+        const int rix = (int) (r % (rx + 1)), riy = (int) ((r / (rx + 1)) % (ry + 1)), riz = (int) (r / ((size_t) (rx + 1) * (ry + 1)));
+        const int x0 = max(rix - 1, 0), x1 = min(rix, rx - 1), y0 = max(riy - 1, 0), y1 = min(riy, ry - 1), z0 = max(riz - 1, 0), z1 = min(riz, rz - 1);
+        auto at = [&](int x, int y, int z) { return data[((size_t) z * ry + y) * rx + x]; };
+        fat[2 * r] = make_float4(at(x0, y0, z0), at(x1, y0, z0), at(x0, y1, z0), at(x1, y1, z0));
+        fat[2 * r + 1] = make_float4(at(x0, y0, z1), at(x1, y0, z1), at(x0, y1, z1), at(x1, y1, z1));
+    }
+}
+
 static int refresh_grid_derived(lr_ctx *c, uint32_t gi) {
     DGrid &g = c->h_grids[gi]; size_t n = c->grid_floats[gi];
     // max over all channels
@@ -240,6 +252,7 @@ static int refresh_grid_derived(lr_ctx *c, uint32_t gi) {
     g.maxv = (gi < c->grid_fixed_max.size() && c->grid_fixed_max[gi] >= 0.f) ? c->grid_fixed_max[gi] : mx;
     int nc = g.mx * g.my * g.mz;
     k_majorant_grid<<<(nc + 127) / 128, 128, 0, c->stream>>>(g.data, g.rx, g.ry, g.rz, g.ch, g.cell, g.mx, g.my, g.mz, (float *) g.maj);
+    if (g.fat) k_grid_fatten<<<c->n_sm * 8, 256, 0, c->stream>>>(g.data, g.rx, g.ry, g.rz, (float4 *) g.fat);
     LR_CUDA(c, cudaGetLastError());
     for (auto &m : c->h_media) if (m.m.kind == LR_MEDIUM_HETEROGENEOUS && m.m.sigma_t_grid == (int) gi) m.max_density = m.m.scale * g.maxv;
     LR_CUDA(c, cudaMemcpyAsync(c->d_grids->p, c->h_grids.data(), c->h_grids.size() * sizeof(DGrid), cudaMemcpyHostToDevice, c->stream));

@@ -182,6 +182,9 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         d.cell = s->integrator.majorant_cell ? (int) s->integrator.majorant_cell : 8;
         d.mx = (d.rx + d.cell - 1) / d.cell; d.my = (d.ry + d.cell - 1) / d.cell; d.mz = (d.rz + d.cell - 1) / d.cell;
         DevBuf *bm = c->newbuf(); LR_CUDA(c, bm->alloc((size_t) d.mx * d.my * d.mz * 4)); d.maj = bm->as<float>();
+        if (g.channels == 1 && g.filter == LR_FILTER_TRILINEAR && g.wrap == LR_WRAP_CLAMP && getenv("LR_NO_FAT") == nullptr) {      // fat-voxel copy: 32 B per record
+            DevBuf *bf = c->newbuf(); LR_CUDA(c, bf->alloc((size_t) (d.rx + 1) * (d.ry + 1) * (d.rz + 1) * 32)); d.fat = bf->as<float4>();
+        }
         if (g.differentiable) { DevBuf *bg = c->newbuf(); LR_CUDA(c, bg->alloc(n * 4)); LR_CUDA(c, cudaMemsetAsync(bg->p, 0, n * 4, c->stream)); d.grad = bg->as<float>(); }
     }
     c->h_media.resize(s->n_media);

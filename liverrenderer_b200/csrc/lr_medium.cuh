@@ -36,6 +36,17 @@ LR_DEV V3 grid_eval(const DGrid &g, V3 pw, GridTap *tap) {
     float flx = floorf(fx), fly = floorf(fy), flz = floorf(fz);
     int ix = (int) flx, iy = (int) fly, iz = (int) flz;
     float w1x = fx - flx, w1y = fy - fly, w1z = fz - flz, w0x = 1.f - w1x, w0y = 1.f - w1y, w0z = 1.f - w1z;
+    if (!WANT_TAP && g.fat) {                                      // fat-voxel record: same eight values, same weights, same fmadd order
+        const int rix = min(max(ix + 1, 0), g.rx), riy = min(max(iy + 1, 0), g.ry), riz = min(max(iz + 1, 0), g.rz);
+        const float4 *rec = g.fat + 2 * (((size_t) riz * (g.ry + 1) + riy) * (g.rx + 1) + rix);
+        const float4 a = __ldg(rec), b = __ldg(rec + 1);
+        float o = 0.f;
+        o = fmaf(a.x, __fmul_rn(__fmul_rn(w0x, w0y), w0z), o); o = fmaf(a.y, __fmul_rn(__fmul_rn(w1x, w0y), w0z), o);
+        o = fmaf(a.z, __fmul_rn(__fmul_rn(w0x, w1y), w0z), o); o = fmaf(a.w, __fmul_rn(__fmul_rn(w1x, w1y), w0z), o);
+        o = fmaf(b.x, __fmul_rn(__fmul_rn(w0x, w0y), w1z), o); o = fmaf(b.y, __fmul_rn(__fmul_rn(w1x, w0y), w1z), o);
+        o = fmaf(b.z, __fmul_rn(__fmul_rn(w0x, w1y), w1z), o); o = fmaf(b.w, __fmul_rn(__fmul_rn(w1x, w1y), w1z), o);
+        return mk3(o);
+    }
     int x0 = wrap_i(ix, g.rx, g.wrap), x1 = wrap_i(ix + 1, g.rx, g.wrap), y0 = wrap_i(iy, g.ry, g.wrap), y1 = wrap_i(iy + 1, g.ry, g.wrap),
         z0 = wrap_i(iz, g.rz, g.wrap), z1 = wrap_i(iz + 1, g.rz, g.wrap);
     uint32_t r00 = ((uint32_t) z0 * g.ry + y0) * g.rx, r10 = ((uint32_t) z0 * g.ry + y1) * g.rx,

@@ -6,7 +6,7 @@
 //   tris   : DTri[n_tris]     48 B each = 3 x float4 (p0,p1,p2 ; w lanes carry mesh / face ids),
 //            stored in Morton order (= leaf order) so neighbouring leaves share cache lines
 //   grids  : fp32 [z][y][x][c] as the reference (src/volumes/grid.cpp:152-156) + majorant
-//            super-grid [mz][my][mx] of local maxima (DDA mode)
+//            super-grid [mz][my][mx] of local maxima (DDA mode) + fat-voxel copy (DGrid::fat)
 #pragma once
 #include "lr_math.cuh"
 #include "../../include/lr_api.h"
@@ -33,6 +33,11 @@ struct DMesh {
 
 struct DGrid {
     const float *data; float *grad; const float *maj;              // maj: super-grid of local majorants (raw grid units)
+    // "fat voxel" copy for 1-channel trilinear clamp grids: record (ix+1, iy+1, iz+1) of (rx+1)(ry+1)(rz+1) holds the eight corner
+    // values of the lookup whose base corner is (ix, iy, iz), ix in [-1, rx-1] (indices clamped as the lookup clamps them), in the
+    // reference's corner order 000,100,010,110 | 001,101,011,111: one trilinear tap = two LDG.128 from ONE 32-byte sector
+    // instead of eight scattered 4-byte loads from four sectors.  Rebuilt from `data` whenever the grid changes.
+    const float4 *fat;
     int rx, ry, rz, ch; int mx, my, mz, cell;
     M4 to_local; V3 bmin, bmax; uint32_t filter, wrap; float maxv;
     uint32_t differentiable;

@@ -65,15 +65,15 @@ LR_DEV void trace_pop(TraceRay &r, const TraceStack<STK> &st) {
 }
 
 // Visit of an inner node (DNodeQ, lr_scene.cuh): the hit children -- inner nodes and triangles alike -- go onto the stack
-// farthest first (ORDERED) and the nearest becomes the lane's next item.  Triangles are NOT tested here: lanes that reach a
-// triangle wait until enough lanes of the warp hold one (trace kernel loop), so the Moeller-Trumbore code runs with many
+// farthest first and the nearest becomes the lane's next item (occlusion queries use the same order: near boxes first).
+// Triangles are NOT tested here: lanes that reach a triangle wait until enough lanes of the warp hold one (trace kernel loop), so the Moeller-Trumbore code runs with many
 // lanes instead of 2-3.  Nodes below `n_smem` are read from the shared-memory copy `s_nodes` (16-byte chunks rotated by
 // node >> 1 so that lanes at different nodes spread over all bank groups), the others from global memory.
 // Slab test per axis: plane = origin + q * cell, t = (plane - o) / d = f * A + B with f = 1 + q/128 (one PRMT per byte),
 // A = 128 * cell / d, B = (origin - o) / d - A.  Near / far planes are picked by the sign of d, so an unused child
 // (lo = 127 > hi = 0) fails, and fmaxf / fminf drop the NaNs of an axis-parallel ray (that axis then does not cull:
 // conservative).  The far side is widened by 4 ulp like the two-wide traversal does.
-template <bool ORDERED, typename STK>
+template <typename STK>
 LR_DEV void trace_visit(const DScene &sc, TraceRay &r, const uint4 *s_nodes, const uint32_t n_smem, const TraceStack<STK> &st) {
     const uint32_t n = (uint32_t) r.node; uint4 c0, c1, c2, c3;
     if (n < n_smem) {
@@ -98,22 +98,15 @@ LR_DEV void trace_visit(const DScene &sc, TraceRay &r, const uint4 *s_nodes, con
         t[i] = (tn <= tf && c[i] != 0x7fffffff) ? tn : LR_INF;
     }
 #undef LR_PL
-    if (ORDERED) {
-        // sort the (entry distance, child) pairs: 5-comparator network, nearest first
+    // sort the (entry distance, child) pairs: 5-comparator network, nearest first (misses last)
 #define LR_CSWAP(a, b) { const bool s = t[b] < t[a]; const float tlo = s ? t[b] : t[a], thi = s ? t[a] : t[b]; \
                          const int clo = s ? c[b] : c[a], chi = s ? c[a] : c[b]; t[a] = tlo; t[b] = thi; c[a] = clo; c[b] = chi; }
-        LR_CSWAP(0, 1) LR_CSWAP(2, 3) LR_CSWAP(0, 2) LR_CSWAP(1, 3) LR_CSWAP(1, 2)
+    LR_CSWAP(0, 1) LR_CSWAP(2, 3) LR_CSWAP(0, 2) LR_CSWAP(1, 3) LR_CSWAP(1, 2)
 #undef LR_CSWAP
-        if (t[3] != LR_INF) trace_push(r, st, c[3]);
-        if (t[2] != LR_INF) trace_push(r, st, c[2]);
-        if (t[1] != LR_INF) trace_push(r, st, c[1]);
-        if (t[0] != LR_INF) { r.node = c[0]; return; }
-    } else {
-        int next = TR_DONE;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) if (t[i] != LR_INF) { if (next != TR_DONE) trace_push(r, st, next); next = c[i]; }
-        if (next != TR_DONE) { r.node = next; return; }
-    }
+    if (t[3] != LR_INF) trace_push(r, st, c[3]);
+    if (t[2] != LR_INF) trace_push(r, st, c[2]);
+    if (t[1] != LR_INF) trace_push(r, st, c[1]);
+    if (t[0] != LR_INF) { r.node = c[0]; return; }
     trace_pop(r, st);
 }
 

@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(LR_TRACE_THREADS, 1) k_wv_trace(const __grid_c
         const unsigned leaves = __ballot_sync(0xffffffffu, at_leaf), inner = __ballot_sync(0xffffffffu, trace_walking(r) && !at_leaf);
         if (leaves != 0u && ((uint32_t) __popc(leaves) >= LR_TRACE_LEAF_BATCH || inner == 0u)) {
             if (at_leaf) trace_leaf<MODE == 1, false, STK>(sc, r, st);
-        } else if ((inner >> lane) & 1u) trace_visit<MODE != 1, STK>(sc, r, s_nodes, cfg.n_smem, st);
+        } else if ((inner >> lane) & 1u) trace_visit<STK>(sc, r, s_nodes, cfg.n_smem, st);
         if (exhausted && !__any_sync(0xffffffffu, r.node != TR_IDLE || have_a || have_b)) break;
     }
     flush_counters(cnt, 0, a.stats);

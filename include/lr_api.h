@@ -339,6 +339,25 @@ size_t lr_grid_size(const lr_ctx *ctx, uint32_t grid);       /* number of floats
 /* rays[n][8] = ox,oy,oz,dx,dy,dz,maxt,unused ; hits[n][4] = t, prim(as float bits), u, v */
 int  lr_ray_intersect(lr_ctx *ctx, const float *rays, uint64_t n, float *hits);
 
+/* ---- device known-answer probes ------------------------------------------ */
+/* The shading / lookup arithmetic of the hot path, one query per CUDA thread, so the reference's function-level tests run on
+   the device code: src/bsdfs/tests/test_principled.py:124-205, test_rough_dielectric.py:209-229, test_diffuse.py:14-37,
+   src/phase/tests/test_hg.py, test_isotropic.py, src/volumes/tests/test_grid.py:43-118, src/emitters/tests/test_envmap.py.
+   All buffers are HOST pointers; directions are in the local shading frame (BSDF) or world space (phase, emitters).       */
+/* BSDF::eval + BSDF::pdf: wi[n][3], wo[n][3] -> out[n][4] = value rgb (cosine included), pdf.  No textured parameter blocks. */
+int  lr_kat_bsdf_eval_pdf(lr_ctx *ctx, const lr_bsdf *bsdf, const float *wi, const float *wo, uint64_t n, float *out);
+/* BSDF::sample: wi[n][3], u[n][3] = sample1, sample2.x, sample2.y -> out[n][9] = wo(3), pdf, eta, weight(3), sampled_type (bits) */
+int  lr_kat_bsdf_sample(lr_ctx *ctx, const lr_bsdf *bsdf, const float *wi, const float *u, uint64_t n, float *out);
+/* PhaseFunction::sample + eval_pdf: wi[n][3], u[n][2] -> out[n][5] = wo(3), sampled pdf, eval_pdf(wi, wo) */
+int  lr_kat_phase(lr_ctx *ctx, uint32_t kind, float g, const float *wi, const float *u, uint64_t n, float *out);
+/* Volume::eval of grid `grid` of the uploaded scene at world points p[n][3] -> out[n][3]; use_fat = 0 forces the reference
+   layout path, 1 lets the lookup use the fat-voxel copy where the grid has one (identical results)                        */
+int  lr_kat_grid_eval(lr_ctx *ctx, uint32_t grid, const float *p, uint64_t n, float *out, int use_fat);
+/* Scene::sample_emitter_direction (no visibility test): in[n][5] = ref_p(3), u(2) -> out[n][7] = d(3), pdf, weight rgb */
+int  lr_kat_emitter_sample(lr_ctx *ctx, const float *ref_p_u, uint64_t n, float *out);
+/* environment emitter of the scene: d[n][3] = direction of travel -> out[n][4] = radiance rgb, pdf_direction(d) */
+int  lr_kat_env_eval_pdf(lr_ctx *ctx, const float *d, uint64_t n, float *out);
+
 /* ---- control ------------------------------------------------------------ */
 int  lr_cancel(lr_ctx *ctx);                    /* async-signal-safe             */
 int  lr_stats_get(lr_ctx *ctx, lr_stats *out);

@@ -117,6 +117,7 @@ API_SYMBOLS = [
     "lr_sample_lanes", "lr_render_backward", "lr_grid_update", "lr_grid_grad_zero", "lr_grid_grad_read",
     "lr_grid_grad_device_ptr", "lr_grid_size", "lr_ray_intersect", "lr_cancel", "lr_stats_get", "lr_set_stream",
     "lr_profile_enable", "lr_profile_get", "lr_stage_name",
+    "lr_kat_bsdf_eval_pdf", "lr_kat_bsdf_sample", "lr_kat_phase", "lr_kat_grid_eval", "lr_kat_emitter_sample", "lr_kat_env_eval_pdf",
 ]
 
 _LIB = None
@@ -161,6 +162,12 @@ def load_library(path: str | None = None):
     lib.lr_profile_enable.argtypes = [vp, C.c_int]; lib.lr_profile_enable.restype = C.c_int
     lib.lr_profile_get.argtypes = [vp, C.POINTER(lr_stage_profile)]; lib.lr_profile_get.restype = C.c_int
     lib.lr_stage_name.argtypes = [C.c_uint32]; lib.lr_stage_name.restype = C.c_char_p
+    lib.lr_kat_bsdf_eval_pdf.argtypes = [vp, C.POINTER(lr_bsdf), vp, vp, C.c_uint64, vp]; lib.lr_kat_bsdf_eval_pdf.restype = C.c_int
+    lib.lr_kat_bsdf_sample.argtypes = [vp, C.POINTER(lr_bsdf), vp, vp, C.c_uint64, vp]; lib.lr_kat_bsdf_sample.restype = C.c_int
+    lib.lr_kat_phase.argtypes = [vp, C.c_uint32, C.c_float, vp, vp, C.c_uint64, vp]; lib.lr_kat_phase.restype = C.c_int
+    lib.lr_kat_grid_eval.argtypes = [vp, C.c_uint32, vp, C.c_uint64, vp, C.c_int]; lib.lr_kat_grid_eval.restype = C.c_int
+    lib.lr_kat_emitter_sample.argtypes = [vp, vp, C.c_uint64, vp]; lib.lr_kat_emitter_sample.restype = C.c_int
+    lib.lr_kat_env_eval_pdf.argtypes = [vp, vp, C.c_uint64, vp]; lib.lr_kat_env_eval_pdf.restype = C.c_int
     if path is None:
         _LIB = lib
     return lib

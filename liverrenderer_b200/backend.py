@@ -92,8 +92,12 @@ class Context:
         return self.lib.lr_film_device_ptr(self.ctx)
 
     def sample_lanes(self, seed, spp, begin, end, out=None):
+        """Per-lane radiance [(end - begin) * n_passes, 4]; a render beyond 2^32 - 1 lanes is split into passes
+        (src/render/integrator.cpp:275-293) and every lane then has one row per pass: row = (lane - begin) * n_passes + pass."""
         if out is None:
-            out = np.empty((end - begin, 4), dtype=np.float32)
+            from .multi import lane_count
+            W, H = self.scene.film_size
+            out = np.empty(((end - begin) * lane_count(W, H, spp)[2], 4), dtype=np.float32)
         p, dev = _ptr(out)
         self._chk(self.lib.lr_sample_lanes(self.ctx, seed & 0xffffffff, spp, begin, end, p, dev), "lr_sample_lanes")
         return out
@@ -128,6 +132,41 @@ class Context:
         hits = np.empty((rays.shape[0], 4), dtype=np.float32)
         self._chk(self.lib.lr_ray_intersect(self.ctx, C.c_void_p(rays.ctypes.data), rays.shape[0], C.c_void_p(hits.ctypes.data)), "lr_ray_intersect")
         return hits
+
+    # -- device known-answer probes (lr_kat_*): numpy in, numpy out ---------------------------------
+    @staticmethod
+    def _f32(a, cols):
+        return np.ascontiguousarray(a, dtype=np.float32).reshape(-1, cols)
+
+    def kat_bsdf_eval_pdf(self, bsdf, wi, wo):
+        wi = self._f32(wi, 3); wo = self._f32(wo, 3); out = np.empty((wi.shape[0], 4), dtype=np.float32)
+        self._chk(self.lib.lr_kat_bsdf_eval_pdf(self.ctx, C.byref(bsdf), C.c_void_p(wi.ctypes.data), C.c_void_p(wo.ctypes.data), wi.shape[0], C.c_void_p(out.ctypes.data)), "lr_kat_bsdf_eval_pdf")
+        return out[:, :3], out[:, 3]
+
+    def kat_bsdf_sample(self, bsdf, wi, u):
+        wi = self._f32(wi, 3); u = self._f32(u, 3); out = np.empty((wi.shape[0], 9), dtype=np.float32)
+        self._chk(self.lib.lr_kat_bsdf_sample(self.ctx, C.byref(bsdf), C.c_void_p(wi.ctypes.data), C.c_void_p(u.ctypes.data), wi.shape[0], C.c_void_p(out.ctypes.data)), "lr_kat_bsdf_sample")
+        return {"wo": out[:, 0:3], "pdf": out[:, 3], "eta": out[:, 4], "weight": out[:, 5:8], "sampled_type": out[:, 8].copy().view(np.uint32)}
+
+    def kat_phase(self, kind, g, wi, u):
+        wi = self._f32(wi, 3); u = self._f32(u, 2); out = np.empty((wi.shape[0], 5), dtype=np.float32)
+        self._chk(self.lib.lr_kat_phase(self.ctx, kind, g, C.c_void_p(wi.ctypes.data), C.c_void_p(u.ctypes.data), wi.shape[0], C.c_void_p(out.ctypes.data)), "lr_kat_phase")
+        return out[:, :3], out[:, 3], out[:, 4]
+
+    def kat_grid_eval(self, grid, p, use_fat=True):
+        p = self._f32(p, 3); out = np.empty((p.shape[0], 3), dtype=np.float32)
+        self._chk(self.lib.lr_kat_grid_eval(self.ctx, grid, C.c_void_p(p.ctypes.data), p.shape[0], C.c_void_p(out.ctypes.data), 1 if use_fat else 0), "lr_kat_grid_eval")
+        return out
+
+    def kat_emitter_sample(self, ref_p, u):
+        a = np.concatenate([self._f32(ref_p, 3), self._f32(u, 2)], axis=1); a = np.ascontiguousarray(a); out = np.empty((a.shape[0], 7), dtype=np.float32)
+        self._chk(self.lib.lr_kat_emitter_sample(self.ctx, C.c_void_p(a.ctypes.data), a.shape[0], C.c_void_p(out.ctypes.data)), "lr_kat_emitter_sample")
+        return out[:, :3], out[:, 3], out[:, 4:7]
+
+    def kat_env_eval_pdf(self, d):
+        d = self._f32(d, 3); out = np.empty((d.shape[0], 4), dtype=np.float32)
+        self._chk(self.lib.lr_kat_env_eval_pdf(self.ctx, C.c_void_p(d.ctypes.data), d.shape[0], C.c_void_p(out.ctypes.data)), "lr_kat_env_eval_pdf")
+        return out[:, :3], out[:, 3]
 
     def cancel(self):
         self.lib.lr_cancel(self.ctx)

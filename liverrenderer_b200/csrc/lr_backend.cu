@@ -309,3 +309,4 @@ static int build_bvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi) {
 }
 
 #include "lr_backend_api.inl"
+#include "lr_kat.inl"

@@ -137,6 +137,14 @@ LR_DEV bool medium_clip(const DGrid &g, const Ray &ray, float &mint, float &maxt
     mint = fmaxf(0.f, mint); maxt = fminf(ray.maxt, maxt);
     return true;
 }
+// The reference weights a free-flight step that ends on a surface (or at the emitter) with Tr / pdf = exp(-majorant * t) / exp(-majorant * t),
+// t = the distance from the step's start to that surface, measured with the GLOBAL majorant and NOT clipped to the volume's box
+// (volpath.cpp:228-232, :504-511).  The ratio is 1 -- unless exp() underflows to 0 in fp32 (majorant * t > ~103), in which case the
+// reference sets the weight to 0.  That happens for a ray that carries a medium through open space (an unbounded segment: si.t = inf,
+// or a far emitter), e.g. behind the intersecting shells of the Liver-MultiMesh scene.  The DDA walks reproduce the rule on their last
+// step, so that production tracking agrees with the reference on such scenes too.  `t_from`: start of the last step, `t_to`: its end.
+LR_DEV bool reference_step_underflows(const DMedium &m, float t_from, float t_to) { return expf(-m.max_density * (t_to - t_from)) == 0.f; }
+
 LR_DEV bool medium_uses_dda(const DScene &sc, const DMedium &m) {
     return sc.integ.tracking == LR_TRACKING_DDA && m.m.kind == LR_MEDIUM_HETEROGENEOUS;
 }

@@ -76,9 +76,13 @@ LR_DEV Sampler wv_rng(const WVPlanes &p, uint32_t s) { const ulonglong2 r = p.rn
 LR_DEV void wv_rng_store(const WVPlanes &p, uint32_t s, const Sampler &m) { p.rng(s) = make_ulonglong2(m.state, m.inc); }
 LR_DEV uint32_t wv_bucket(const DScene &sc, const Hit &h) { return (__float_as_uint(sc.tris_gid[h.prim].v2.w) >> 1) & 3u; }
 
+LR_DEV bool wv_finite(V3 v) { return isfinite(v.x + v.y + v.z); }
+
 // volpath.cpp:160-178: the russian-roulette + depth test at the top of a loop iteration
+// (a throughput that is no longer finite -- 0 * inf after an underflowed pdf, about one path in 1e6 on the nested-shell scene -- ends the
+// path: the reference would carry the NaN into the pixel)
 LR_DEV bool wv_rr(const DScene &sc, Sampler &smp, V3 &thr, float eta, uint32_t depth) {
-    bool active = any_nonzero(thr);
+    bool active = any_nonzero(thr) && wv_finite(thr);
     const float q = fminf(hmax(thr) * sqr(eta), .95f);
     const bool perform_rr = depth > (uint32_t) sc.rr_depth;
     if (active) { const float u = smp.next_1d(); active &= (u < q) || !perform_rr; }
@@ -93,6 +97,7 @@ LR_DEV bool wv_rr(const DScene &sc, Sampler &smp, V3 &thr, float eta, uint32_t d
 template <int C, bool TO_FILM>
 LR_DEV void wv_finish(const DScene &sc, const WVArgs &a, bool pred, float4 lane_pos, V3 L, uint32_t flags) {
     const bool valid = (flags & WF_VALID_RAY) != 0;
+    if (!wv_finite(L)) L = mk3(0.f);              // a non-finite path (see wv_rr) contributes nothing instead of poisoning its pixel
     if (!TO_FILM) {
         if (pred) {
             const uint64_t lane = ((uint64_t) __float_as_uint(lane_pos.y) << 32) | __float_as_uint(lane_pos.x);
@@ -402,9 +407,9 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
                     // production tracking: delta tracking against the local majorants of the super-grid.  The majorant is one
                     // scalar for all channels (heterogeneous.cpp:163), so Tr/pdf reduces to 1/mu at a collision and 1 at a surface.
                     const DGrid &g = sc.grids[m.m.sigma_t_grid];
-                    float mint, maxt;
+                    float mint, maxt, t_last = 0.f;
                     if (medium_clip(g, ray, mint, maxt)) {
-                        const float t_end = fminf(maxt, hit_t);
+                        const float t_end = fminf(maxt, hit_t); t_last = mint;
                         if (mint < t_end) {
                             DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
                             while (dda_walk(g, m.m.scale, dd, t, tau, t_end, mu)) {
@@ -412,7 +417,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
                                 V3 pt = ray_at(ray, t);
                                 V3 st = grid_eval<false>(g, pt, nullptr) * m.m.scale, sn = mk3(mu) - st;
                                 float pn = hmean(sn / mu);
-                                if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); continue; }
+                                if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); t_last = t; continue; }
                                 depth += 1; cnt.real_scatters++; p.lsp(slot) = make_float4(pt.x, pt.y, pt.z, p.lsp(slot).w);
                                 if (!(depth < sc.max_depth)) { event = 0; break; }
                                 thr *= (st * medium_albedo(sc, m, pt)) / (mu * hmean(st / mu));
@@ -420,7 +425,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
                             }
                         }
                     }
-                    if (event < 0) event = 2;
+                    if (event < 0) { event = 2; if (reference_step_underflows(m, t_last, hit_t)) thr = mk3(0.f); }
                     break;
                 }
                 MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
@@ -473,7 +478,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
     const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
     uint32_t slot = 0, depth = 0, f = 0; int event = -2;                  // -2 idle, -1 walking, 0 end of path, 1 scatter, 2 boundary
     Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f; V3 thr = mk3(0.f);
-    float hit_t = 0.f, t = 0.f, tau = 0.f, t_end = 0.f, mu_scale = 0.f; int grid_id = 0; DDA dd{};
+    float hit_t = 0.f, t = 0.f, tau = 0.f, t_end = 0.f, mu_scale = 0.f, t_last = 0.f; int grid_id = 0; DDA dd{};
     Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
     bool exhausted = false;
     for (;;) {
@@ -498,12 +503,13 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
                     t4 = p.thr(slot); thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
                     h0 = wf_hit(p.hit(slot)); hit_t = h0.t;
                     const DMedium &m = sc.media[wf_medium(f)]; grid_id = m.m.sigma_t_grid; mu_scale = m.m.scale; const DGrid &g = sc.grids[grid_id];
-                    event = 2;
+                    event = 2; t_last = 0.f;
                     float mint, maxt;
                     if (medium_clip(g, ray, mint, maxt)) {
-                        t_end = fminf(maxt, hit_t);
+                        t_end = fminf(maxt, hit_t); t_last = mint;
                         if (mint < t_end) { dda_init(g, ray, mint, dd); t = mint; tau = -logf(1.f - smp.next_1d()); event = -1; }
                     }
+                    if (event == 2 && reference_step_underflows(m, t_last, hit_t)) thr = mk3(0.f);
                 }
             }
         }
@@ -518,7 +524,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
                 const float dtau = mu * (t_exit - t);
                 if (dtau >= tau && mu > 0.f) { t = fminf(t + tau / mu, t_exit); collide = true; break; }
                 tau -= dtau; t = t_exit;
-                if (t_exit >= t_end) { event = 2; break; }
+                if (t_exit >= t_end) { event = 2; if (reference_step_underflows(sc.media[wf_medium(f)], t_last, hit_t)) thr = mk3(0.f); break; }
                 dda_advance(g, dd);
             }
         }
@@ -529,7 +535,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
             V3 pt = ray_at(ray, t);
             V3 st = grid_eval<false>(g, pt, nullptr) * mu_scale, sn = mk3(mu) - st;
             float pn = hmean(sn / mu);
-            if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); }
+            if (smp.next_1d() < pn) { thr *= sn / (mu * pn); tau = -logf(1.f - smp.next_1d()); t_last = t; }
             else {
                 depth += 1; cnt.real_scatters++;
                 float *lp = reinterpret_cast<float *>(&p.lsp(slot)); lp[0] = pt.x; lp[1] = pt.y; lp[2] = pt.z;
@@ -581,7 +587,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_shade_a_medium(const __gr
                     const float phase_val = phase.eval_pdf(wi, ds.d);
                     const V3 w = thr * phase_val * mis_weight(ds.pdf, ds.delta ? 0.f : phase_val) * ev;
                     p.nw(slot) = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
-                    nee = true;
+                    nee = wv_finite(w);
                 }
                 wv_rng_store(p, slot, smp);
             }
@@ -620,7 +626,7 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_a_surface(cons
                 if (!count_direct) { DirectionSample ds = ds_from_si(sc, si, mk3(l4.x, l4.y, l4.z)); emitter_pdf = pdf_emitter_direction(sc, ds); }
                 const V3 emitted = eval_emitter_at(sc, emitter, si);
                 const V3 c = count_direct ? thr * emitted : thr * mis_weight(l4.w, emitter_pdf) * emitted;
-                float4 r4 = p.res(slot); r4.x += c.x; r4.y += c.y; r4.z += c.z; p.res(slot) = r4;
+                if (wv_finite(c)) { float4 r4 = p.res(slot); r4.x += c.x; r4.y += c.y; r4.z += c.z; p.res(slot) = r4; }
             }
             if (!si_valid(si)) {                                   // only after the hidden-emitter skip above: nothing behind the emitter
                 gone = true; f |= WF_DEAD; reinterpret_cast<float *>(&p.d(slot))[3] = __uint_as_float(f);
@@ -632,7 +638,7 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_a_surface(cons
                         const V3 wo = si.sh.to_local(ds.d); float bsdf_pdf; const V3 bsdf_val = bsdf.eval_pdf(si.wi, wo, bsdf_pdf);
                         const V3 w = thr * bsdf_val * mis_weight(ds.pdf, ds.delta ? 0.f : bsdf_pdf) * ev;
                         p.nw(slot) = make_float4(w.x, w.y, w.z, __int_as_float(walk_medium));
-                        nee = true;
+                        nee = wv_finite(w);
                     }
                     wv_rng_store(p, slot, smp);
                 }
@@ -705,20 +711,21 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_nee(const __grid_constant
                     // ratio tracking over the whole medium segment against the local majorants: T *= sigma_n / mu per tentative collision
                     const DMedium &m = sc.media[medium]; const DGrid &g = sc.grids[m.m.sigma_t_grid];
                     if (needs_intersection) { cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false; }
-                    float mint, maxt;
+                    float mint, maxt, t_last = 0.f;
                     if (medium_clip(g, ray, mint, maxt)) {
-                        const float t_end = fminf(maxt, si_t);
+                        const float t_end = fminf(maxt, si_t); t_last = mint;
                         if (mint < t_end) {
                             DDA dd; dda_init(g, ray, mint, dd); float t = mint, tau = -logf(1.f - smp.next_1d()), mu;
                             while (dda_walk(g, m.m.scale, dd, t, tau, t_end, mu)) {
                                 cnt.collisions++;
                                 V3 st = grid_eval<false>(g, ray_at(ray, t), nullptr) * m.m.scale;
-                                transmittance *= (mk3(mu) - st) / mu;
+                                transmittance *= (mk3(mu) - st) / mu; t_last = t;
                                 if (!any_nonzero(transmittance)) break;
                                 tau = -logf(1.f - smp.next_1d());
                             }
                         }
                     }
+                    if (reference_step_underflows(m, t_last, fminf(remaining_dist, si_t))) transmittance = mk3(0.f);
                     if (si_t > remaining_dist) total_dist = ds_dist;        // nothing but medium up to the emitter (volpath.cpp:494-496)
                     escaped_medium = true; active_medium = false;
                 } else if (active_medium) {

@@ -127,7 +127,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
     const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128, grid_tr = c->n_sm;      // trace: one block of LR_TRACE_THREADS per SM
     const bool stk16 = c->bvh4_small; const size_t smem_tr = c->trace_smem;
     const bool multipass = ra.n_passes > 1;
-    const int shadow_mode = (c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf) ? 1 : 2;
+    const int shadow_mode = (c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf && !getenv("LR_SHADOW_CLOSEST")) ? 1 : 2;   // LR_SHADOW_CLOSEST: A/B of the any-hit query
     uint64_t launches = 0; bool lanes_done = false; const bool dbg_sync = getenv("LR_WF_SYNC") != nullptr;
     // per-stage CUDA events (profile mode: one batch in flight, so the intervals do not overlap)
     std::vector<cudaEvent_t> &kev = c->prof_ev; size_t kev_used = 0; std::vector<int> kev_kind;

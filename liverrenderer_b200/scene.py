@@ -127,6 +127,13 @@ class Scene:
             elif t in ("biovolpath", "biovolpath06", "volpathmis", "direct", "aov", "moment", "ptracer", "stokes", "depth",
                        "prb", "prbvolpath_basic", "direct_projective", "prb_projective"):
                 raise NotImplementedError(f"integrator plugin '{t}' is outside the hot path (path, volpath, prbvolpath)")
+            elif t in ("diffuse", "roughdielectric", "principled", "null", "dielectric", "bumpmap", "homogeneous", "heterogeneous"):
+                pass                                  # named BSDFs / media: handled by the first pass
+            else:
+                # anything else would silently vanish from the render (a `point` emitter, a `ply` shape, a `plastic` BSDF ...)
+                raise NotImplementedError(f"plugin '{t}' (object '{name}') is outside the hot path; supported top-level plugins: "
+                                          "perspective, path/volpath/prbvolpath, rectangle/cube/sphere/obj/mesh, constant/envmap, "
+                                          "diffuse/roughdielectric/principled/null/dielectric/bumpmap, homogeneous/heterogeneous")
         if not hasattr(self, "_sensor_dict"):
             raise ValueError("scene has no 'perspective' sensor")
         self._build_sensor(self._sensor_dict)

@@ -141,3 +141,15 @@ def test_default_parameters_and_errors(tmp_path):
     (tmp_path / "main.xml").write_text(head + '<include filename="inc.xml"/></scene>')
     sc2 = mi.load_file(str(tmp_path / "main.xml"))
     assert len(sc2.emitters) == 1 and len(sc2.meshes) == 2
+
+
+def test_unknown_top_level_plugin_raises():
+    """A plugin the path does not implement must not silently drop out of the render (the reference's PluginManager raises
+    on an unknown plugin name, src/core/plugin.cpp): a point light, a ply shape, a plastic BSDF ..."""
+    base = {"type": "scene", "integrator": {"type": "path"},
+            "sensor": {"type": "perspective", "film": {"type": "hdrfilm", "width": 4, "height": 4}},
+            "env": {"type": "constant", "radiance": {"type": "rgb", "value": 1.0}}}
+    mi.load_dict(dict(base))
+    for extra in ({"type": "point", "intensity": 1.0}, {"type": "ply", "filename": "x.ply"}, {"type": "plastic"}):
+        with pytest.raises(NotImplementedError, match=extra["type"]):
+            mi.load_dict(dict(base, thing=extra))

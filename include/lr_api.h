@@ -338,6 +338,16 @@ size_t lr_grid_size(const lr_ctx *ctx, uint32_t grid);       /* number of floats
 /* ---- ray-cast probe (parity of the LBVH against the oracle) ------------- */
 /* rays[n][8] = ox,oy,oz,dx,dy,dz,maxt,unused ; hits[n][4] = t, prim(as float bits), u, v */
 int  lr_ray_intersect(lr_ctx *ctx, const float *rays, uint64_t n, float *hits);
+/* The same query without any allocation.  NO COUNTERPART IN THE REFERENCE: added for
+   callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).  Its scratch -- staging of host buffers and
+   the per-ray traversal stack of the 4-wide tree -- is one file-scope 3.375 MiB device array held by every GPU that loads the
+   library (liverrenderer_b200/csrc/lr_noalloc.inl).  Limits: n <= lr_noalloc_max_rays() (8192) per call, else
+   LR_ERR_INVALID_ARG; scenes whose tree needs more than 96 stack entries per ray return LR_ERR_UNSUPPORTED.  is_device = 0:
+   HOST buffers, the call returns with hits filled; is_device = 1: 16-byte-aligned DEVICE buffers, the kernel is only
+   enqueued on the context's stream.  Every call shares the array (nothing in it needs clearing between calls): calls that
+   overlap on the GPU race -- serialise them.  Results equal lr_ray_intersect's bit for bit.                                */
+int  lr_ray_intersect_noalloc(lr_ctx *ctx, const float *rays, uint64_t n, float *hits, int is_device);
+uint64_t lr_noalloc_max_rays(void);
 
 /* ---- device known-answer probes ------------------------------------------ */
 /* The shading / lookup arithmetic of the hot path, one query per CUDA thread, so the reference's function-level tests run on

@@ -133,6 +133,22 @@ class Context:
         self._chk(self.lib.lr_ray_intersect(self.ctx, C.c_void_p(rays.ctypes.data), rays.shape[0], C.c_void_p(hits.ctypes.data)), "lr_ray_intersect")
         return hits
 
+    def ray_intersect_noalloc(self, rays, hits=None):
+        """lr_ray_intersect_noalloc: the same query with its scratch in the library's static device array (no cudaMalloc; at
+        most `lr_noalloc_max_rays()` rays per call).  numpy in -> numpy out; a CUDA torch tensor [n, 8] in -> the kernel is
+        enqueued on the context's stream and writes the CUDA tensor `hits` [n, 4], which the caller provides."""
+        if isinstance(rays, np.ndarray) or not hasattr(rays, "data_ptr"):
+            rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+            hits = np.empty((rays.shape[0], 4), dtype=np.float32)
+            self._chk(self.lib.lr_ray_intersect_noalloc(self.ctx, C.c_void_p(rays.ctypes.data), rays.shape[0], C.c_void_p(hits.ctypes.data), 0),
+                      "lr_ray_intersect_noalloc")
+            return hits
+        if hits is None or not rays.is_cuda or not hits.is_cuda or not rays.is_contiguous() or not hits.is_contiguous():
+            raise ValueError("device call: contiguous CUDA float32 tensors rays [n, 8] and hits [n, 4] are both required")
+        self._chk(self.lib.lr_ray_intersect_noalloc(self.ctx, C.c_void_p(rays.data_ptr()), rays.shape[0], C.c_void_p(hits.data_ptr()), 1),
+                  "lr_ray_intersect_noalloc")
+        return hits
+
     # -- device known-answer probes (lr_kat_*): numpy in, numpy out ---------------------------------
     @staticmethod
     def _f32(a, cols):

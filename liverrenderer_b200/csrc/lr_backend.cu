@@ -48,6 +48,7 @@ struct WVPool {
 
 struct lr_ctx {
     int device = 0; cudaStream_t stream = nullptr; bool own_stream = false;
+    void *noalloc_ptr = nullptr;                    // device address of g_noalloc_scratch on `device` (lr_noalloc.inl)
     std::string err; bool has_scene = false;
     DScene sc{};
     // device storage
@@ -310,3 +311,4 @@ static int build_bvh(lr_ctx *c, const std::vector<DTri> &tris, V3 lo, V3 hi) {
 
 #include "lr_backend_api.inl"
 #include "lr_kat.inl"
+#include "lr_noalloc.inl"

@@ -2,18 +2,22 @@
 """bench.py -- headline benchmark of the B200 volumetric path-tracing backend (BASELINE.json metric:
 samples/s + Mrays/s of the `volpath` forward render and the `prbvolpath` gradient step).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--partition samples|seeds]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One "step" = one full render of the workload scene (C3: Liver-SingleMesh, heterogeneous gridvolume, `volpath`,
-1080x1080, --spp samples per pixel) with every input already resident in HBM.  Multi-GPU: one process per GPU,
-weak scaling -- every rank renders the whole config with seed+rank (independent sample sets of the same image), the
-film accumulators are summed with one NCCL all-reduce per step; `value` = samples of all ranks / max-over-ranks time.
-The `prb` object is the C5 inverse step (primal + prbvolpath adjoint + NCCL all-reduce of the grid gradient).
-`e2e` is the same render through the public host API (`params.update()` + `mi.render`) with pinned HOST buffers:
-the density grid goes host->device and the developed image device->host inside the timed region.
-`--impl reference` times the CPU oracle (the restatement of the reference's algorithm, oracle/) on the host cores.
-Prints ONE JSON line on rank 0.
+1080x1080, --spp samples per pixel) with every input already resident in HBM.
+Multi-GPU, one process per GPU.  `--partition samples` (default, "scaling": "strong"): ONE frame is split by sample index --
+rank r renders spp / N samples of every pixel (lr_set_lane_map), no communication while rendering, then the film accumulators are
+summed IN PLACE (NCCL all-reduce on lr_film_device_ptr) and developed; `value` = samples of the frame / max-over-ranks time.
+`--partition seeds` ("weak"): every rank renders the whole config with seed + rank; at N > 1 the default run reports it under
+the key `weak`.  The `prb` object is the C5 inverse step split the same way (primal + prbvolpath adjoint + in-place NCCL
+all-reduce of the grid gradient).  `e2e` is the same render through the public host API (`params.update()` + render) with pinned
+HOST buffers: the density grid goes host->device and the developed image device->host inside the timed region.
+`stages` is the per-stage table of one extra step in the library's profile mode (one batch in flight, CUDA events around every
+launch on the launching stream); `rooflines` bounds each dominant stage, `roofline` is the entry of the largest one.
+`--impl reference` times the CPU oracle (the restatement of the reference's algorithm, oracle/, rebuilt -O3 -march=native on the
+box) on the host cores.  Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -55,6 +59,9 @@ def parse_args():
     ap.add_argument("--res", type=int, default=1080)
     ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step (0 => the config's)")
     ap.add_argument("--tracking", default="dda", choices=["reference", "dda"])
+    ap.add_argument("--partition", default="samples", choices=["samples", "seeds"],
+                    help="N > 1: samples = one frame split by sample index (strong scaling), seeds = every rank renders the frame (weak)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the reference-order / bump-map / C3-XL side measurements")
     ap.add_argument("--no-prb", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-spp", type=int, default=4, help="spp of the bounded CPU-baseline sample")
@@ -135,7 +142,7 @@ def cpu_sample(args, spp_cpu: int, repeats: int = 1):
     from tests import orc
     d, _, name = workload_scene(args, for_cpu=True)
     d["sensor"]["sampler"]["sample_count"] = spp_cpu
-    sc = mi.load_dict(d); o = orc.OracleScene(sc, threads=0)
+    sc = mi.load_dict(d); o = orc.OracleScene(sc, threads=0, fast=True)
     cores = os.cpu_count() or 1
     best = None
     for r in range(repeats):
@@ -146,8 +153,8 @@ def cpu_sample(args, spp_cpu: int, repeats: int = 1):
     dt, st = best
     W, H = sc.film_size
     return st["samples"] / dt, {"value": st["samples"] / dt, "unit": UNIT, "cores": cores, "kind": "port",
-                                "sample": f"{name} at {spp_cpu} spp ({W * H * spp_cpu} samples, {dt:.1f} s), oracle/ liborc.so, std::thread x{cores}, "
-                                          "global-majorant delta tracking as the reference",
+                                "sample": f"{name} at {spp_cpu} spp ({W * H * spp_cpu} samples, {dt:.1f} s), oracle/ rebuilt on this host with g++ {orc.FAST_FLAGS}, "
+                                          f"std::thread x{cores}, global-majorant delta tracking as the reference",
                                 "mrays_per_s": st["rays"] / dt / 1e6, "collisions_per_s": st["collisions"] / dt}
 
 
@@ -160,7 +167,7 @@ def run_reference(args):
     from tests import orc
     spp_cpu = args.cpu_spp
     d["sensor"]["sampler"]["sample_count"] = spp_cpu
-    sc = mi.load_dict(d); o = orc.OracleScene(sc, threads=0); W, H = sc.film_size
+    sc = mi.load_dict(d); o = orc.OracleScene(sc, threads=0, fast=True); W, H = sc.film_size
     cores = os.cpu_count() or 1
     for w in range(min(args.warmup, 1)):                      # one warm-up pass is enough for a CPU code (page-in, thread pool)
         o.render(seed=1000 + w, spp=spp_cpu)
@@ -170,29 +177,102 @@ def run_reference(args):
     dt = time.perf_counter() - t; st = o.stats()
     v = st["samples"] / dt
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong" if args.partition == "samples" else "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": {"workload": name, "spp_per_step": spp_cpu, "samples_per_step": W * H * spp_cpu,
                                             "note": "each step is a bounded sample (reduced spp) of the same scene"},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                             "sample": f"{args.steps} x ({W}x{H} at {spp_cpu} spp) through oracle/liborc.so on {cores} threads"},
+                             "sample": f"{args.steps} x ({W}x{H} at {spp_cpu} spp) through the oracle rebuilt on this host (g++ {orc.FAST_FLAGS}) on {cores} threads"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "mrays_per_s": st["rays"] / dt / 1e6, "collisions_per_s": st["collisions"] / dt, "gpu_launches": 0}
     emit(line)
 
 
+def cpu_sample_prb(args, res: int = 512, spp: int = 1):
+    """C5 on the host cores: primal + prbvolpath adjoint of the oracle (timing build), a bounded sample of the step."""
+    import liverrenderer_b200 as mi
+    from liverrenderer_b200 import scenes
+    from tests import orc
+    sc = mi.load_dict(scenes.sphere_liver_inverse(res=res, spp=spp, grid_res=128, tracking="reference"))
+    o = orc.OracleScene(sc, threads=0, fast=True); cores = os.cpu_count() or 1
+    g = np.full((res, res, 3), 2.0 / (res * res * 3), dtype=np.float32)
+    o.grid_grad_zero(0); o.stats_reset(); t = time.perf_counter()
+    o.render(seed=0, spp=spp); o.render_backward(g, seed=1, spp=spp); dt = time.perf_counter() - t
+    n = res * res * spp
+    return {"value": n / dt, "unit": "grad-samples/s", "cores": cores, "kind": "port",
+            "sample": f"C5 at {res}x{res} x {spp} spp: oracle primal render + render_backward ({n} lanes, {dt:.1f} s), g++ {orc.FAST_FLAGS}, std::thread x{cores}"}
+
+
 # --------------------------------------------------------------------------------------------------
 # B200 arm
 # --------------------------------------------------------------------------------------------------
-def _film_allreduce(ctx, torch, dist, film_buf):
-    """Sum the [H,W,C] film accumulators over ranks (one collective per render)."""
-    ctx.film_read(film_buf); dist.all_reduce(film_buf); ctx.film_write(film_buf)
+TRACE_BYTES_PER_RAY = 48          # 32 B in (origin + maxt, direction) + 16 B out (t, prim, u, v): lr_trace.cuh
+TRACK_BYTES_PER_COLLISION = 32    # the 8 fp32 corners of one trilinear sigma_t tap (SURVEY 8(d))
+PRB_BYTES_PER_COLLISION = 64      # the same tap read + its 8 gradient atomics
+
+
+def _load_json(name):
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", name)))
+    except Exception:
+        return None
+
+
+def timed_render(torch, ctx, stream, barrier, seed, spp, reps=1):
+    """One warm render, then `reps` timed ones (CUDA events on the context's stream); returns (ms per render, stats of the last)."""
+    ctx.film_clear(); ctx.render_lanes(seed, spp, 0, 0); barrier()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e0.record(stream)
+    for k in range(reps):
+        ctx.film_clear(); ctx.render_lanes(seed + 1 + k, spp, 0, 0)
+    e1.record(stream); barrier()
+    return e0.elapsed_time(e1) / reps, ctx.stats()
+
+
+def stage_table(ctx, seed, spp, hbm_peak, ncu):
+    """One extra step in profile mode -> per-stage ms / launches / items, and the rooflines built on it."""
+    ctx.profile(True); ctx.film_clear(); ctx.render_lanes(seed, spp, 0, 0); st = ctx.stats(); prof = ctx.stage_profile(); ctx.profile(False)
+    total = sum(v["ms"] for v in prof.values()) or 1.0
+    stages = {k: {"ms": round(v["ms"], 3), "share": round(v["ms"] / total, 4), "launches": v["launches"], "items": v["items"]}
+              for k, v in prof.items() if v["launches"] or v["items"]}
+    def ncu_of(kernel):
+        return (ncu or {}).get("kernels", {}).get(kernel)
+    def issue_entry(name, kernel, what):
+        s = prof.get(name)
+        if not s or not s["ms"]:
+            return None
+        per_s = s["items"] / (s["ms"] * 1e-3); gbs = per_s * TRACE_BYTES_PER_RAY / 1e9; m = ncu_of(kernel) or {}
+        e = {"kernel": kernel, "stage": name, "what": what, "bound": "sm_issue", "share_of_step": round(s["ms"] / total, 4),
+             "achieved": per_s / 1e6, "unit": "Mrays/s", "kernel_ms": s["ms"] / max(s["launches"], 1), "units_per_launch": s["items"] / max(s["launches"], 1),
+             "algorithmic_bytes_per_unit": TRACE_BYTES_PER_RAY, "algorithmic_GBps": gbs, "frac_of_hbm_peak": gbs / hbm_peak,
+             "issue_active_pct": m.get("issue_active_pct"), "threads_per_inst": m.get("threads_per_inst"),
+             "lane_issue_utilisation": (m["issue_active_pct"] / 100.0 * m["threads_per_inst"] / 32.0) if m.get("issue_active_pct") and m.get("threads_per_inst") else None,
+             "traffic": m.get("dram_bytes_per_launch"), "source": (ncu or {}).get("source")}
+        return e
+    rl = []
+    for name, kernel, what in (("trace_closest", "k_wv_trace<0>", "closest-hit query of every path segment, 4-wide quantized BVH in shared memory"),
+                               ("trace_shadow", "k_wv_trace<1>", "any-hit shadow rays of emitter sampling")):
+        e = issue_entry(name, kernel, what)
+        if e:
+            rl.append(e)
+    tn_ms = prof.get("track", {}).get("ms", 0.0) + prof.get("nee", {}).get("ms", 0.0)
+    if tn_ms > 0:
+        b = st["collisions"] * float(TRACK_BYTES_PER_COLLISION); ach = b / (tn_ms * 1e-3) / 1e9
+        n_l = prof["track"]["launches"] + prof["nee"]["launches"]; m = ncu_of("k_wv_track_dda") or {}
+        rl.append({"kernel": "k_wv_track_dda + k_wv_nee", "stage": "track+nee", "what": "majorant-DDA free-flight / ratio tracking, trilinear sigma_t taps", "bound": "hbm",
+                   "share_of_step": round(tn_ms / total, 4), "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                   "algorithmic_bytes_per_unit": TRACK_BYTES_PER_COLLISION, "units_per_launch": st["collisions"] / max(n_l, 1), "kernel_ms": tn_ms / max(n_l, 1),
+                   "traffic": m.get("dram_bytes_per_launch"), "l2_GBps": m.get("l2_GBps"), "source": (ncu or {}).get("source")})
+    if ncu and ncu.get("dram_bytes_per_sample"):
+        ach = ncu["dram_bytes_per_sample"] * st["samples"] / (total * 1e-3) / 1e9
+        rl.append({"kernel": "all stages", "stage": "step", "what": "path state + queues + grid + film: DRAM bytes of every kernel of the step (ncu) / step time", "bound": "hbm",
+                   "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "dram_bytes_per_sample": ncu["dram_bytes_per_sample"], "source": ncu.get("source")})
+    return {"stages": stages, "total_ms": total, "samples": st["samples"], "rays": st["rays"], "collisions": st["collisions"]}, rl
 
 
 def run_b200(args):
     import torch
     import torch.distributed as dist
     import liverrenderer_b200 as mi
-    from liverrenderer_b200 import scenes
+    from liverrenderer_b200 import multi
 
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
@@ -211,16 +291,24 @@ def run_b200(args):
     sc = mi.load_dict(d); W, H = sc.film_size
     ctx = mi.Context(local).upload(sc)
     stream = torch.cuda.current_stream(dev); ctx.set_stream(stream.cuda_stream)
-    C = ctx.film_channels()
-    film_buf = torch.empty((H, W, C), dtype=torch.float32, device=dev)
+    film = multi.film_tensor(ctx, dev)                                      # aliases lr_film_device_ptr: the all-reduce runs in place
     out_dev = torch.empty((H, W, sc.out_channels), dtype=torch.float32, device=dev)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)          # > 126 MB L2
+    _, spp_pass, _ = multi.lane_count(W, H, spp)
 
-    def fwd_step(k):
-        ctx.film_clear(); ctx.render_lanes(1000 * k + rank, spp, 0, 0)
+    def set_partition(mode):
+        share = multi.sample_share(spp_pass, rank, world) if (mode == "samples" and world > 1) else None
+        if share is not None:
+            ctx.set_lane_map(*share)
+        else:
+            ctx.set_lane_map()
+        return share
+
+    def fwd_step(k, mode):
+        ctx.film_clear(); ctx.render_lanes(1000 * k + (rank if mode == "seeds" else 0), spp, 0, 0)
         st = ctx.stats()
         if world > 1:
-            _film_allreduce(ctx, torch, dist, film_buf)
+            dist.all_reduce(film)
         ctx.film_develop(out_dev)
         return st
 
@@ -229,97 +317,107 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize(dev)
 
-    for w in range(args.warmup):
-        fwd_step(-1 - w)
-    clocks = ClockSampler(local); barrier(); clocks.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    tot = {"samples": 0, "rays": 0, "collisions": 0, "real_scatters": 0, "launches": 0, "tracking_ms": 0.0, "tracking_launches": 0}
-    for k in range(args.steps):
-        flush.fill_(k & 0xff)                                                 # L2 flush between timed iterations
+    def timed(mode, steps, warmup, clocks=None):
+        set_partition(mode)
+        for w in range(warmup):
+            fwd_step(-1 - w, mode)
         barrier()
-        ev[k][0].record(stream); st = fwd_step(k); ev[k][1].record(stream)
-        for key in tot:
-            tot[key] += st[key]
-        tot["launches"] += 1 + (2 if world > 1 else 0)                         # develop (+ 2 D2D copies around the NCCL all-reduce)
-    barrier(); clk = clocks.stop()
-    ms = sum(a.elapsed_time(b) for a, b in ev)
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    cnt = torch.tensor([tot["samples"], tot["rays"], tot["collisions"]], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt)
-    ms_max = float(t.item()); samples, rays, colls = (float(x) for x in cnt.tolist())
-    value = samples / (ms_max * 1e-3)
+        if clocks:
+            clocks.start()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        tot = {"samples": 0, "rays": 0, "collisions": 0, "real_scatters": 0, "launches": 0}
+        for k in range(steps):
+            flush.fill_(k & 0xff)                                             # L2 flush between timed iterations
+            barrier()
+            ev[k][0].record(stream); st = fwd_step(k, mode); ev[k][1].record(stream)
+            for key in tot:
+                tot[key] += st[key]
+            tot["launches"] += 1                                               # develop (the all-reduce is NCCL's kernel, not counted)
+        barrier(); clk = clocks.stop() if clocks else None
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        cnt = torch.tensor([tot["samples"], tot["rays"], tot["collisions"], tot["launches"]], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt)
+        set_partition("seeds")
+        samples, rays, colls, launches = (float(x) for x in cnt.tolist())
+        return dict(ms=float(t.item()), samples=samples, rays=rays, colls=colls, launches=launches, clk=clk, steps=steps)
 
-    # ---- roofline of the dominant kernel (rank 0): algorithmic 32 B per collision (8 fp32 corners of the sigma_t tap) ----
-    k_ms = tot["tracking_ms"] / max(tot["tracking_launches"], 1)
-    bytes_per_launch = tot["collisions"] / max(tot["tracking_launches"], 1) * 32.0
-    achieved = bytes_per_launch / (k_ms * 1e-3) / 1e9 if k_ms > 0 else 0.0
-    traffic = None; traffic_src = None
-    try:                                                     # dram__bytes_read+write per TRACK/NEE launch from the committed ncu capture
-        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_tracking_traffic.json")))
-        if args.workload == "c3" and args.tracking == "dda":
-            traffic = float(tj["traffic_bytes_per_launch"]); traffic_src = "profiles/r1_tracking_traffic.json (ncu dram__bytes_read.sum + dram__bytes_write.sum, mean over %d launches of: %s)" % (tj["launches"], tj["command"])
-    except Exception:
-        pass
-    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic, "traffic_source": traffic_src,
-                "algorithmic_bytes_per_launch": bytes_per_launch,
-                "kernel": "k_wf_track + k_wf_nee (free-flight / ratio tracking with trilinear sigma_t taps; CUDA events around every launch, "
-                          "lr_stats.tracking_ms / tracking_launches)",
-                "algorithmic_bytes_per_unit": 32, "units_per_launch": tot["collisions"] / max(tot["tracking_launches"], 1),
-                "kernel_ms": k_ms, "peak_source": peak_src}
-    ref_order = None
-    if args.tracking == "dda" and args.workload in ("c3", "c3xl"):
-        # the same render with the reference's draw order (one global majorant): the mode the per-path parity tests use
-        a2 = argparse.Namespace(**vars(args)); a2.tracking = "reference"
-        d2, _, _ = workload_scene(a2); c2 = mi.Context(local).upload(mi.load_dict(d2)); c2.set_stream(stream.cuda_stream)
-        c2.film_clear(); c2.render_lanes(7, spp, 0, 0); barrier()
-        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        e0.record(stream); c2.film_clear(); c2.render_lanes(8 + rank, spp, 0, 0); e1.record(stream); barrier()
-        st2 = c2.stats(); ms2 = e0.elapsed_time(e1)
-        ref_order = {"value": st2["samples"] / (ms2 * 1e-3), "unit": UNIT + " per GPU", "collisions_per_sample": st2["collisions"] / max(st2["samples"], 1),
-                     "collisions_per_s": st2["collisions"] / (ms2 * 1e-3), "tracking_GBps_algorithmic": st2["collisions"] * 32.0 / max(st2["tracking_ms"], 1e-9) / 1e6,
-                     "note": "LR_TRACKING_REFERENCE: identical PCG32 draw order to the reference (global majorant)"}
-        c2.close()
-    bump = None
-    if args.workload == "c3":
-        # the same config with the fork's own boundary (bumpmap(bitmap) over a smooth dielectric, scene.xml:31-40) instead of
-        # SURVEY 8(d)'s roughdielectric substitute: exercises the bitmap-texture / bump-frame code on the full workload
+    main_run = timed(args.partition, args.steps, args.warmup, ClockSampler(local))
+    weak = None
+    if world > 1 and args.partition == "samples":
+        r = timed("seeds", min(args.steps, 2), 1)
+        weak = {"value": r["samples"] / (r["ms"] * 1e-3), "unit": UNIT, "ms_per_step": r["ms"] / r["steps"], "steps": r["steps"],
+                "partition": "every rank renders the whole config with seed + rank; film all-reduce in place"}
+
+    # ---- per-stage table + rooflines: one extra step of this rank's share in profile mode ----
+    ncu = _load_json("r2_kernel_metrics.json") if (args.workload == "c3" and args.tracking == "dda") else None
+    set_partition(args.partition)
+    table, rooflines = stage_table(ctx, 4242, spp, hbm_peak, ncu)
+    set_partition("seeds"); barrier()
+    for e in rooflines:
+        e["peak_source"] = peak_src
+    dom = max((e for e in rooflines if e["stage"] != "step"), key=lambda e: e.get("share_of_step", 0.0), default=None)
+    roofline = None
+    if dom is not None:
+        gbs = dom.get("algorithmic_GBps", dom.get("achieved")) if dom["bound"] == "sm_issue" else dom["achieved"]
+        roofline = {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "traffic": dom.get("traffic"),
+                    "kernel": dom["kernel"], "stage": dom["stage"], "share_of_step": dom.get("share_of_step"), "kernel_ms": dom["kernel_ms"],
+                    "algorithmic_bytes_per_unit": dom["algorithmic_bytes_per_unit"], "units_per_launch": dom["units_per_launch"],
+                    "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_unit"] * dom["units_per_launch"], "peak_source": peak_src,
+                    "limiter": dom["bound"], "lane_issue_utilisation": dom.get("lane_issue_utilisation"), "issue_active_pct": dom.get("issue_active_pct"),
+                    "threads_per_inst": dom.get("threads_per_inst"), "traffic_source": dom.get("source"),
+                    "timing": "CUDA events around every launch of the stage on its stream, one extra step in profile mode (one batch in flight; "
+                              "in the timed region batches overlap on 3 streams, so per-launch intervals there would overlap too)",
+                    "note": "the dominant kernel reads its BVH from shared memory: its HBM fraction is small by design and SM issue is the bound "
+                            "(north star: 'SM issue rate for traversal'); see `rooflines` for every stage"}
+
+    extras = {}
+    if world == 1 and not args.no_extras and args.workload in ("c3", "c3xl") and args.tracking == "dda":
         from liverrenderer_b200 import scenes as _sc
-        d3 = _sc.liver_single_mesh(res=args.res, spp=spp, grid_res=256, tracking=args.tracking, surface="bumpmap")
-        c3 = mi.Context(local).upload(mi.load_dict(d3)); c3.set_stream(stream.cuda_stream)
-        c3.film_clear(); c3.render_lanes(7, spp, 0, 0); barrier()
-        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-        e0.record(stream); c3.film_clear(); c3.render_lanes(8 + rank, spp, 0, 0); e1.record(stream); barrier()
-        st3 = c3.stats(); ms3 = e0.elapsed_time(e1)
-        bump = {"value": st3["samples"] / (ms3 * 1e-3), "unit": UNIT + " per GPU", "mrays_per_s": st3["rays"] / (ms3 * 1e-3) / 1e6,
-                "collisions_per_sample": st3["collisions"] / max(st3["samples"], 1),
-                "note": "C3 with the boundary BSDF bumpmap(scale 0.005, bitmap 512^2 rgb) -> dielectric 1.38"}
-        c3.close()
-    return dict(ref_order=ref_order, bump=bump, torch=torch, dist=dist, mi=mi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local, spp=spp, name=name,
-                W=W, H=H, value=value, ms_max=ms_max, rays=rays, colls=colls, samples=samples, tot=tot, roofline=roofline, clk=clk,
-                barrier=barrier, flush=flush, hbm_peak=hbm_peak)
+        def side(dd, label, reps=2):
+            c2 = mi.Context(local).upload(mi.load_dict(dd)); c2.set_stream(stream.cuda_stream)
+            ms, st2 = timed_render(torch, c2, stream, barrier, 7, spp, reps); c2.close()
+            return {"value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "mrays_per_s": st2["rays"] / (ms * 1e-3) / 1e6,
+                    "collisions_per_sample": st2["collisions"] / max(st2["samples"], 1), "collisions_per_s": st2["collisions"] / (ms * 1e-3), "note": label}
+        a2 = argparse.Namespace(**vars(args)); a2.tracking = "reference"
+        extras["reference_order_tracking"] = side(workload_scene(a2)[0], "LR_TRACKING_REFERENCE: identical PCG32 draw order to the reference (one global majorant), "
+                                                  "the mode of the per-path parity tests and the algorithm the CPU baseline runs", reps=1)
+        if args.workload == "c3":
+            extras["bumpmap_surface"] = side(_sc.liver_single_mesh(res=args.res, spp=spp, grid_res=256, tracking="dda", surface="bumpmap"),
+                                             "C3 with the fork's own boundary BSDF: bumpmap(scale 0.005, bitmap 512^2 rgb) -> dielectric 1.38 (scene.xml:31-40)")
+            xl = side(_sc.liver_single_mesh(res=args.res, spp=spp, grid_res=512, tracking="dda"), "C3-XL: the same frame on a 512^3 sigma_t grid (512 MiB fp32 > 126 MB L2)")
+            b = xl["collisions_per_s"] * TRACK_BYTES_PER_COLLISION / 1e9
+            xl["ratio_to_c3"] = xl["value"] / (main_run["samples"] / (main_run["ms"] * 1e-3))
+            xl["roofline"] = {"bound": "hbm", "achieved": b, "peak": hbm_peak, "unit": "GB/s", "frac": b / hbm_peak, "traffic": None,
+                              "note": "32 B per collision over the WHOLE step time (tracking is one stage of several), so a lower bound on the tracking kernels' own rate"}
+            extras["c3xl"] = xl
+    return dict(extras=extras, weak=weak, torch=torch, dist=dist, mi=mi, multi=multi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local,
+                spp=spp, name=name, W=W, H=H, run=main_run, table=table, rooflines=rooflines, roofline=roofline, barrier=barrier, flush=flush, hbm_peak=hbm_peak,
+                set_partition=set_partition, film=film)
 
 
 def run_e2e(R, args):
     """Same render through the host API with HOST buffers: density grid pinned-host -> device (params.update():
-    lr_grid_update recomputes majorant + super-grid), render, developed image device -> pinned host."""
+    lr_grid_update recomputes majorant + super-grid), render of this rank's share, film all-reduce, developed image device ->
+    pinned host on rank 0 (the other ranks read one pixel of their own copy)."""
     torch, ctx, sc, dev, world, rank = R["torch"], R["ctx"], R["sc"], R["dev"], R["world"], R["rank"]
     dist = R["dist"]; W, H, spp = R["W"], R["H"], R["spp"]
     has_grid = len(sc.grid_arrays) > 0                            # C1/C2 have no gridvolume: the step's only host traffic is the image
     gi = 0; n = ctx.grid_size(gi) if has_grid else 0
     grid_host = torch.from_numpy(np.ascontiguousarray(sc.grid_arrays[gi]).reshape(-1)).pin_memory() if has_grid else None
     out_host = torch.empty((H, W, sc.out_channels), dtype=torch.float32).pin_memory()
-    film_buf = torch.empty((H, W, ctx.film_channels()), dtype=torch.float32, device=dev)
     steps = max(1, min(args.steps, 2))
+    R["set_partition"](args.partition)
 
     def step(k):
         if has_grid:
             ctx.grid_update(gi, grid_host)                      # H2D of the step's input + majorant rebuild
         if world == 1:
-            ctx.render(seed=1000 * k + rank, spp=spp, out=out_host)          # render + develop + D2H
+            ctx.render(seed=1000 * k, spp=spp, out=out_host)     # render + develop + D2H
         else:
-            ctx.film_clear(); ctx.render_lanes(1000 * k + rank, spp, 0, 0)
-            _film_allreduce(ctx, torch, dist, film_buf); ctx.film_develop(out_host)
+            ctx.film_clear(); ctx.render_lanes(1000 * k + (rank if args.partition == "seeds" else 0), spp, 0, 0)
+            dist.all_reduce(R["film"]); ctx.film_develop(out_host)
         return float(out_host[H // 2, W // 2, 0])                # the result is read on the host
 
     step(-1)
@@ -328,58 +426,70 @@ def run_e2e(R, args):
     for k in range(steps):
         step(k)
     e1.record(R["stream"]); R["barrier"](); wall = time.perf_counter() - t0
-    ms = max(e0.elapsed_time(e1), 0.0)
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    R["set_partition"]("seeds")
+    t = torch.tensor([max(e0.elapsed_time(e1), 0.0)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    return {"value": W * H * spp * steps * world / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(n * 4),
+    ms = float(t.item()); frames = world if args.partition == "seeds" else 1
+    return {"value": W * H * spp * steps * frames / (ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(n * 4),
             "d2h_bytes_per_step": int(out_host.numel() * 4), "steps": steps, "ms_per_step": ms / steps, "wall_ms_per_step": wall / steps * 1e3,
-            "api": "params.update() [lr_grid_update, pinned host grid] + mi.render [lr_render -> pinned host image]"}
+            "api": "params.update() [lr_grid_update, pinned host grid] + mi.render [lr_render -> pinned host image]"
+                   + ("; N > 1: lr_set_lane_map share + in-place film all-reduce + lr_film_develop -> pinned host" if world > 1 else "")}
 
 
 def run_prb(R, args):
     """C5: SphereLiverConstEnv inverse step = primal render + prbvolpath adjoint (spp_grad 64) + NCCL all-reduce of the
-    128^3 density-grid gradient.  Lanes are dealt to ranks by contiguous ranges (strong split of one step) -- here the
-    bench keeps per-GPU work fixed instead: every rank replays the full lane set with seed+rank (weak)."""
-    torch, mi, dev, world, rank, dist = R["torch"], R["mi"], R["dev"], R["world"], R["rank"], R["dist"]
+    128^3 density-grid gradient.  Partition "samples": ONE step, every rank takes spp / N samples of every pixel for the primal
+    and for the adjoint (multi.render_distributed / backward_distributed), both reductions in place on the backend's buffers."""
+    torch, mi, multi, dev, world, rank, dist = R["torch"], R["mi"], R["multi"], R["dev"], R["world"], R["rank"], R["dist"]
     from liverrenderer_b200 import scenes
     res, spp, gr = 512, 64, 128
     sc = mi.load_dict(scenes.sphere_liver_inverse(res=res, spp=spp, grid_res=gr, tracking=args.tracking))
     ctx = mi.Context(R["local"]).upload(sc); ctx.set_stream(R["stream"].cuda_stream)
     img = torch.empty((res, res, 3), dtype=torch.float32, device=dev)
-    grad = torch.empty(ctx.grid_size(0), dtype=torch.float32, device=dev)
     target = torch.full_like(img, 0.5)
     steps = max(1, min(args.steps, 3)); tot = {"samples": 0, "rays": 0, "collisions": 0, "ms_bwd": 0.0}
+    strong = args.partition == "samples"; mode = "samples" if strong else "seeds"
+    red = True if world > 1 else None
 
     def step(k):
-        ctx.render(seed=k + rank, spp=spp, out=img)
+        seed = k if strong else k + rank
+        multi.render_distributed(ctx, seed, spp, rank, world, mode=mode, film_buf=red, out=img)
         g = (2.0 / img.numel()) * (img - target)                 # L2 loss adjoint (notebook cell 11); torch elementwise = plumbing
-        ctx.grid_grad_zero(0)
-        ctx.render_backward(g, seed=mi.sample_tea_32(k + rank, 1)[0], spp=spp)
-        st = ctx.stats()
-        ctx.grid_grad_read(0, grad)
-        if world > 1:
-            dist.all_reduce(grad)
-        return st
+        if strong:
+            grad = multi.backward_distributed(ctx, g, mi.sample_tea_32(seed, 1)[0], spp, rank, world, grad_buf=red if red else None, mode="samples")
+        else:
+            ctx.grid_grad_zero(0); ctx.render_backward(g, seed=mi.sample_tea_32(seed, 1)[0], spp=spp)
+            grad = multi.grid_grad_tensor(ctx, 0, dev)
+            if world > 1:
+                dist.all_reduce(grad)
+        return ctx.stats(), grad
 
     step(-1); R["barrier"]()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True); e0.record(R["stream"])
     for k in range(steps):
-        st = step(k)
+        st, grad = step(k)
         tot["samples"] += st["samples"]; tot["rays"] += st["rays"]; tot["collisions"] += st["collisions"]; tot["ms_bwd"] += st["device_ms"]
     e1.record(R["stream"]); R["barrier"]()
+    if not torch.is_tensor(grad):
+        grad = torch.from_numpy(np.asarray(grad)).to(dev)
     t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([tot["collisions"]], dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item()); n = res * res * spp * steps * world
-    ach = tot["collisions"] * 64.0 / (tot["ms_bwd"] * 1e-3) / 1e9 if tot["ms_bwd"] > 0 else 0.0
-    return {"workload": f"C5 SphereLiverConstEnv prbvolpath {res}x{res}, spp {spp} primal + spp_grad {spp}, sigma_t grid {gr}^3",
-            "grad_samples_per_s": n / (ms * 1e-3), "ms_per_step": ms / steps, "steps": steps, "adjoint_kernel_ms": tot["ms_bwd"] / steps,
-            "adjoint_collisions_per_s": tot["collisions"] / (tot["ms_bwd"] * 1e-3) if tot["ms_bwd"] > 0 else 0.0,
-            "adjoint_GBps_algorithmic_64B_per_collision": ach, "adjoint_frac_of_hbm_peak": ach / R["hbm_peak"],
-            "allreduce_bytes": int(grad.numel() * 4) if world > 1 else 0, "grad_finite": bool(torch.isfinite(grad).all().item()),
-            "grad_abs_max": float(grad.abs().max().item())}
+        dist.all_reduce(t, op=dist.ReduceOp.MAX); dist.all_reduce(cnt)
+    ms = float(t.item()); n = res * res * spp * steps * (1 if strong else world)
+    ach = tot["collisions"] * float(PRB_BYTES_PER_COLLISION) / (tot["ms_bwd"] * 1e-3) / 1e9 if tot["ms_bwd"] > 0 else 0.0
+    out = {"workload": f"C5 SphereLiverConstEnv prbvolpath {res}x{res}, spp {spp} primal + spp_grad {spp}, sigma_t grid {gr}^3",
+           "grad_samples_per_s": n / (ms * 1e-3), "ms_per_step": ms / steps, "steps": steps, "adjoint_kernel_ms": tot["ms_bwd"] / steps, "scaling": "strong" if strong else "weak",
+           "adjoint_collisions_per_s": tot["collisions"] / (tot["ms_bwd"] * 1e-3) if tot["ms_bwd"] > 0 else 0.0,
+           "gradient_atomics_per_s": 8.0 * tot["collisions"] / (tot["ms_bwd"] * 1e-3) if tot["ms_bwd"] > 0 else 0.0,
+           "roofline": {"bound": "hbm", "achieved": ach, "peak": R["hbm_peak"], "unit": "GB/s", "frac": ach / R["hbm_peak"], "traffic": None,
+                        "kernel": "adjoint pass (k_wfp_* kernels, rank 0)", "algorithmic_bytes_per_unit": PRB_BYTES_PER_COLLISION,
+                        "note": "64 B per adjoint collision (tap + 8 gradient atomics, pre-aggregation) over the adjoint's device time"},
+           "allreduce_bytes": int(grad.numel() * 4) if world > 1 else 0, "grad_finite": bool(torch.isfinite(grad).all().item()),
+           "grad_abs_max": float(grad.abs().max().item())}
+    ctx.close()
+    return out
 
 
 def main():
@@ -392,19 +502,31 @@ def main():
     cpu = None
     if R["rank"] == 0 and R["world"] == 1 and not args.no_cpu:
         _, cpu = cpu_sample(args, args.cpu_spp)
+        if prb is not None:
+            prb["cpu_baseline"] = cpu_sample_prb(args)
     if R["world"] > 1:
         R["dist"].barrier()
     if R["rank"] == 0:
-        secs = R["ms_max"] * 1e-3
-        line = {"metric": METRIC, "value": R["value"], "unit": UNIT, "n_gpus": R["world"], "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": R["ms_max"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        run = R["run"]; secs = run["ms"] * 1e-3; value = run["samples"] / secs; strong = args.partition == "samples"
+        ex = R["extras"]; same_alg = None
+        if cpu and ex.get("reference_order_tracking"):
+            same_alg = {"value": ex["reference_order_tracking"]["value"] / cpu["value"],
+                        "note": "same algorithm on both sides: GPU reference-order tracking (global majorant, the reference's draw order) / CPU oracle"}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": R["world"], "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": run["ms"] / args.steps, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic",
-                "config": {"workload": R["name"], "spp": R["spp"], "samples_per_step_per_gpu": R["W"] * R["H"] * R["spp"], "tracking": args.tracking,
-                           "l2": "flushed between timed iterations (512 MiB write)", "partition": "every rank renders the config with seed+rank; film all-reduce"},
-                "mrays_per_s": R["rays"] / secs / 1e6, "collisions_per_s": R["colls"] / secs,
-                "collisions_per_sample": R["colls"] / max(R["samples"], 1), "rays_per_sample": R["rays"] / max(R["samples"], 1),
-                "e2e": e2e, "gpu_launches": int(R["tot"]["launches"]), "clocks": R["clk"], "roofline": R["roofline"], "cpu_baseline": cpu, "prb": prb,
-                "reference_order_tracking": R["ref_order"], "bumpmap_surface": R["bump"]}
+                "config": {"workload": R["name"], "spp": R["spp"], "samples_per_step": run["samples"] / args.steps, "tracking": args.tracking,
+                           "l2": "flushed between timed iterations (512 MiB write)",
+                           "partition": ("one frame split by sample index: rank r renders spp/N samples of every pixel; in-place film all-reduce" if strong
+                                         else "every rank renders the config with seed+rank; in-place film all-reduce"),
+                           "same_config_as_reference_arm": False,
+                           "reference_arm_note": "--impl reference renders the same scene at --cpu-spp samples per pixel with the reference's global-majorant tracking "
+                                                 "(samples/s does not depend on spp); see same_algorithm_ratio for the like-for-like ratio"},
+                "mrays_per_s": run["rays"] / secs / 1e6, "collisions_per_s": run["colls"] / secs,
+                "collisions_per_sample": run["colls"] / max(run["samples"], 1), "rays_per_sample": run["rays"] / max(run["samples"], 1),
+                "e2e": e2e, "gpu_launches": int(run["launches"]), "clocks": run["clk"], "roofline": R["roofline"], "rooflines": R["rooflines"],
+                "stages": R["table"], "cpu_baseline": cpu, "same_algorithm_ratio": same_alg, "prb": prb, "weak": R["weak"]}
+        line.update(ex)
         emit(line)
     if R["world"] > 1:
         R["dist"].destroy_process_group()

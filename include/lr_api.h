@@ -278,6 +278,7 @@ typedef struct lr_stage_profile {
     uint32_t n_stages, reserved;
     double   ms[LR_MAX_STAGES];
     uint64_t launches[LR_MAX_STAGES];
+    uint64_t items[LR_MAX_STAGES];       /* queue entries the stage consumed (rays for the trace stages, lanes for gen); counted in every mode */
 } lr_stage_profile;
 
 typedef struct lr_ctx lr_ctx;
@@ -307,6 +308,13 @@ int  lr_film_clear(lr_ctx *ctx);
 int  lr_render_lanes(lr_ctx *ctx, uint32_t seed, uint32_t spp,
                      uint64_t lane_begin, uint64_t lane_end);
 /* raw accumulator [H][W][C] with C = 4 (RGBW) or 5 (RGBAW) */
+/* Split of ONE frame over devices by sample index (the reference has no multi-GPU code; its render loop's lane <-> (pixel,
+   sample) map is src/render/integrator.cpp:321-338): after lr_set_lane_map(ctx, period, offset, len) the lane arguments of
+   lr_render_lanes / lr_sample_lanes / lr_render_backward count LOCAL indices i of the context's share,
+   lane = (i / len) * period + offset + (i mod len); begin = end = 0 renders the whole share.  period = spp per pass, len =
+   spp / N, offset = rank * len gives each of N devices spp / N samples of every pixel (perfectly balanced); PCG32 streams
+   stay keyed by the global lane, so the sum of the devices' films is the single-device film.  len = 0 removes the map.   */
+int  lr_set_lane_map(lr_ctx *ctx, uint64_t period, uint64_t offset, uint64_t len);
 int  lr_film_channels(const lr_ctx *ctx);
 int  lr_film_read(lr_ctx *ctx, float *block, int is_device);
 int  lr_film_write(lr_ctx *ctx, const float *block, int is_device);

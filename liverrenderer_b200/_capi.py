@@ -107,7 +107,7 @@ class lr_stats(C.Structure):
 
 
 class lr_stage_profile(C.Structure):
-    _fields_ = [("n_stages", C.c_uint32), ("reserved", C.c_uint32), ("ms", C.c_double * 16), ("launches", C.c_uint64 * 16)]
+    _fields_ = [("n_stages", C.c_uint32), ("reserved", C.c_uint32), ("ms", C.c_double * 16), ("launches", C.c_uint64 * 16), ("items", C.c_uint64 * 16)]
 
 
 # every symbol include/lr_api.h declares (tests check the library exports all of them)
@@ -115,7 +115,7 @@ API_SYMBOLS = [
     "lr_api_version", "lr_create", "lr_destroy", "lr_last_error", "lr_scene_upload", "lr_render", "lr_film_clear",
     "lr_render_lanes", "lr_film_channels", "lr_film_read", "lr_film_write", "lr_film_develop", "lr_film_device_ptr",
     "lr_sample_lanes", "lr_render_backward", "lr_grid_update", "lr_grid_grad_zero", "lr_grid_grad_read",
-    "lr_grid_grad_device_ptr", "lr_grid_size", "lr_ray_intersect", "lr_ray_intersect_noalloc", "lr_noalloc_max_rays", "lr_cancel", "lr_stats_get", "lr_set_stream",
+    "lr_grid_grad_device_ptr", "lr_grid_size", "lr_set_lane_map", "lr_ray_intersect", "lr_ray_intersect_noalloc", "lr_noalloc_max_rays", "lr_cancel", "lr_stats_get", "lr_set_stream",
     "lr_profile_enable", "lr_profile_get", "lr_stage_name",
     "lr_kat_bsdf_eval_pdf", "lr_kat_bsdf_sample", "lr_kat_phase", "lr_kat_grid_eval", "lr_kat_emitter_sample", "lr_kat_env_eval_pdf",
 ]
@@ -158,6 +158,7 @@ def load_library(path: str | None = None):
     lib.lr_ray_intersect.argtypes = [vp, vp, C.c_uint64, vp]; lib.lr_ray_intersect.restype = C.c_int
     lib.lr_ray_intersect_noalloc.argtypes = [vp, vp, C.c_uint64, vp, C.c_int]; lib.lr_ray_intersect_noalloc.restype = C.c_int
     lib.lr_noalloc_max_rays.argtypes = []; lib.lr_noalloc_max_rays.restype = C.c_uint64
+    lib.lr_set_lane_map.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_uint64]; lib.lr_set_lane_map.restype = C.c_int
     lib.lr_cancel.argtypes = [vp]; lib.lr_cancel.restype = C.c_int
     lib.lr_stats_get.argtypes = [vp, C.POINTER(lr_stats)]; lib.lr_stats_get.restype = C.c_int
     lib.lr_set_stream.argtypes = [vp, vp]; lib.lr_set_stream.restype = C.c_int

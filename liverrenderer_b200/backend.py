@@ -70,6 +70,11 @@ class Context:
     def render_lanes(self, seed, spp, begin, end):
         self._chk(self.lib.lr_render_lanes(self.ctx, seed & 0xffffffff, spp, begin, end), "lr_render_lanes")
 
+    def set_lane_map(self, period: int = 0, offset: int = 0, length: int = 0):
+        """lr_set_lane_map: the following render / sample / backward calls work on the lanes l with (l mod period) in
+        [offset, offset + length) -- `multi.sample_share` gives the triple for rank r of N; length 0 removes the map."""
+        self._chk(self.lib.lr_set_lane_map(self.ctx, period, offset, length), "lr_set_lane_map")
+
     def film_channels(self):
         return self.lib.lr_film_channels(self.ctx)
 
@@ -193,7 +198,7 @@ class Context:
 
     def stage_profile(self) -> dict:
         p = K.lr_stage_profile(); self._chk(self.lib.lr_profile_get(self.ctx, C.byref(p)), "lr_profile_get")
-        return {self.lib.lr_stage_name(i).decode(): {"ms": p.ms[i], "launches": int(p.launches[i])} for i in range(p.n_stages)}
+        return {self.lib.lr_stage_name(i).decode(): {"ms": p.ms[i], "launches": int(p.launches[i]), "items": int(p.items[i])} for i in range(p.n_stages)}
 
     def stats(self) -> dict:
         s = K.lr_stats(); self._chk(self.lib.lr_stats_get(self.ctx, C.byref(s)), "lr_stats_get")

@@ -48,6 +48,7 @@ struct WVPool {
 
 struct lr_ctx {
     int device = 0; cudaStream_t stream = nullptr; bool own_stream = false;
+    LaneMap lane_map{0, 0, 0};                      // lr_set_lane_map: strided lane set of the following render / backward calls
     void *noalloc_ptr = nullptr;                    // device address of g_noalloc_scratch on `device` (lr_noalloc.inl)
     std::string err; bool has_scene = false;
     DScene sc{};
@@ -69,7 +70,7 @@ struct lr_ctx {
     WVPool *wv[4] = {nullptr, nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // forward pools: batches in flight
     uint32_t bvh4_nodes = 0; bool bvh4_small = false; uint32_t trace_n_smem = 0, trace_sd = 1; size_t trace_smem = 0;   // trace-kernel shared-memory plan
     DevBuf lane_cursor;                                                // device-side lane cursor shared by the batches of one render
-    bool profile_on = false; std::vector<cudaEvent_t> prof_ev; double prof_ms[16] = {0}; uint64_t prof_launches[16] = {0};
+    bool profile_on = false; std::vector<cudaEvent_t> prof_ev; double prof_ms[16] = {0}; uint64_t prof_launches[16] = {0}, prof_items[16] = {0};
     cudaEvent_t fork_ev = nullptr; int wf_runs = 3, wf_grid_mult = LR_WF_OCC, wf_grid_mult128 = LR_WF_OCC_SURF;   // one resident wave of CTAs per stage launch (profiles/r1_ab_register_budgets.txt)
     uint64_t wf_pool_slots = 1ull << 25; uint32_t surf_bucket_mask = 0; bool use_wavefront = true, all_media_dda = false;
     uint64_t wf_launches = 0, wf_tracking_launches = 0; double wf_tracking_ms = 0, wf_track_ms = 0, wf_nee_ms = 0;

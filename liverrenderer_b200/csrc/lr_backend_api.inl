@@ -284,12 +284,22 @@ static int end_call(lr_ctx *c, uint64_t launches, bool tracking) {
     return LR_OK;
 }
 
+// lanes of this context's share under lr_set_lane_map (n_lanes when no map is set)
+static int lane_map_count(lr_ctx *c, uint64_t n_lanes, uint64_t &n_local) {
+    const LaneMap &m = c->lane_map; n_local = n_lanes;
+    if (!m.len) return LR_OK;
+    if (n_lanes % m.period) LR_FAIL(c, LR_ERR_INVALID_ARG, "lane map: period %llu does not divide the %llu lanes of a pass", (unsigned long long) m.period, (unsigned long long) n_lanes);
+    n_local = n_lanes / m.period * m.len; return LR_OK;
+}
+
 static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t begin, uint64_t end, float *lanes_out) {
     PassPlan p = plan_passes(c, spp);
     if (c->sc.integ.sampler == LR_SAMPLER_LD && !ld_spp_ok(spp)) LR_FAIL(c, LR_ERR_INVALID_ARG, "ldsampler: spp %u is not a square power of two", spp);
-    if (end == 0 && begin == 0) end = p.n_lanes;
-    if (begin > end || end > p.n_lanes) LR_FAIL(c, LR_ERR_INVALID_ARG, "lane range [%llu,%llu) outside [0,%llu)", (unsigned long long) begin, (unsigned long long) end, (unsigned long long) p.n_lanes);
-    RenderArgs a{}; a.tris_gid = c->tris_gid->as<DTri>(); a.film = c->film.as<float>(); a.lanes_out = lanes_out;
+    uint64_t n_local = p.n_lanes;
+    if (int r = lane_map_count(c, p.n_lanes, n_local)) return r;
+    if (end == 0 && begin == 0) end = n_local;
+    if (begin > end || end > n_local) LR_FAIL(c, LR_ERR_INVALID_ARG, "lane range [%llu,%llu) outside [0,%llu)", (unsigned long long) begin, (unsigned long long) end, (unsigned long long) n_local);
+    RenderArgs a{}; a.map = c->lane_map; a.tris_gid = c->tris_gid->as<DTri>(); a.film = c->film.as<float>(); a.lanes_out = lanes_out;
     a.lane_begin = begin; a.lane_end = end; a.seed = seed; a.spp_per_pass = p.spp_per_pass; a.n_passes = p.n_passes; a.total_spp = spp;
     a.work_counter = c->work_counter.as<unsigned long long>(); a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev;
     if (begin == end) return LR_OK;
@@ -381,15 +391,17 @@ int lr_render_backward(lr_ctx *c, uint32_t seed, uint32_t spp, const float *grad
     PassPlan p = plan_passes(c, spp);
     if (c->sc.integ.sampler == LR_SAMPLER_LD && !ld_spp_ok(spp)) LR_FAIL(c, LR_ERR_INVALID_ARG, "ldsampler: spp %u is not a square power of two", spp);
     if (p.n_passes != 1) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_render_backward: W*H*spp exceeds 2^32 (the reference raises as well, common.py:359-364)");
-    if (lane_begin == 0 && lane_end == 0) lane_end = p.n_lanes;
-    if (lane_begin > lane_end || lane_end > p.n_lanes) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render_backward: lane range out of bounds");
+    uint64_t n_local = p.n_lanes;
+    if (int r = lane_map_count(c, p.n_lanes, n_local)) return r;
+    if (lane_begin == 0 && lane_end == 0) lane_end = n_local;
+    if (lane_begin > lane_end || lane_end > n_local) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_render_backward: lane range out of bounds");
     uint32_t gc = c->film_channels - 1; size_t gbytes = (size_t) c->W * c->H * gc * 4;
     const float *g = grad_in; DevBuf tmp;
     if (!grad_is_device) { LR_CUDA(c, tmp.alloc(gbytes)); LR_CUDA(c, cudaMemcpyAsync(tmp.p, grad_in, gbytes, cudaMemcpyHostToDevice, c->stream)); g = tmp.as<float>(); }
     LR_CUDA(c, cudaMemsetAsync(c->weight_img.p, 0, c->weight_img.bytes, c->stream));
     k_weight_image<<<c->n_sm * 8, 256, 0, c->stream>>>(c->sc, c->weight_img.as<float>(), p.n_lanes, seed, spp);
     LR_CUDA(c, cudaGetLastError());
-    RenderArgs a{}; a.tris_gid = c->tris_gid->as<DTri>(); a.lane_begin = lane_begin; a.lane_end = lane_end; a.seed = seed;
+    RenderArgs a{}; a.tris_gid = c->tris_gid->as<DTri>(); a.lane_begin = lane_begin; a.lane_end = lane_end; a.seed = seed; a.map = c->lane_map;
     a.spp_per_pass = spp; a.n_passes = 1; a.total_spp = spp; a.work_counter = c->work_counter.as<unsigned long long>();
     a.stats = c->stats.as<unsigned long long>(); a.cancel = c->cancel_dev; a.grad_in = g; a.weight_img = c->weight_img.as<float>(); a.grad_channels = gc;
     c->wf_launches = 0;
@@ -435,17 +447,25 @@ int lr_ray_intersect(lr_ctx *c, const float *rays, uint64_t n, float *hits) {
     return copy_out(c, hits, dh.p, n * 16, 0);
 }
 
+int lr_set_lane_map(lr_ctx *c, uint64_t period, uint64_t offset, uint64_t len) {
+    if (!c) return LR_ERR_INVALID_ARG;
+    if (len == 0) { c->lane_map = LaneMap{0, 0, 0}; return LR_OK; }
+    if (period == 0 || offset + len > period) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_set_lane_map: need 0 < offset + len <= period (got period %llu offset %llu len %llu)",
+                                                     (unsigned long long) period, (unsigned long long) offset, (unsigned long long) len);
+    c->lane_map = LaneMap{period, offset, len}; return LR_OK;
+}
+
 int lr_stats_get(lr_ctx *c, lr_stats *out) { if (!c || !out) return LR_ERR_INVALID_ARG; *out = c->st; return LR_OK; }
 
 int lr_profile_enable(lr_ctx *c, int on) {
     if (!c) return LR_ERR_INVALID_ARG;
-    c->profile_on = on != 0; memset(c->prof_ms, 0, sizeof c->prof_ms); memset(c->prof_launches, 0, sizeof c->prof_launches);
+    c->profile_on = on != 0; memset(c->prof_ms, 0, sizeof c->prof_ms); memset(c->prof_launches, 0, sizeof c->prof_launches); memset(c->prof_items, 0, sizeof c->prof_items);
     return LR_OK;
 }
 int lr_profile_get(lr_ctx *c, lr_stage_profile *out) {
     if (!c || !out) return LR_ERR_INVALID_ARG;
     memset(out, 0, sizeof *out); out->n_stages = ST_COUNT;
-    for (int k = 0; k < ST_COUNT; ++k) { out->ms[k] = c->prof_ms[k]; out->launches[k] = c->prof_launches[k]; }
+    for (int k = 0; k < ST_COUNT; ++k) { out->ms[k] = c->prof_ms[k]; out->launches[k] = c->prof_launches[k]; out->items[k] = c->prof_items[k]; }
     return LR_OK;
 }
 const char *lr_stage_name(uint32_t stage) { return stage < ST_COUNT ? kStageNames[stage] : ""; }

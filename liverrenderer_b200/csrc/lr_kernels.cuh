@@ -88,9 +88,18 @@ __global__ void k_gather_tris(const DTri *tris_gid, const uint32_t *order, uint3
 // counter (primary rays of a warp stay pixel-coherent); a lane index keys the PCG32 stream, so
 // the result does not depend on how lanes are distributed over warps, kernels or GPUs.
 // ------------------------------------------------------------------------------------------
+// Strided lane sets (multi-GPU split of ONE frame by sample index): with len != 0 a call renders only the lanes l of the whole
+// render with (l mod period) in [off, off + len); [lane_begin, lane_end) then counts LOCAL indices i, lane = (i / len) * period +
+// off + (i mod len).  period = spp_per_pass, len = spp_per_pass / N gives every rank spp / N samples of every pixel.  Streams stay
+// keyed by the GLOBAL lane, so the union of the ranks' films is the single-GPU film.  len == 0: identity.
+struct LaneMap { uint64_t period, off, len; };
+LR_DEV uint64_t lane_global(const LaneMap &m, uint64_t i) { return m.len ? (i / m.len) * m.period + m.off + (i % m.len) : i; }
+LR_DEV uint64_t lane_local(const LaneMap &m, uint64_t lane) { return m.len ? (lane / m.period) * m.len + (lane % m.period - m.off) : lane; }
+
 struct RenderArgs {
     const DTri *tris_gid; float *film; float *lanes_out;
-    uint64_t lane_begin, lane_end; uint32_t seed, spp_per_pass, n_passes, total_spp;
+    uint64_t lane_begin, lane_end; uint32_t seed, spp_per_pass, n_passes, total_spp;     // local indices when map.len != 0
+    LaneMap map;
     unsigned long long *work_counter, *stats; const volatile int *cancel;
     // adjoint
     const float *grad_in; const float *weight_img; uint32_t grad_channels;
@@ -143,8 +152,9 @@ __global__ void __launch_bounds__(128) k_render(const __grid_constant__ DScene s
         if (lane_id == 0) base = (*a.cancel) ? ~0ull : atomicAdd(a.work_counter, 32ull);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base == ~0ull || a.lane_begin + base >= a.lane_end) break;
-        uint64_t lane = a.lane_begin + base + lane_id;
-        if (lane < a.lane_end) {
+        const uint64_t li = a.lane_begin + base + lane_id;
+        if (li < a.lane_end) {
+            const uint64_t lane = lane_global(a.map, li);
             LaneSetup L; seed_sampler(sc, L.smp, a.seed, lane, a.spp_per_pass, a.n_passes);
             lane_begin_sample(sc, L, lane, a.spp_per_pass);
             for (uint32_t pass = 0; pass < a.n_passes; ++pass) {
@@ -158,7 +168,7 @@ __global__ void __launch_bounds__(128) k_render(const __grid_constant__ DScene s
                     film_put<C>(sc, a.film, box ? L.pos : L.sample_pos, aovs, coalesce);
                 } else {
                     float4 o = make_float4(r.L.x, r.L.y, r.L.z, r.valid ? 1.f : 0.f);
-                    reinterpret_cast<float4 *>(a.lanes_out)[(lane - a.lane_begin) * a.n_passes + pass] = o;
+                    reinterpret_cast<float4 *>(a.lanes_out)[(li - a.lane_begin) * a.n_passes + pass] = o;
                 }
             }
         }
@@ -217,8 +227,9 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene
         if (lane_id == 0) base = (*a.cancel) ? ~0ull : atomicAdd(a.work_counter, 32ull);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base == ~0ull || a.lane_begin + base >= a.lane_end) break;
-        uint64_t lane = a.lane_begin + base + lane_id;
-        if (lane < a.lane_end) {
+        const uint64_t li = a.lane_begin + base + lane_id;
+        if (li < a.lane_end) {
+            const uint64_t lane = lane_global(a.map, li);
             LaneSetup L; seed_sampler(sc, L.smp, a.seed, lane, a.spp_per_pass, a.n_passes);
             lane_begin_sample(sc, L, lane, a.spp_per_pass);
             lane_next_ray(sc, L);

@@ -69,7 +69,7 @@ struct WVArgs {
     float *film; float *lanes_out;
     uint64_t lane_begin, lane_end; unsigned long long *lane_next;      // lane cursor shared by all batches of one render call
     uint32_t seed, spp_per_pass, n_passes;
-    unsigned long long *stats;
+    unsigned long long *stats; LaneMap map;
 };
 
 LR_DEV Sampler wv_rng(const WVPlanes &p, uint32_t s) { const ulonglong2 r = p.rng(s); Sampler m; m.state = r.x; m.inc = r.y; return m; }
@@ -102,7 +102,7 @@ LR_DEV void wv_finish(const DScene &sc, const WVArgs &a, bool pred, float4 lane_
         if (pred) {
             const uint64_t lane = ((uint64_t) __float_as_uint(lane_pos.y) << 32) | __float_as_uint(lane_pos.x);
             const uint32_t pass = flags >> WF_PASS_SHIFT;
-            reinterpret_cast<float4 *>(a.lanes_out)[(lane - a.lane_begin) * a.n_passes + pass] = make_float4(L.x, L.y, L.z, valid ? 1.f : 0.f);
+            reinterpret_cast<float4 *>(a.lanes_out)[(lane_local(a.map, lane) - a.lane_begin) * a.n_passes + pass] = make_float4(L.x, L.y, L.z, valid ? 1.f : 0.f);
         }
         return;
     }
@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_gen(const __grid_constant
         }
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base == ~0ull || base >= n_total) break;
-        const bool have = base + l < n_total; const uint64_t lane = a.lane_begin + base + l;
+        const bool have = base + l < n_total; const uint64_t lane = lane_global(a.map, a.lane_begin + base + l);
         Sampler smp; smp.state = smp.inc = 0;
         if (have) seed_sampler(sc, smp, a.seed, lane, a.spp_per_pass, a.n_passes);
         wv_start_paths<C, TO_FILM>(sc, a, have, lane, 0u, smp, false, 0u, cnt, nsamples);
@@ -856,13 +856,22 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_b_surface(cons
 }
 
 // counters of the queues the second half of an iteration fills (after SHADE_B has consumed the scatter / surface queues)
-__global__ void k_wv_mid_iteration(WVQueues *q) {
+// `items`: per-stage totals of queue entries consumed (lr_stage_profile.items; index = the host's stage enum, passed in `st`)
+struct WVStageIds { int track, shade_a_med, shade_a_surf, escape, trace_s, nee, shade_b_med, shade_b_surf, trace_c, regen; };
+__global__ void k_wv_mid_iteration(WVQueues *q, unsigned long long *items, const WVStageIds st) {
+    uint32_t surf = 0; for (int b = 0; b < WF_N_SURF; ++b) surf += q->n_surf[b];
+    atomicAdd(items + st.track, (unsigned long long) q->n_track); atomicAdd(items + st.shade_a_med, (unsigned long long) q->n_scatter);
+    atomicAdd(items + st.shade_b_med, (unsigned long long) q->n_scatter); atomicAdd(items + st.shade_a_surf, (unsigned long long) surf);
+    atomicAdd(items + st.shade_b_surf, (unsigned long long) surf); atomicAdd(items + st.escape, (unsigned long long) q->n_escape);
+    atomicAdd(items + st.trace_s, (unsigned long long) q->n_shadow); atomicAdd(items + st.nee, (unsigned long long) q->n_nee);
     q->n_track = 0; q->n_scatter = 0; q->n_escape = 0; q->n_shadow = 0; q->n_nee = 0;
     for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
     q->cursor[0] = q->cursor[1] = q->cursor[2] = 0;
 }
 // end of an iteration: what is still alive; the consumed trace / regen queues are emptied
-__global__ void k_wv_end_iteration(WVQueues *q, uint32_t *live_out, const unsigned long long *lane_next, unsigned long long *lane_next_out) {
+__global__ void k_wv_end_iteration(WVQueues *q, uint32_t *live_out, const unsigned long long *lane_next, unsigned long long *lane_next_out,
+                                   unsigned long long *items, const WVStageIds st) {
+    atomicAdd(items + st.trace_c, (unsigned long long) q->n_trace); atomicAdd(items + st.regen, (unsigned long long) q->n_regen);
     uint32_t live = q->n_track + q->n_escape;
     for (int b = 0; b < WF_N_SURF; ++b) live += q->n_surf[b];
     q->live = live; q->n_trace = 0; q->n_regen = 0;

@@ -80,7 +80,7 @@ static int wv_prepare(lr_ctx *c, uint64_t n_lanes) {
         }
         if (!c->fork_ev) LR_CUDA(c, cudaEventCreateWithFlags(&c->fork_ev, cudaEventDisableTiming));
     }
-    if (!c->lane_cursor.p) LR_CUDA(c, c->lane_cursor.alloc(8));
+    if (!c->lane_cursor.p) LR_CUDA(c, c->lane_cursor.alloc(8 + 16 * 8));       // lane cursor + per-stage item totals
     return LR_OK;
 }
 
@@ -121,7 +121,9 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
         LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream));
         for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0));
     }
-    LR_CUDA(c, cudaMemsetAsync(c->lane_cursor.p, 0, 8, c->stream));
+    LR_CUDA(c, cudaMemsetAsync(c->lane_cursor.p, 0, 8 + 16 * 8, c->stream));
+    unsigned long long *d_items = (unsigned long long *) c->lane_cursor.p + 1;
+    const WVStageIds sids{ST_TRACK, ST_SHADE_A_MED, ST_SHADE_A_SURF, ST_ESCAPE, ST_TRACE_S, ST_NEE, ST_SHADE_B_MED, ST_SHADE_B_SURF, ST_TRACE_C, ST_REGEN};
     if (n_runs > 1) { LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream)); for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0)); }
     const uint32_t surf_mask = c->surf_bucket_mask;                    // surface buckets present in this scene
     const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128, grid_tr = c->n_sm;      // trace: one block of LR_TRACE_THREADS per SM
@@ -146,7 +148,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
     };
     auto readback = [&](WvRun &r) -> int {                             // live count + lane cursor of the work enqueued so far -> ring slot
         WVPool &w = *r.w; int slot = (int) (r.iter % WF_RING);
-        k_wv_end_iteration<<<1, 1, 0, r.s>>>(r.a.q, &w.ring_dev[slot].live, (const unsigned long long *) c->lane_cursor.p, &w.ring_dev[slot].lane_next);
+        k_wv_end_iteration<<<1, 1, 0, r.s>>>(r.a.q, &w.ring_dev[slot].live, (const unsigned long long *) c->lane_cursor.p, &w.ring_dev[slot].lane_next, d_items, sids);
         if (cudaEventRecord(w.ring_ev[slot], r.s) != cudaSuccess) return -1;
         ++r.iter; ++launches;
         return cudaGetLastError() == cudaSuccess ? 0 : -1;
@@ -154,7 +156,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
     auto start = [&](WvRun &r) -> int {                                // a new batch on this pool
         WVArgs &a = r.a; a = WVArgs{}; wv_bind(a, *r.w);
         a.film = ra.film; a.lanes_out = ra.lanes_out; a.seed = ra.seed; a.spp_per_pass = ra.spp_per_pass; a.n_passes = ra.n_passes; a.stats = ra.stats;
-        a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end; a.lane_next = (unsigned long long *) c->lane_cursor.p;
+        a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end; a.map = ra.map; a.lane_next = (unsigned long long *) c->lane_cursor.p;
         // GEN hands out lanes while n_alloc + slack <= cap; slack = 32 slots per resident warp of the GEN grid bounds the overshoot
         r.gen_grid = (int) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) grid, a.cap / 512)); a.slack = (uint32_t) r.gen_grid * 256u;
         k_wv_init<<<1, 1, 0, r.s>>>(a.q); ++launches;
@@ -180,7 +182,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
         launch(r, ST_NEE, [&] { k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });
         launch(r, ST_SHADE_B_MED, [&] { k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_B_SURF, [&] { k_wv_shade_b_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); });
-        k_wv_mid_iteration<<<1, 1, 0, s>>>(a.q); ++launches;
+        k_wv_mid_iteration<<<1, 1, 0, s>>>(a.q, d_items, sids); ++launches;
         launch(r, ST_TRACE_C, [&] { if (stk16) k_wv_trace<0, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<0, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); });
         if (multipass) launch(r, ST_REGEN, [&] { k_wv_regen<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         return readback(r);
@@ -200,6 +202,11 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
     for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamSynchronize(runs[k].s));
     LR_CUDA(c, cudaGetLastError());
+    {   // queue entries each stage consumed in this call (GEN: the lanes of the call)
+        unsigned long long h_items[16]; LR_CUDA(c, cudaMemcpy(h_items, d_items, sizeof h_items, cudaMemcpyDeviceToHost));
+        for (int k = 0; k < ST_COUNT; ++k) c->prof_items[k] += h_items[k];
+        c->prof_items[ST_GEN] += n_lanes;
+    }
     if (prof) {
         for (size_t i = 0; i < kev_kind.size(); ++i) {
             float ms = 0.f; if (cudaEventElapsedTime(&ms, kev[2 * i], kev[2 * i + 1]) != cudaSuccess) continue;
@@ -218,7 +225,7 @@ template <int C, bool TO_FILM, bool ADJ>
 static int wavefront_prb_pass(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs &pa) {
     WavefrontBuffers &w = *c->wf; cudaStream_t s = c->stream;
     WFArgs a{}; wf_bind(a, w);
-    a.tris_gid = ra.tris_gid; a.film = ra.film; a.lanes_out = ra.lanes_out; a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end;
+    a.tris_gid = ra.tris_gid; a.film = ra.film; a.lanes_out = ra.lanes_out; a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end; a.map = ra.map;
     a.seed = ra.seed; a.spp_per_pass = ra.spp_per_pass; a.n_passes = 1; a.stats = ra.stats;
     uint32_t surf_mask = 1u | c->surf_bucket_mask;
     const int grid = c->n_sm * 8;

@@ -34,14 +34,14 @@ __global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_gen(const __grid_consta
     uint32_t *q_out = a.q_active[a.cur ^ 1], *n_out = &a.q->n_active[a.cur ^ 1];
     const bool box = sc.sensor.rfilter == LR_RFILTER_BOX, coalesce = a.spp_per_pass >= 4;
     WF_FOR_QUEUE(a.q->n_regen) {
-        bool item = qi < _n; uint32_t slot = item ? a.q_regen[qi] : 0; bool live = false; uint64_t lane = 0;
+        bool item = qi < _n; uint32_t slot = item ? a.q_regen[qi] : 0; bool live = false; uint64_t lane = 0, li = 0;
         WState *S = a.st + slot;
         {
             unsigned m = __ballot_sync(0xffffffffu, item); unsigned l = threadIdx.x & 31; unsigned long long base = 0;
             if (m) {
                 if (l == (unsigned) (__ffs(m) - 1)) base = atomicAdd(&a.q->lane_next, (unsigned long long) __popc(m));
                 base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-                if (item) { lane = a.lane_begin + base + __popc(m & ((1u << l) - 1u)); live = lane < a.lane_end; }
+                if (item) { li = a.lane_begin + base + __popc(m & ((1u << l) - 1u)); live = li < a.lane_end; lane = lane_global(a.map, li); }
             }
         }
         if (item && !live) S->lsp_flags.w = __uint_as_float(WF_DEAD);
@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(256, LR_WFP_OCC) k_wfp_gen(const __grid_consta
             cnt.rays++; Hit h = bvh_trace<false, false>(sc, L.ray); nsamples++;
             V3 Lin = mk3(0.f), dL = mk3(0.f);
             if (ADJ) {
-                float4 p = reinterpret_cast<const float4 *>(pa.primal_L)[lane - a.lane_begin]; Lin = mk3(p.x, p.y, p.z);
+                float4 p = reinterpret_cast<const float4 *>(pa.primal_L)[li - a.lane_begin]; Lin = mk3(p.x, p.y, p.z);
                 Footprint fp; const int W = (int) sc.sensor.film_width, H = (int) sc.sensor.film_height;
                 if (film_footprint(sc, fp2, coalesce, fp)) {
                     for (int j = 0; j < fp.ny; ++j) { int y = fp.y0 + j; if (y < 0 || y >= H) continue;

@@ -54,7 +54,7 @@ struct WFArgs {
     uint32_t cap; int cur;            // slots; index of the input active queue
     const DTri *tris_gid; float *film; float *lanes_out;
     uint64_t lane_begin, lane_end; uint32_t seed, spp_per_pass, n_passes;
-    unsigned long long *stats;
+    unsigned long long *stats; LaneMap map;
 };
 
 // ---- queue push: ballot + popc, one atomic per warp; call at a point where the whole warp is converged ----
@@ -89,7 +89,7 @@ LR_DEV void wf_finish(const DScene &sc, const WFArgs &a, const WState &S, V3 L, 
     } else {
         uint64_t lane = ((uint64_t) __float_as_uint(S.lane_pos.y) << 32) | __float_as_uint(S.lane_pos.x);
         uint32_t pass = flags >> WF_PASS_SHIFT;
-        reinterpret_cast<float4 *>(a.lanes_out)[(lane - a.lane_begin) * a.n_passes + pass] = make_float4(L.x, L.y, L.z, valid ? 1.f : 0.f);
+        reinterpret_cast<float4 *>(a.lanes_out)[(lane_local(a.map, lane) - a.lane_begin) * a.n_passes + pass] = make_float4(L.x, L.y, L.z, valid ? 1.f : 0.f);
     }
 }
 

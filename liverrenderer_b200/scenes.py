@@ -22,10 +22,12 @@ def sigmat_field(res: int) -> np.ndarray:
     (resources/data/tests/scenes/participating_media/create_volume_data.py:33-36),
     evaluated at (i+0)/res per axis; max 5.0.  Returns [z][y][x][1] fp32."""
     c = np.arange(res, dtype=np.float64) / res
-    z, y, x = np.meshgrid(c, c, c, indexing="ij")
-    f = np.maximum(0.0, (np.sin(16 * (x + 4 * ((y - 0.5) ** 2 - 0.25)) + 1) * 0.5))
-    f = np.where((x > 0.2) & (y > 0.7) & (z < 0.5), 5.0, f)
-    return np.ascontiguousarray(f[..., None], dtype=np.float32)
+    y, x = np.meshgrid(c, c, indexing="ij")                      # the field depends on z only through the block below
+    f = np.maximum(0.0, (np.sin(16 * (x + 4 * ((y - 0.5) ** 2 - 0.25)) + 1) * 0.5)).astype(np.float32)
+    blk = (x > 0.2) & (y > 0.7)
+    out = np.empty((res, res, res, 1), dtype=np.float32); out[..., 0] = f[None]
+    out[: int(np.count_nonzero(c < 0.5)), :, :, 0][:, blk] = 5.0
+    return out
 
 
 def tissue_texture(res: int = 512, seed: int = 7) -> np.ndarray:

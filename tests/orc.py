@@ -12,20 +12,49 @@ from liverrenderer_b200 import _capi as K
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "oracle", "liborc.so")
+LIB_FAST = os.path.join(ROOT, "oracle", "_fast", "liborc_fast.so")
+FAST_FLAGS = "-O3 -march=native"            # the TIMING build (bench.py's CPU legs only); parity always uses liborc.so (-O2 -ffp-contract=off)
 _lib = None
+_libs = {}
 
 
 def build():
     subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
 
 
-def lib():
+def build_fast():
+    """Compiles the oracle once more with FAST_FLAGS ON THE MACHINE IT WILL BE TIMED ON (-march=native is not portable, so this
+    binary never travels: it is rebuilt, ~10 s, whenever the CPU differs from the one recorded in the stamp)."""
+    d = os.path.dirname(LIB_FAST); os.makedirs(d, exist_ok=True)
+    try:
+        cpu = [l for l in open("/proc/cpuinfo") if l.startswith(("model name", "flags"))][:2]
+    except OSError:
+        cpu = []
+    stamp = FAST_FLAGS + "\n" + "".join(cpu); sp = os.path.join(d, "stamp")
+    src = os.path.join(ROOT, "oracle")
+    newest = max(os.path.getmtime(os.path.join(src, f)) for f in os.listdir(src) if f.endswith((".cpp", ".h", ".inl")))
+    if not (os.path.exists(LIB_FAST) and os.path.exists(sp) and open(sp).read() == stamp and os.path.getmtime(LIB_FAST) >= newest):
+        subprocess.check_call(["make", "-s", "-B", "-C", src, "fast", "FASTFLAGS=" + FAST_FLAGS])
+        open(sp, "w").write(stamp)
+    return LIB_FAST
+
+
+def lib(fast: bool = False):
     global _lib
+    if fast:
+        if "fast" not in _libs:
+            _libs["fast"] = _bind(C.CDLL(build_fast()))
+        return _libs["fast"]
     if _lib is not None:
         return _lib
     if not os.path.exists(LIB):
         build()
-    L = C.CDLL(LIB); vp = C.c_void_p
+    _lib = _bind(C.CDLL(LIB))
+    return _lib
+
+
+def _bind(L):
+    vp = C.c_void_p
     L.orc_last_error.restype = C.c_char_p
     L.orc_scene_create.argtypes = [C.POINTER(K.lr_scene)]; L.orc_scene_create.restype = vp
     L.orc_scene_destroy.argtypes = [vp]
@@ -59,7 +88,6 @@ def lib():
     L.orc_kat_env_eval.argtypes = [vp, vp, vp]; L.orc_kat_env_sample.argtypes = [vp, vp, C.c_float, C.c_float, vp]
     L.orc_kat_env_pdf.argtypes = [vp, vp]; L.orc_kat_env_pdf.restype = C.c_float
     L.orc_kat_erfinv.argtypes = [C.c_float]; L.orc_kat_erfinv.restype = C.c_float
-    _lib = L
     return L
 
 
@@ -86,8 +114,9 @@ def bump_frame(bsdf, tex, n, sh_n, sh_s, dp_du, dp_dv, wi, uv):
 class OracleScene:
     """CPU-oracle twin of liverrenderer_b200.Context for one scene."""
 
-    def __init__(self, scene, threads: int = 0):
-        self.L = lib(); self.scene = scene; self.threads = threads
+    def __init__(self, scene, threads: int = 0, fast: bool = False):
+        """`fast`: the -O3 -march=native timing build (bench.py); parity tests never set it."""
+        self.L = lib(fast); self.scene = scene; self.threads = threads
         pod = scene.pod()
         self.h = self.L.orc_scene_create(C.byref(pod))
         if not self.h:

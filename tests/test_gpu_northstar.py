@@ -19,7 +19,10 @@ pytestmark = pytest.mark.gpu
 
 
 # ------------------------------------------------------------------------------------------------ (a)
-def _converged_image_check(d_ref, d_dda, res, spp, seed_gpu=11, seed_cpu=5):
+def _converged_image_check(d_ref, d_dda, res, spp, seed_gpu=11, seed_cpu=5, clt_share=None):
+    """`clt_share`: None = every pixel-channel takes part in the per-pixel criterion.  A number = the criterion is applied where the
+    central limit theorem can hold at this sample count for BOTH estimators -- the largest single sample carries less than that share
+    of the pixel-channel's second moment -- and the remaining pixel-channels are reported and bounded in aggregate (see the C4 test)."""
     n = res * res * spp
     sc_d = mi.load_dict(d_dda); ctx = mi.Context(0).upload(sc_d)
     gpu = ctx.sample_lanes(seed_gpu, spp, 0, n)[:, :3].reshape(res * res, spp, 3).astype(np.float64); st = ctx.stats(); ctx.close()
@@ -32,19 +35,30 @@ def _converged_image_check(d_ref, d_dda, res, spp, seed_gpu=11, seed_cpu=5):
     assert n_bad <= 1e-5 * n, n_bad
     ma, mb = gpu.mean(1), cpu.mean(1); va, vb = gpu.var(1, ddof=1) / spp, cpu.var(1, ddof=1) / spp
     se = np.sqrt(va + vb); ok = se > 0
-    z = np.abs(ma - mb)[ok] / se[ok]
+    sel = ok
+    if clt_share is not None:
+        share = lambda x: (x ** 2).max(1) / np.maximum((x ** 2).sum(1), 1e-300)
+        sel = ok & (share(gpu) < clt_share) & (share(cpu) < clt_share)
+    z = np.abs(ma - mb)[sel] / se[sel]
     frac3 = float((z < 3.0).mean())
-    mean = mb.mean(); mse = float(((ma - mb) ** 2).mean()); mc = float((va + vb).mean())
-    se_resid = math.sqrt(2.0 * float(((va + vb) ** 2).mean()) / ma.size)           # standard error of the MSE estimate under H0
+    mean = mb.mean(); mse = float(((ma - mb)[sel] ** 2).mean()); mc = float((va + vb)[sel].mean())
+    se_resid = math.sqrt(2.0 * float(((va + vb)[sel] ** 2).mean()) / int(sel.sum()))   # standard error of the MSE estimate under H0
     resid = mse - mc; rel_rmse = math.sqrt(max(resid, 0.0)) / mean
     g_bias = (ma.mean() - mb.mean()) / mean; g_se = math.sqrt(float((va + vb).sum())) / ma.size / mean
-    print(f"[north star (a)] {res}x{res} x {spp} spp: |d| < 3 sigma on {frac3 * 100:.2f} % of pixel-channels; rel RMSE after MC term {rel_rmse:.2e} "
-          f"(raw {math.sqrt(mse) / mean:.2e}, MC {math.sqrt(mc) / mean:.2e}, resolution {math.sqrt(3 * se_resid) / mean:.2e}); image-mean bias {g_bias:+.2e} +- {g_se:.1e}; "
-          f"collisions/sample GPU-DDA {st['collisions'] / st['samples']:.2f} vs oracle {so['collisions'] / so['samples']:.2f}; non-finite oracle lanes {n_bad}")
+    print(f"[north star (a)] {res}x{res} x {spp} spp: |d| < 3 sigma on {frac3 * 100:.2f} % of {'the ' + format(sel.mean() * 100, '.1f') + ' % CLT-valid ' if clt_share is not None else ''}pixel-channels; "
+          f"rel RMSE after MC term {rel_rmse:.2e} (raw {math.sqrt(mse) / mean:.2e}, MC {math.sqrt(mc) / mean:.2e}, resolution {math.sqrt(3 * se_resid) / mean:.2e}); "
+          f"image-mean bias {g_bias:+.2e} +- {g_se:.1e}; collisions/sample GPU-DDA {st['collisions'] / st['samples']:.2f} vs oracle {so['collisions'] / so['samples']:.2f}; "
+          f"non-finite oracle lanes {n_bad}; largest sample GPU {gpu.max():.1f} oracle {cpu.max():.1f}")
     assert frac3 >= 0.994, frac3                                   # Gaussian expectation 0.9973
     assert resid <= (1e-3 * mean) ** 2 + 3.0 * se_resid, (resid, se_resid)
     assert abs(g_bias) <= 1e-3 + 3.0 * g_se, (g_bias, g_se)
     assert st["collisions"] < 0.6 * so["collisions"]
+    if clt_share is not None:
+        rest = ok & ~sel
+        assert sel.mean() >= 0.6, sel.mean()
+        h_bias = float((ma[rest].sum() - mb[rest].sum()) / mb[rest].sum()); h_z = np.abs(ma - mb)[rest] / se[rest]
+        print(f"                 heavy-tailed pixel-channels ({rest.mean() * 100:.1f} %): |d| < 3 (sample) sigma on {(h_z < 3).mean() * 100:.2f} %, summed-radiance difference {h_bias:+.2e}")
+        assert abs(h_bias) <= 5e-2, h_bias                         # sanity bound only: the sample sigma of these pixels is not an error bar
 
 
 def test_c3_converged_image_dda_vs_oracle():
@@ -54,12 +68,23 @@ def test_c3_converged_image_dda_vs_oracle():
 
 
 def test_c4_converged_image_dda_vs_oracle():
-    """C4 plugin set (principled shell + roughdielectric inner boundary, two nested heterogeneous media, hg g = 0.9), 64x64 x 4096 spp."""
-    def scene(tr):
+    """C4 plugin set (principled shell + roughdielectric inner boundary, two nested heterogeneous media, hg g = 0.9), 64x64 x 4096 spp.
+
+    Two legs.  The reference performs Russian roulette once per LOOP ITERATION past rr_depth (volpath.cpp:160-178) -- null collisions
+    included -- so a path of the reference-order estimator that survives k further iterations carries 0.95^-k: on this scene (63
+    collisions per sample) single oracle samples reach 1e3 times the pixel mean, the sample variance of such a pixel is not an error
+    bar at 4096 spp (nor at 32768: tools/dbg_c4z2.py) and its sample mean sits below the true mean most of the time.  The production
+    estimator plays roulette at real vertices only and has no such tail (largest sample ~3).  So:
+      leg 1, roulette off (rr_depth > max_depth), both estimators light-tailed: the north star's criteria on EVERY pixel-channel;
+      leg 2, the configuration as it is: the same criteria where the CLT can hold for both estimators (largest sample < 2 % of the
+             pixel-channel's second moment), the image mean over all pixels, and a sanity bound on the rest.
+    Roulette itself is compared per path (same PCG32 streams, reference order) in the window tests below."""
+    def scene(tr, **kw):
         d = scenes.liver_multi_mesh(res=64, spp=4096, tracking=tr)
         d["capsule"]["sigma_t"]["grid"] = scenes.sigmat_field(64); d["parenchyma"]["sigma_t"]["grid"] = scenes.sigmat_field(128)
-        return d
-    _converged_image_check(scene("reference"), scene("dda"), 64, 4096)
+        d["integrator"].update(kw); return d
+    _converged_image_check(scene("reference", rr_depth=1000), scene("dda", rr_depth=1000), 64, 4096)
+    _converged_image_check(scene("reference"), scene("dda"), 64, 4096, clt_share=0.02)
 
 
 # ------------------------------------------------------------------------------------------------ (b)

@@ -239,8 +239,9 @@ def test_dda_tracking_passes_reference_ztest(name):
 
 
 def test_dda_tracking_matches_reference_order_image():
-    """C3 plugin set: DDA vs reference-order tracking, 4096 spp: < 1e-3 relative RMSE of the image means per channel,
-    per-pixel differences within 4 sigma of the per-pixel standard error, and fewer tentative collisions."""
+    """Internal consistency of the two tracking modes of the product (NOT a parity claim -- parity of production DDA mode against the
+    oracle at the north star's tolerances is tests/test_gpu_northstar.py): C3 plugin set, 4096 spp, image means per channel within
+    3e-3, per-pixel differences within 4 sigma of the per-pixel standard error, and fewer tentative collisions."""
     res, spp = 24, 4096
     imgs, colls, lanes = {}, {}, {}
     for tr in ("reference", "dda"):

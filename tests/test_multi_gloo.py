@@ -31,6 +31,24 @@ def test_pass_splitting_rule():
     assert (spp_pp, passes) == (2048, 2) and n == 1080 * 1080 * 2048 and n <= 0xffffffff
 
 
+def test_sample_shares_partition_exactly():
+    """multi.sample_share: the ranks' sample intervals tile [0, spp) and the local <-> global lane maps are inverse bijections."""
+    for spp in (1, 3, 4, 64, 1024, 2048):
+        for world in (1, 2, 3, 8):
+            shares = [multi.sample_share(spp, r, world) for r in range(world)]
+            cover = sorted((s[1], s[1] + s[2]) for s in shares if s is not None)
+            assert cover[0][0] == 0 and cover[-1][1] == spp and all(a[1] == b[0] for a, b in zip(cover, cover[1:]))
+            assert all(s is None or s[0] == spp for s in shares)
+            n_px = 5; seen = []
+            for s in shares:
+                if s is None:
+                    continue
+                loc = np.arange(n_px * s[2]); g = multi.lane_global(s, loc)
+                assert np.array_equal(multi.lane_local(s, g), loc) and np.all((g % spp >= s[1]) & (g % spp < s[1] + s[2]))
+                seen.append(g)
+            assert np.array_equal(np.sort(np.concatenate(seen)), np.arange(n_px * spp))
+
+
 def _worker(rank, world, port, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -49,8 +67,14 @@ def _worker(rank, world, port, q):
     n2, _, _ = multi.lane_count(8, 8, 4); b, e = multi.lane_range(n2, rank, world)
     g_in = np.ones((8, 8, 3), dtype=np.float32); o2.grid_grad_zero(0); o2.render_backward(g_in, seed=5, spp=4, begin=b, end=e)
     grad = torch.from_numpy(o2.grid_grad_read(0)); multi.allreduce_sum_(grad)
+    # the sample-index split of one frame (multi.sample_share): every rank takes spp / world samples of every pixel
+    share = multi.sample_share(4, rank, world); o.film_clear()
+    for px in range(12 * 12):
+        o.render_lanes(3, 4, px * 4 + share[1], px * 4 + share[1] + share[2])
+    film = torch.from_numpy(o.film_read()); multi.allreduce_sum_(film)
+    img_s = multi.develop(film).numpy()
     if rank == 0:
-        q.put((img, grad.numpy()))
+        q.put((img, grad.numpy(), img_s))
     dist.barrier(); dist.destroy_process_group()
 
 
@@ -62,11 +86,11 @@ def test_world_size_2_film_and_gradient_reduce():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    img, grad = q.get(timeout=300)
+    img, grad, img_s = q.get(timeout=300)
     for p in procs:
         p.join(timeout=120); assert p.exitcode == 0
     sc = mi.load_dict(scenes.liver_single_mesh(res=12, spp=4, grid_res=8)); ref = orc.OracleScene(sc, threads=1).render(seed=3, spp=4)
-    assert np.allclose(img, ref, rtol=1e-5, atol=1e-7)
+    assert np.allclose(img, ref, rtol=1e-5, atol=1e-7) and np.allclose(img_s, ref, rtol=1e-5, atol=1e-7)
     sc2 = mi.load_dict(scenes.sphere_liver_inverse(res=8, spp=4, grid_res=4)); o2 = orc.OracleScene(sc2, threads=1)
     o2.grid_grad_zero(0); o2.render_backward(np.ones((8, 8, 3), dtype=np.float32), seed=5, spp=4)
     assert np.allclose(grad, o2.grid_grad_read(0), rtol=1e-4, atol=1e-9)

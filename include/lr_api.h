@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define LR_API_VERSION 2
+#define LR_API_VERSION 3
 
 typedef enum lr_status {
     LR_OK                = 0,
@@ -225,13 +225,15 @@ typedef struct lr_sensor {
     float    to_world[16];          /* camera -> world (no scale)               */
     float    sample_to_camera[16];  /* inverse of perspective_projection (include/mitsuba/render/sensor.h:234-269) */
     float    near_clip, far_clip;
-    uint32_t film_width, film_height;       /* full film == crop (no crop window on this path) */
+    uint32_t film_width, film_height;       /* size of the rendered window = the film's CROP size (Film::crop_size, integrator.cpp:163);
+                                               sample_to_camera is built for that window (perspective_projection, sensor.h:234-269) */
     uint32_t rfilter;               /* lr_rfilter_kind                          */
     float    rfilter_radius;        /* box .5, tent 1, gaussian 4*stddev        */
     float    rfilter_stddev;        /* gaussian                                 */
     uint32_t has_alpha;             /* pixel_format rgba => 1                   */
     int32_t  medium;                /* medium the sensor sits in, or -1         */
-    uint32_t reserved;
+    uint32_t crop_offset_x, crop_offset_y;  /* Film::crop_offset (hdrfilm crop_offset_x / _y): added to the pixel position before the
+                                               camera sample position is formed (integrator.cpp:338, :465-468)                       */
 } lr_sensor;
 
 typedef struct lr_integrator {

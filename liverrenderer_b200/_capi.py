@@ -14,7 +14,7 @@ c_uint32_p = C.POINTER(C.c_uint32)
 
 # ---- enums (values mirror lr_api.h) -----------------------------------------
 LR_OK = 0
-LR_API_VERSION = 2
+LR_API_VERSION = 3
 LR_ERR = {-1: "invalid argument", -2: "no CUDA device (this backend has no CPU path)", -3: "CUDA error",
           -4: "unsupported plugin/option", -5: "no scene uploaded", -6: "cancelled", -7: "out of memory"}
 
@@ -84,7 +84,7 @@ class lr_sensor(C.Structure):
     _fields_ = [("to_world", C.c_float * 16), ("sample_to_camera", C.c_float * 16), ("near_clip", C.c_float),
                 ("far_clip", C.c_float), ("film_width", C.c_uint32), ("film_height", C.c_uint32), ("rfilter", C.c_uint32),
                 ("rfilter_radius", C.c_float), ("rfilter_stddev", C.c_float), ("has_alpha", C.c_uint32),
-                ("medium", C.c_int32), ("reserved", C.c_uint32)]
+                ("medium", C.c_int32), ("crop_offset_x", C.c_uint32), ("crop_offset_y", C.c_uint32)]
 
 
 class lr_integrator(C.Structure):

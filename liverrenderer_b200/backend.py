@@ -12,14 +12,35 @@ from . import _capi as K
 from .scene import Scene
 
 
-def _ptr(a):
-    """numpy array or torch tensor -> (void*, is_device)."""
+def _ptr(a, n: int, what: str, convert: bool = False):
+    """numpy array or torch tensor -> (void*, is_device, keep-alive).  The C side moves exactly `n` fp32 elements through the
+    pointer, so the buffer must be float32, C-contiguous and hold exactly `n` elements.  `convert` (INPUT buffers only): anything
+    else of the right element count is converted to a contiguous float32 copy; an OUTPUT buffer that does not qualify raises
+    (TypeError for the dtype, ValueError for layout / size) -- writing through a reinterpreted or short buffer is never right."""
+    if isinstance(a, (list, tuple)) and convert:
+        a = np.asarray(a, dtype=np.float32)
     if isinstance(a, np.ndarray):
-        return C.c_void_p(a.ctypes.data), 0
+        if a.size != n:
+            raise ValueError(f"{what}: expected {n} elements, got {a.size} (shape {a.shape})")
+        if a.dtype != np.float32 or not a.flags.c_contiguous:
+            if not convert:
+                if a.dtype != np.float32:
+                    raise TypeError(f"{what}: output buffer must be float32, got {a.dtype}")
+                raise ValueError(f"{what}: output buffer must be C-contiguous")
+            a = np.ascontiguousarray(a, dtype=np.float32)
+        return C.c_void_p(a.ctypes.data), 0, a
     # torch tensor (duck-typed to keep torch optional at import time)
     if hasattr(a, "data_ptr"):
-        return C.c_void_p(a.data_ptr()), 1 if a.is_cuda else 0
-    raise TypeError("expected a numpy array or a torch tensor")
+        if a.numel() != n:
+            raise ValueError(f"{what}: expected {n} elements, got {a.numel()} (shape {tuple(a.shape)})")
+        if str(a.dtype) != "torch.float32" or not a.is_contiguous():
+            if not convert:
+                if str(a.dtype) != "torch.float32":
+                    raise TypeError(f"{what}: output buffer must be float32, got {a.dtype}")
+                raise ValueError(f"{what}: output buffer must be contiguous")
+            a = a.float().contiguous()
+        return C.c_void_p(a.data_ptr()), (1 if a.is_cuda else 0), a
+    raise TypeError(f"{what}: expected a numpy array or a torch tensor, got {type(a).__name__}")
 
 
 class Context:
@@ -60,7 +81,7 @@ class Context:
         sc = self.scene; W, H = sc.film_size; spp = spp or sc.spp
         if out is None:
             out = np.empty((H, W, sc.out_channels), dtype=np.float32)
-        p, dev = _ptr(out)
+        p, dev, _ = _ptr(out, H * W * sc.out_channels, "render(out=)")
         self._chk(self.lib.lr_render(self.ctx, seed & 0xffffffff, spp, p, dev), "lr_render")
         return out
 
@@ -82,16 +103,17 @@ class Context:
         W, H = self.scene.film_size
         if out is None:
             out = np.empty((H, W, self.film_channels()), dtype=np.float32)
-        p, dev = _ptr(out); self._chk(self.lib.lr_film_read(self.ctx, p, dev), "lr_film_read"); return out
+        p, dev, _ = _ptr(out, H * W * self.film_channels(), "film_read(out=)"); self._chk(self.lib.lr_film_read(self.ctx, p, dev), "lr_film_read"); return out
 
     def film_write(self, block):
-        p, dev = _ptr(block); self._chk(self.lib.lr_film_write(self.ctx, p, dev), "lr_film_write")
+        W, H = self.scene.film_size
+        p, dev, _keep = _ptr(block, H * W * self.film_channels(), "film_write(block)", convert=True); self._chk(self.lib.lr_film_write(self.ctx, p, dev), "lr_film_write")
 
     def film_develop(self, out=None):
         sc = self.scene; W, H = sc.film_size
         if out is None:
             out = np.empty((H, W, sc.out_channels), dtype=np.float32)
-        p, dev = _ptr(out); self._chk(self.lib.lr_film_develop(self.ctx, p, dev), "lr_film_develop"); return out
+        p, dev, _ = _ptr(out, H * W * sc.out_channels, "film_develop(out=)"); self._chk(self.lib.lr_film_develop(self.ctx, p, dev), "lr_film_develop"); return out
 
     def film_device_ptr(self):
         return self.lib.lr_film_device_ptr(self.ctx)
@@ -99,22 +121,24 @@ class Context:
     def sample_lanes(self, seed, spp, begin, end, out=None):
         """Per-lane radiance [(end - begin) * n_passes, 4]; a render beyond 2^32 - 1 lanes is split into passes
         (src/render/integrator.cpp:275-293) and every lane then has one row per pass: row = (lane - begin) * n_passes + pass."""
+        from .multi import lane_count
+        W, H = self.scene.film_size; rows = (end - begin) * lane_count(W, H, spp)[2]
         if out is None:
-            from .multi import lane_count
-            W, H = self.scene.film_size
-            out = np.empty(((end - begin) * lane_count(W, H, spp)[2], 4), dtype=np.float32)
-        p, dev = _ptr(out)
+            out = np.empty((rows, 4), dtype=np.float32)
+        p, dev, _ = _ptr(out, rows * 4, "sample_lanes(out=)")
         self._chk(self.lib.lr_sample_lanes(self.ctx, seed & 0xffffffff, spp, begin, end, p, dev), "lr_sample_lanes")
         return out
 
     # -- adjoint -----------------------------------------------------------------
     def render_backward(self, grad_in, seed: int = 0, spp: int | None = None, begin: int = 0, end: int = 0):
         spp = spp or self.scene.spp
-        p, dev = _ptr(grad_in)
+        W, H = self.scene.film_size
+        p, dev, _keep = _ptr(grad_in, H * W * (self.film_channels() - 1), "render_backward(grad_in)", convert=True)
         self._chk(self.lib.lr_render_backward(self.ctx, seed & 0xffffffff, spp, p, dev, begin, end), "lr_render_backward")
 
     def grid_update(self, grid: int, data):
-        p, dev = _ptr(data); self._chk(self.lib.lr_grid_update(self.ctx, grid, p, dev), "lr_grid_update")
+        p, dev, _keep = _ptr(data, self.lib.lr_grid_size(self.ctx, grid), "grid_update(data)", convert=True)
+        self._chk(self.lib.lr_grid_update(self.ctx, grid, p, dev), "lr_grid_update")
 
     def grid_grad_zero(self, grid: int):
         self._chk(self.lib.lr_grid_grad_zero(self.ctx, grid), "lr_grid_grad_zero")
@@ -123,7 +147,7 @@ class Context:
         n = self.lib.lr_grid_size(self.ctx, grid)
         if out is None:
             out = np.empty(n, dtype=np.float32)
-        p, dev = _ptr(out); self._chk(self.lib.lr_grid_grad_read(self.ctx, grid, p, dev), "lr_grid_grad_read"); return out
+        p, dev, _ = _ptr(out, n, "grid_grad_read(out=)"); self._chk(self.lib.lr_grid_grad_read(self.ctx, grid, p, dev), "lr_grid_grad_read"); return out
 
     def grid_grad_device_ptr(self, grid: int):
         return self.lib.lr_grid_grad_device_ptr(self.ctx, grid)

@@ -220,15 +220,19 @@ static void build_envmap(const lr_emitter &e, std::vector<float> &pixels, std::v
 }
 
 // majorant super-grid: max of the raw grid over each cell's trilinear support (cell voxels +1 apron)
-__global__ void k_majorant_grid(const float *data, int rx, int ry, int rz, int ch, int cell, int mx, int my, int mz, float *maj) {
+__global__ void k_majorant_grid(const float *data, int rx, int ry, int rz, int ch, int cell, int mx, int my, int mz, int wrap, float *maj) {
     int c = blockIdx.x * blockDim.x + threadIdx.x; if (c >= mx * my * mz) return;
     int cx = c % mx, cy = (c / mx) % my, cz = c / (mx * my);
-    // a lookup at local coordinate u in [cx*cell, (cx+1)*cell) voxels touches voxel indices floor(u-.5) .. floor(u-.5)+1
-    int x0 = max(cx * cell - 1, 0), x1 = min((cx + 1) * cell, rx - 1), y0 = max(cy * cell - 1, 0), y1 = min((cy + 1) * cell, ry - 1),
-        z0 = max(cz * cell - 1, 0), z1 = min((cz + 1) * cell, rz - 1);
+    // a lookup at local coordinate u in [cx*cell, (cx+1)*cell) voxels touches voxel indices floor(u-.5) .. floor(u-.5)+1: the cell's
+    // voxels plus a one-voxel apron, whose indices leave the grid at its faces and are brought back by the grid's wrap mode exactly as
+    // the lookup does it (grid_wrap, lr_medium.cuh): clamp / mirror stay at the face, REPEAT reaches the voxels of the opposite face
+    auto wr = [wrap](int i, int n) { return wrap == LR_WRAP_REPEAT ? ((i % n) + n) % n : min(max(i, 0), n - 1); };
+    const int x0 = cx * cell - 1, x1 = min((cx + 1) * cell, rx), y0 = cy * cell - 1, y1 = min((cy + 1) * cell, ry), z0 = cz * cell - 1, z1 = min((cz + 1) * cell, rz);
     float m = 0.f;
-    for (int z = z0; z <= z1; ++z) for (int y = y0; y <= y1; ++y) for (int x = x0; x <= x1; ++x)
-        for (int k = 0; k < ch; ++k) m = fmaxf(m, data[(((size_t) z * ry + y) * rx + x) * ch + k]);
+    for (int z = z0; z <= z1; ++z) for (int y = y0; y <= y1; ++y) for (int x = x0; x <= x1; ++x) {
+        const size_t v = ((size_t) wr(z, rz) * ry + wr(y, ry)) * rx + wr(x, rx);
+        for (int k = 0; k < ch; ++k) m = fmaxf(m, data[v * ch + k]);
+    }
     maj[c] = m;
 }
 
@@ -253,7 +257,7 @@ static int refresh_grid_derived(lr_ctx *c, uint32_t gi) {
     LR_CUDA(c, cudaStreamSynchronize(c->stream));
     g.maxv = (gi < c->grid_fixed_max.size() && c->grid_fixed_max[gi] >= 0.f) ? c->grid_fixed_max[gi] : mx;
     int nc = g.mx * g.my * g.mz;
-    k_majorant_grid<<<(nc + 127) / 128, 128, 0, c->stream>>>(g.data, g.rx, g.ry, g.rz, g.ch, g.cell, g.mx, g.my, g.mz, (float *) g.maj);
+    k_majorant_grid<<<(nc + 127) / 128, 128, 0, c->stream>>>(g.data, g.rx, g.ry, g.rz, g.ch, g.cell, g.mx, g.my, g.mz, (int) g.wrap, (float *) g.maj);
     if (g.fat) k_grid_fatten<<<c->n_sm * 8, 256, 0, c->stream>>>(g.data, g.rx, g.ry, g.rz, (float4 *) g.fat);
     LR_CUDA(c, cudaGetLastError());
     for (auto &m : c->h_media) if (m.m.kind == LR_MEDIUM_HETEROGENEOUS && m.m.sigma_t_grid == (int) gi) m.max_density = m.m.scale * g.maxv;

@@ -119,8 +119,12 @@ LR_DEV void lane_begin_sample(const DScene &sc, LaneSetup &L, uint64_t lane, uin
 }
 LR_DEV void lane_next_ray(const DScene &sc, LaneSetup &L) {
     V2 j = L.smp.next_2d();
-    L.sample_pos = mk2(L.pos.x + j.x, L.pos.y + j.y);
-    V2 adjusted = mk2(__fmul_rn(L.sample_pos.x, 1.f / (float) sc.sensor.film_width), __fmul_rn(L.sample_pos.y, 1.f / (float) sc.sensor.film_height));
+    L.sample_pos = mk2(L.pos.x + j.x, L.pos.y + j.y);                       // film position, relative to the crop window
+    // integrator.cpp:338, :465-468: pos += crop_offset; scale = 1 / crop_size, offset = -crop_offset * scale;
+    // adjusted_pos = fmadd(pos + jitter, scale, offset).  Without a crop this is sample_pos * scale exactly (offset = -0).
+    const float sx = 1.f / (float) sc.sensor.film_width, sy = 1.f / (float) sc.sensor.film_height;
+    const float ox = (float) sc.sensor.crop_offset_x, oy = (float) sc.sensor.crop_offset_y;
+    V2 adjusted = mk2(fmaf((L.pos.x + ox) + j.x, sx, -(ox * sx)), fmaf((L.pos.y + oy) + j.y, sy, -(oy * sy)));
     L.ray = camera_ray(sc, adjusted);
 }
 

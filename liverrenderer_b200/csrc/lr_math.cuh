@@ -39,7 +39,8 @@ LR_HD V3 operator*(V3 a, V3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
 LR_HD V3 operator/(V3 a, V3 b) { return mk3(a.x / b.x, a.y / b.y, a.z / b.z); }
 LR_HD V3 operator*(V3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
 LR_HD V3 operator*(float s, V3 a) { return mk3(a.x * s, a.y * s, a.z * s); }
-LR_HD V3 operator/(V3 a, float s) { return mk3(a.x / s, a.y / s, a.z / s); }
+// array / scalar is array * rcp(scalar) in Dr.Jit (ext/drjit/include/drjit/array_router.h:218-232): one correctly rounded 1 / s, then three products
+LR_HD V3 operator/(V3 a, float s) { const float r = 1.f / s; return mk3(a.x * r, a.y * r, a.z * r); }
 LR_HD V3 operator-(V3 a) { return mk3(-a.x, -a.y, -a.z); }
 LR_HD void operator+=(V3 &a, V3 b) { a = a + b; }
 LR_HD void operator*=(V3 &a, V3 b) { a = a * b; }

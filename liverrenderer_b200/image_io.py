@@ -20,10 +20,14 @@ def read_image_rgb(path: str) -> np.ndarray:
     img = cv2.imread(path, cv2.IMREAD_UNCHANGED)
     if img is None:
         raise RuntimeError(f'could not read image "{path}"')
-    img = img.astype(np.float32)
     if img.ndim == 2:
         img = np.repeat(img[..., None], 3, axis=2)
-    return np.ascontiguousarray(img[..., 2::-1])     # BGR(A) -> RGB
+    img = img[..., 2::-1]                            # BGR(A) -> RGB
+    if img.dtype == np.uint8 or img.dtype == np.uint16:
+        # 8/16-bit files hold sRGB-encoded values in 0..255 / 0..65535: normalise and linearise as the reference's Bitmap
+        # conversion does for every non-raw integer image (src/emitters/envmap.cpp:95-107, src/textures/bitmap.cpp:295-345)
+        img = srgb_to_linear(img.astype(np.float32) / np.float32(255.0 if img.dtype == np.uint8 else 65535.0))
+    return np.ascontiguousarray(img, dtype=np.float32)
 
 
 def srgb_to_linear(v: np.ndarray) -> np.ndarray:

@@ -423,9 +423,14 @@ class Scene:
             fl = float(str(v.get("focal_length", "50mm")).replace("mm", ""))
             import math
             fov_x = parse_fov(2.0 * math.degrees(math.atan(math.sqrt(36.0 * 36 + 24 * 24) / (2.0 * fl))), "diagonal", W / H)
-        c2s = perspective_projection((W, H), (W, H), (0, 0), fov_x, near, far)
+        # crop window (Film::Film, src/render/film.cpp:30-52): crop_offset_x/_y, crop_width/_height; the render covers the crop only
+        cw = int(film.get("crop_width", W)); chh = int(film.get("crop_height", H))
+        cx = int(film.get("crop_offset_x", 0)); cy = int(film.get("crop_offset_y", 0))
+        if cx < 0 or cy < 0 or cw <= 0 or chh <= 0 or cx + cw > W or cy + chh > H:
+            raise RuntimeError("Invalid crop window specification!")
+        c2s = perspective_projection((W, H), (cw, chh), (cx, cy), fov_x, near, far)
         s.to_world = _f16(to_world.matrix); s.sample_to_camera = _f16(c2s.inverse().matrix)
-        s.near_clip = near; s.far_clip = far; s.film_width = W; s.film_height = H
+        s.near_clip = near; s.far_clip = far; s.film_width = cw; s.film_height = chh; s.crop_offset_x = cx; s.crop_offset_y = cy
         rf = film.get("rfilter", {"type": "gaussian"}); rt = rf.get("type", "gaussian")
         if rt == "box":
             s.rfilter = K.RFILTER_BOX; s.rfilter_radius = 0.5

@@ -13,6 +13,7 @@
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
  * --impl reference legs may load this library.
  */
+#include "kat_fn.h"
 #include "orc_integrators.h"
 #include <thread>
 #include <mutex>
@@ -99,8 +100,9 @@ static LaneSetup lane_setup(const Scene &sc, uint32_t seed, uint32_t spp, uint64
     L.pos = {(float) px, (float) py};
     V2 j = L.smp.next_2d();
     L.sample_pos = {L.pos.x + j.x, L.pos.y + j.y};
-    V2 scale = {1.f / (float) W, 1.f / (float) sc.sensor.film_height};
-    V2 adjusted = {fmaf(L.sample_pos.x, scale.x, -0.f), fmaf(L.sample_pos.y, scale.y, -0.f)};
+    V2 scale = {1.f / (float) W, 1.f / (float) sc.sensor.film_height};            /* 1 / crop_size (:465) */
+    float ox = (float) sc.sensor.crop_offset_x, oy = (float) sc.sensor.crop_offset_y; /* pos += crop_offset (:338); offset = -crop_offset * scale (:466) */
+    V2 adjusted = {fmaf((L.pos.x + ox) + j.x, scale.x, -(ox * scale.x)), fmaf((L.pos.y + oy) + j.y, scale.y, -(oy * scale.y))};
     L.ray = camera_ray(sc, adjusted);
     return L;
 }
@@ -311,5 +313,45 @@ float orc_kat_env_pdf(void *h, const float *d) {
     return em.pdf_direction(o.sc.env, it, ds);
 }
 float orc_kat_erfinv(float x) { return erfinv_(x); }
+
+/* generic probe with the same function ids as oracle/_ref/libref_kat.so (the reference's own headers): kat_fn.h */
+int orc_kat_fn(int fn, const float *in, float *out) {
+    auto bits = [](float f) { uint32_t u; memcpy(&u, &f, 4); return u; };
+    auto fbits = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };
+    auto v3 = [](const float *p) { return V3(p[0], p[1], p[2]); };
+    auto put3 = [](float *o, V3 v) { o[0] = v.x; o[1] = v.y; o[2] = v.z; };
+    auto mf = [](const float *i) { return Microfacet(i[0] == 0.f ? LR_MF_BECKMANN : LR_MF_GGX, i[1], i[2], i[3] != 0.f); };
+    switch (fn) {
+        case KAT_TEA32: { uint32_t a0, a1; tea32(bits(in[0]), bits(in[1]), (int) bits(in[2]), a0, a1); out[0] = fbits(a0); out[1] = fbits(a1); return 2; }
+        case KAT_TEA_FLOAT32: out[0] = tea_float32(bits(in[0]), bits(in[1]), (int) bits(in[2])); return 1;
+        case KAT_PCG32: {
+            PCG32 rng; rng.seed(((uint64_t) bits(in[1]) << 32) | bits(in[0]), ((uint64_t) bits(in[3]) << 32) | bits(in[2]));
+            for (int i = 0; i < 4; ++i) out[i] = rng.next_f32();
+            for (int i = 0; i < 4; ++i) out[4 + i] = fbits(rng.next_u32());
+            return 8; }
+        case KAT_WARP_DISK: { V2 p = square_to_uniform_disk_concentric(V2{in[0], in[1]}); out[0] = p.x; out[1] = p.y; return 2; }
+        case KAT_WARP_COS_HEMI: { V3 v = square_to_cosine_hemisphere(V2{in[0], in[1]}); put3(out, v); out[3] = square_to_cosine_hemisphere_pdf(v); return 4; }
+        case KAT_WARP_SPHERE: put3(out, square_to_uniform_sphere(V2{in[0], in[1]})); return 3;
+        case KAT_WARP_TRIANGLE: { V2 p = square_to_uniform_triangle(V2{in[0], in[1]}); out[0] = p.x; out[1] = p.y; return 2; }
+        case KAT_FRESNEL: fresnel(in[0], in[1], out[0], out[1], out[2], out[3]); return 4;
+        case KAT_REFLECT: put3(out, reflect(v3(in), v3(in + 3))); return 3;
+        case KAT_REFRACT: put3(out, refract(v3(in), v3(in + 3), in[6], in[7])); return 3;
+        case KAT_MF_EVAL: out[0] = mf(in).eval(v3(in + 4)); return 1;
+        case KAT_MF_PDF: out[0] = mf(in).pdf(v3(in + 4), v3(in + 7)); return 1;
+        case KAT_MF_SAMPLE: { V3 m; float pdf; mf(in).sample(v3(in + 4), V2{in[7], in[8]}, m, pdf); put3(out, m); out[3] = pdf; return 4; }
+        case KAT_MF_G1: out[0] = mf(in).smith_g1(v3(in + 4), v3(in + 7)); return 1;
+        case KAT_MF_G: out[0] = mf(in).G(v3(in + 4), v3(in + 7), v3(in + 10)); return 1;
+        case KAT_GTR1: { GTR1 g{in[0]}; out[0] = g.eval(v3(in + 1)); out[1] = g.pdf(v3(in + 1)); put3(out + 2, g.sample(V2{in[4], in[5]})); return 5; }
+        case KAT_SMITH_GGX1: out[0] = smith_ggx1(v3(in), v3(in + 3), in[6]); out[1] = clearcoat_G(v3(in), v3(in + 7), v3(in + 3), in[6]); return 2;
+        case KAT_SCHLICK: out[0] = schlick_weight(in[0]); out[1] = calc_schlick1(in[1], in[0], in[2]); out[2] = schlick_R0_eta(in[2]); return 3;
+        case KAT_MAC_MIC: out[0] = mac_mic_compat(v3(in), v3(in + 3), v3(in + 6), in[9], true) ? 1.f : 0.f;
+                          out[1] = mac_mic_compat(v3(in), v3(in + 3), v3(in + 6), in[9], false) ? 1.f : 0.f; return 2;
+        case KAT_PRINCIPLED_FRESNEL: put3(out, principled_fresnel(in[0], in[1], in[2], v3(in + 3), in[6], in[7], in[8] != 0.f, in[9], in[10], in[11] != 0.f, in[12] != 0.f)); return 3;
+        case KAT_DIST_PARAMS: calc_dist_params(in[0], in[1], in[2] != 0.f, out[0], out[1]); return 2;
+        case KAT_COORD_SYSTEM: { V3 s_, t_; coordinate_system(v3(in), s_, t_); put3(out, s_); put3(out + 3, t_); return 6; }
+        case KAT_ERFINV: out[0] = erfinv_(in[0]); return 1;
+    }
+    return -1;
+}
 
 } // extern "C"

@@ -47,7 +47,8 @@ inline V3 operator*(V3 a, V3 b) { return {a.x * b.x, a.y * b.y, a.z * b.z}; }
 inline V3 operator/(V3 a, V3 b) { return {a.x / b.x, a.y / b.y, a.z / b.z}; }
 inline V3 operator*(V3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
 inline V3 operator*(float s, V3 a) { return {a.x * s, a.y * s, a.z * s}; }
-inline V3 operator/(V3 a, float s) { return {a.x / s, a.y / s, a.z / s}; }
+/* array / scalar is array * rcp(scalar) in Dr.Jit (ext/drjit/include/drjit/array_router.h:218-232), one rounding of 1 / s shared by the lanes */
+inline V3 operator/(V3 a, float s) { float r = 1.f / s; return {a.x * r, a.y * r, a.z * r}; }
 inline V3 operator-(V3 a) { return {-a.x, -a.y, -a.z}; }
 inline V3 &operator+=(V3 &a, V3 b) { a = a + b; return a; }
 inline V3 &operator*=(V3 &a, V3 b) { a = a * b; return a; }

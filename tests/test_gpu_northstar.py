@@ -32,7 +32,7 @@ def _converged_image_check(d_ref, d_dda, res, spp, seed_gpu=11, seed_cpu=5, clt_
     # the REFERENCE algorithm does on the Liver-MultiMesh geometry (its shells intersect, so rays carry a medium through open space and
     # exp(+majorant * distance) / itself = inf / inf, volpath.cpp:228-232): such oracle lanes are left out of the statistics and counted
     bad = ~np.isfinite(cpu).all(axis=2); n_bad = int(bad.sum()); cpu[bad] = 0.0
-    assert n_bad <= 1e-5 * n, n_bad
+    assert n_bad <= 1e-4 * n, n_bad
     ma, mb = gpu.mean(1), cpu.mean(1); va, vb = gpu.var(1, ddof=1) / spp, cpu.var(1, ddof=1) / spp
     se = np.sqrt(va + vb); ok = se > 0
     sel = ok
@@ -102,11 +102,19 @@ def _window_per_path(d, spp_gpu, spp_cpu, x0, y0, tol, frac_min, seed=0, w=16, h
     for b, e in _window_ranges(W, spp_pass, x0, y0, w, h):
         g.append(ctx.sample_lanes(seed, spp_gpu, b, e).reshape(e - b, n_passes, 4)); c.append(o.sample_lanes(seed, spp_cpu, b, e))
     g = np.concatenate(g); c = np.concatenate(c); ctx.close()
+    # The reference algorithm itself yields a non-finite lane now and then (2.7e-5 of the lanes of the C3 organ windows): a shadow ray that
+    # leaves the organ but is given the interior medium (target_medium by the sign of d . n) carries it through open space; where
+    # exp(-majorant t) is DENORMAL, `tr / tr_pdf` is evaluated as tr * rcp(tr_pdf) = denormal * inf = inf (Dr.Jit's array / scalar,
+    # array_router.h:218-232; rcp = 1 / x on the LLVM backend, drjit-core op.cpp:1484-1495; volpath.cpp:504-511), and inf * (bsdf value 0)
+    # = NaN.  The oracle restates that; the product sets a non-finite path to 0 instead of poisoning its pixel.  Counted and left out.
+    bad = ~np.isfinite(c[:, :3]).all(axis=1); n_bad = int(bad.sum()); assert n_bad <= max(2, int(1e-4 * len(c))), n_bad
+    assert np.isfinite(g).all()
+    g = g[~bad]; c = c[~bad]
     err = np.abs(g[:, 0, :3] - c[:, :3]) / np.maximum(np.abs(c[:, :3]), 1e-3)
     frac = float((err.max(axis=1) < tol).mean())
     print(f"[north star (b)] window ({x0},{y0}) {w}x{h} of the {W}x{W} x {spp_gpu} frame: {len(c)} lanes, {frac * 100:.2f} % within {tol:g} of the oracle; "
-          f"window mean GPU {g[:, 0, :3].mean():.5f} oracle {c[:, :3].mean():.5f}")
-    assert np.isfinite(g).all() and frac > frac_min, frac
+          f"window mean GPU {g[:, 0, :3].mean():.5f} oracle {c[:, :3].mean():.5f}; non-finite oracle lanes left out: {n_bad}")
+    assert frac > frac_min, frac
     assert np.array_equal(g[:, 0, 3], c[:, 3])
     assert abs(g[:, 0, :3].mean() - c[:, :3].mean()) <= 2e-2 * c[:, :3].mean()
     return g, c

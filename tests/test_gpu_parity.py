@@ -9,6 +9,7 @@ import numpy as np
 import pytest
 
 import liverrenderer_b200 as mi
+from liverrenderer_b200 import _capi as K
 from liverrenderer_b200 import scenes
 from tests import orc, golden_scenes as G
 
@@ -25,7 +26,7 @@ def path_match_fraction(gpu, cpu, tol):
 
 def test_library_loaded_and_device():
     ctx = mi.Context(0)
-    assert ctx.lib.lr_api_version() == 2
+    assert ctx.lib.lr_api_version() == K.LR_API_VERSION == 3
 
 
 def test_no_scene_error():
@@ -380,3 +381,67 @@ def test_bumpmap_prbvolpath_primal_and_adjoint():
             continue
         total += 1; good += np.linalg.norm(ggpu - gcpu) <= 1e-3 * max(np.linalg.norm(gcpu), 1e-12)
     assert total >= 16 and good >= 0.85 * total, (good, total)
+
+
+def test_dda_majorant_covers_the_repeat_wrap_apron():
+    """gridvolume wrap_mode = repeat: a lookup in the first half voxel blends in the voxels of the OPPOSITE face (grid.cpp:495-521,
+    texture.h wrap), so the majorant of a border super-voxel has to cover them.  A grid that is empty except for its last x-slab:
+    with a clamped apron the first super-voxel's majorant would be 0 while the lookup there is not -- sigma_n < 0, a biased image.
+    DDA tracking against the oracle's reference-order tracking (global majorant), image means per channel within 3 standard errors."""
+    res, spp, gr = 24, 512, 16
+    grid = np.zeros((gr, gr, gr, 1), np.float32); grid[:, :, -1, 0] = 4.0
+    def scene(tr):
+        return {"type": "scene", "integrator": {"type": "volpath", "max_depth": 6, "rr_depth": 64, "tracking": tr, "majorant_cell": 4},
+                "sensor": {"type": "perspective", "fov": 30.0, "near_clip": 0.01, "far_clip": 100.0,
+                           "to_world": mi.T().look_at(origin=[0.3, 0.4, -4.0], target=[0, 0, 0], up=[0, 1, 0]),
+                           "sampler": {"type": "independent", "sample_count": spp},
+                           "film": {"type": "hdrfilm", "width": res, "height": res, "rfilter": {"type": "box"}, "pixel_format": "rgb"}},
+                "cube": {"type": "cube", "to_world": mi.T().scale(0.5), "bsdf": {"type": "null"},
+                         "interior": {"type": "heterogeneous", "scale": 3.0,
+                                      "sigma_t": {"type": "gridvolume", "grid": grid, "wrap_mode": "repeat", "to_world": mi.T().translate([-0.5, -0.5, -0.5])},
+                                      "albedo": {"type": "rgb", "value": [0.2, 0.5, 0.8]}}},
+                "env": {"type": "constant", "radiance": {"type": "rgb", "value": [1, 1, 1]}}}
+    n = res * res * spp
+    gpu = mi.Context(0).upload(mi.load_dict(scene("dda"))).sample_lanes(3, spp, 0, n)[:, :3].astype(np.float64)
+    cpu = orc.OracleScene(mi.load_dict(scene("reference"))).sample_lanes(5, spp, 0, n)[:, :3].astype(np.float64)
+    se = np.sqrt(gpu.var(0) / n + cpu.var(0) / n)
+    assert np.all(np.abs(gpu.mean(0) - cpu.mean(0)) < 3.5 * se), (gpu.mean(0), cpu.mean(0), se)
+    assert cpu.mean(0).max() < 0.995                                  # the slab does attenuate: the test is not vacuous
+
+
+def test_crop_window_per_path_and_reference_pixel():
+    """Film crop (crop_offset_x/_y, crop_width/_height; integrator.cpp:163,315,338): the reference's own crop test
+    (test_integrators.py:29-52: 1 x 1 crop at (124, 36) of mi.cornell_box(), max_depth 1 => the emitter radiance) through lr_render, and
+    a 40 x 24 window of the Cornell box per path against the oracle (same crop, same streams)."""
+    d = mi.cornell_box(); d["integrator"] = {"type": "path", "max_depth": 1, "hide_emitters": False}
+    d["sensor"]["film"].update({"crop_offset_x": 124, "crop_offset_y": 36, "crop_width": 1, "crop_height": 1})
+    img = mi.Context(0).upload(mi.load_dict(d)).render(seed=0, spp=64)
+    assert img.shape[:2] == (1, 1) and np.allclose(img[0, 0, :3], [18.387, 13.9873, 6.75357], rtol=1e-5)
+    d["integrator"]["hide_emitters"] = True
+    assert np.all(mi.Context(0).upload(mi.load_dict(d)).render(seed=0, spp=64)[..., :3] == 0)
+    w = scenes.cornell_box_path(res=256, spp=8); w["sensor"]["film"].update({"crop_offset_x": 100, "crop_offset_y": 90, "crop_width": 40, "crop_height": 24})
+    sc = mi.load_dict(w); n = 40 * 24 * 8
+    gpu = mi.Context(0).upload(sc).sample_lanes(0, 8, 0, n); cpu = orc.OracleScene(sc).sample_lanes(0, 8, 0, n)
+    assert path_match_fraction(gpu, cpu, 1e-4) > 0.995
+    full = mi.load_dict(scenes.cornell_box_path(res=256, spp=8))
+    assert abs(float(cpu[:, :3].mean()) - float(orc.OracleScene(full).render(seed=1, spp=64)[90:114, 100:140, :3].mean())) < 0.05 * float(cpu[:, :3].mean())
+
+
+def test_cancel_from_another_thread():
+    """lr_cancel (Integrator::cancel, include/mitsuba/render/integrator.h:102-107) from a second thread while lr_render runs: the render
+    returns LR_ERR_CANCELLED (status -6) within a few wavefront iterations, and the context renders normally afterwards."""
+    import threading, time
+    sc = mi.load_dict(scenes.liver_single_mesh(res=1080, spp=512, grid_res=64, tracking="dda")); ctx = mi.Context(0).upload(sc)
+    ctx.film_clear(); ctx.render_lanes(0, 1, 0, 0)                                    # warm: pools allocated
+    t0 = time.perf_counter(); ctx.film_clear(); ctx.render_lanes(1, 512, 0, 0); full = time.perf_counter() - t0
+    res = {}
+    def work():
+        try:
+            ctx.film_clear(); ctx.render_lanes(2, 512, 0, 0); res["ok"] = True
+        except RuntimeError as e:
+            res["err"] = str(e)
+        res["t"] = time.perf_counter()
+    th = threading.Thread(target=work); t1 = time.perf_counter(); th.start(); time.sleep(0.05); ctx.cancel(); tc = time.perf_counter(); th.join(timeout=60)
+    assert "err" in res and "status -6" in res["err"] and "cancel" in res["err"].lower(), res
+    assert res["t"] - tc < 0.5 * full + 0.05, (res["t"] - tc, full)                  # stopped early, not after finishing the frame
+    ctx.film_clear(); ctx.render_lanes(3, 1, 0, 0); assert ctx.stats()["samples"] == 1080 * 1080

@@ -54,3 +54,20 @@ def test_write_bitmap_exr_and_png(tmp_path):
     np.testing.assert_allclose(linear_to_srgb(np.float32([0.0031308, 0.5])), [0.04045, 0.735357], atol=2e-5)
     with pytest.raises(RuntimeError):
         mi.write_bitmap(str(tmp_path / "bad.exr"), np.zeros((4, 4, 2), np.float32))
+
+
+def test_ldr_environment_image_is_normalised_and_linearised(tmp_path):
+    """An 8-bit PNG / 16-bit PNG given to `envmap` is sRGB data in 0..255 (0..65535): read_image_rgb returns linear values in
+    0..1 like the `bitmap` texture path (envmap.cpp:95-107 converts through Bitmap), not raw integers 255x too bright."""
+    import cv2
+    from liverrenderer_b200.image_io import read_image_rgb
+    rng = np.random.default_rng(3); px8 = rng.integers(0, 256, size=(6, 9, 3), dtype=np.uint8)
+    p8 = str(tmp_path / "env8.png"); cv2.imwrite(p8, px8[..., ::-1])
+    got = read_image_rgb(p8)
+    assert got.dtype == np.float32 and got.shape == (6, 9, 3) and got.max() <= 1.0
+    assert np.allclose(got, srgb_to_linear(px8.astype(np.float32) / 255.0), atol=1e-7)
+    assert np.array_equal(np.round(linear_to_srgb(got) * 255.0).astype(np.uint8), px8)           # uint8 round trip
+    px16 = rng.integers(0, 65536, size=(4, 5, 3), dtype=np.uint16); p16 = str(tmp_path / "env16.png"); cv2.imwrite(p16, px16[..., ::-1])
+    assert np.allclose(read_image_rgb(p16), srgb_to_linear(px16.astype(np.float32) / 65535.0), atol=1e-7)
+    f = rng.random((3, 4, 3)).astype(np.float32) * 7.0; np.save(tmp_path / "env.npy", f)          # float data stays as stored
+    assert np.array_equal(read_image_rgb(str(tmp_path / "env.npy")), f)

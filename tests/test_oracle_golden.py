@@ -44,6 +44,35 @@ def test_cornell_directly_visible_pixel():
     assert np.all(lanes[:, :3] == 0)
 
 
+def test_cornell_crop_window_as_the_reference_tests_it():
+    """test_integrators.py:29-52 as written there: an actual crop (crop_offset 124, 36; crop 1 x 1) of mi.cornell_box(), path max_depth = 1:
+    the rendered 1 x 1 image is the emitter radiance; hide_emitters => 0.  And the crop is the SAME camera: a crop window renders what
+    the full frame shows there (identical sub-pixel jitter => identical rays: crop pixel (x, y) with lane-local jitter j looks through
+    full-frame position (x + ox + j) -- checked on a window that straddles the light's edge)."""
+    d = mi.cornell_box(); d["integrator"] = {"type": "path", "max_depth": 1, "hide_emitters": False}
+    d["sensor"]["film"].update({"crop_offset_x": 124, "crop_offset_y": 36, "crop_width": 1, "crop_height": 1})
+    sc = mi.load_dict(d); assert sc.film_size == (1, 1)
+    img = orc.OracleScene(sc).render(seed=0, spp=64)
+    assert img.shape[:2] == (1, 1) and np.allclose(img[0, 0, :3], [18.387, 13.9873, 6.75357], rtol=1e-5)
+    d["integrator"]["hide_emitters"] = True
+    assert np.all(orc.OracleScene(mi.load_dict(d)).render(seed=0, spp=64)[..., :3] == 0)
+    # window vs full frame: the directly visible emitter (max_depth 1) is a deterministic function of the ray
+    full = mi.cornell_box(); full["integrator"] = {"type": "path", "max_depth": 1}; full["sensor"]["film"]["rfilter"] = {"type": "box"}
+    win = mi.cornell_box(); win["integrator"] = dict(full["integrator"]); win["sensor"]["film"]["rfilter"] = {"type": "box"}
+    ox, oy, w, h = 96, 24, 48, 32
+    win["sensor"]["film"].update({"crop_offset_x": ox, "crop_offset_y": oy, "crop_width": w, "crop_height": h})
+    spp = 256
+    a = orc.OracleScene(mi.load_dict(full)).render(seed=1, spp=spp)[oy:oy + h, ox:ox + w, :3]
+    b = orc.OracleScene(mi.load_dict(win)).render(seed=2, spp=spp)[..., :3]
+    assert b.shape == (h, w, 3)
+    lit_a, lit_b = a[..., 0] > 0, b[..., 0] > 0
+    inside = (a[..., 0] == a.max()) & (b[..., 0] == b.max()); outside = ~lit_a & ~lit_b
+    assert inside.sum() > 100 and outside.sum() > 100 and (inside | outside).mean() > 0.9      # same silhouette but for the edge pixels
+    edge = ~(inside | outside); assert np.abs(a[edge] - b[edge]).max() < 0.2 * a.max()            # coverage of an edge pixel: MC at 256 spp
+    with pytest.raises(RuntimeError, match="crop"):
+        bad = mi.cornell_box(); bad["sensor"]["film"].update({"crop_offset_x": 250, "crop_width": 10}); mi.load_dict(bad)
+
+
 def test_box_film_is_mean_of_lanes():
     """hdrfilm + box filter (imageblock.cpp:206-235, hdrfilm.cpp:402): pixel = mean of its lanes' radiance."""
     sc = mi.load_dict(scenes.liver_single_mesh(res=8, spp=4, grid_res=16)); o = orc.OracleScene(sc)

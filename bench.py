@@ -457,7 +457,7 @@ def run_prb(R, args):
         multi.render_distributed(ctx, seed, spp, rank, world, mode=mode, film_buf=red, out=img)
         g = (2.0 / img.numel()) * (img - target)                 # L2 loss adjoint (notebook cell 11); torch elementwise = plumbing
         if strong:
-            grad = multi.backward_distributed(ctx, g, mi.sample_tea_32(seed, 1)[0], spp, rank, world, grad_buf=red if red else None, mode="samples")
+            grad = multi.backward_distributed(ctx, g, mi.sample_tea_32(seed, 1)[0], spp, rank, world, grad_buf=True, mode="samples")   # True: the backend's buffer, reduced in place
         else:
             ctx.grid_grad_zero(0); ctx.render_backward(g, seed=mi.sample_tea_32(seed, 1)[0], spp=spp)
             grad = multi.grid_grad_tensor(ctx, 0, dev)

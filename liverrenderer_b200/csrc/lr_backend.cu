@@ -25,18 +25,6 @@ struct DevBuf {
     template <typename T> T *as() const { return (T *) p; }
 };
 
-struct WavefrontBuffers {
-    DevBuf states, queues, counters; uint32_t cap = 0;
-    uint32_t *live_host = nullptr;                       // pinned ring of live counts
-    std::vector<cudaEvent_t> ring_ev;                    // one per ring slot
-    std::vector<cudaEvent_t> kev;                        // event pool timing the TRACK / NEE launches
-    ~WavefrontBuffers() {
-        if (live_host) cudaFreeHost(live_host);
-        for (auto e : ring_ev) cudaEventDestroy(e);
-        for (auto e : kev) cudaEventDestroy(e);
-    }
-};
-
 // forward wavefront pool (lr_wavefront.cuh): SoA state planes + index queues + counters, and the mapped pinned ring the
 // iterations write their live counts to
 struct WVRing { uint32_t live; uint32_t pad; unsigned long long lane_next; };
@@ -66,7 +54,6 @@ struct lr_ctx {
     lr_stats st{};
     int blocks_per_sm[8] = {0}; int n_sm = 148;
     // wavefront volpath (lr_wavefront.cuh / lr_wavefront_host.inl)
-    WavefrontBuffers *wf = nullptr;                                    // prbvolpath pool
     WVPool *wv[4] = {nullptr, nullptr, nullptr, nullptr}; cudaStream_t stream_more[3] = {nullptr, nullptr, nullptr};   // forward pools: batches in flight
     uint32_t bvh4_nodes = 0; bool bvh4_small = false; uint32_t trace_n_smem = 0, trace_sd = 1; size_t trace_smem = 0;   // trace-kernel shared-memory plan
     DevBuf lane_cursor;                                                // device-side lane cursor shared by the batches of one render
@@ -123,7 +110,7 @@ void lr_destroy(lr_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    c->free_scene(); delete c->wf; c->wf = nullptr;
+    c->free_scene();
     for (int k = 0; k < 4; ++k) { delete c->wv[k]; c->wv[k] = nullptr; }
     for (int k = 0; k < 3; ++k) if (c->stream_more[k]) { cudaStreamDestroy(c->stream_more[k]); c->stream_more[k] = nullptr; }
     for (auto e : c->prof_ev) cudaEventDestroy(e);

@@ -138,12 +138,20 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         c->trace_smem = fixed + (size_t) c->trace_n_smem * sizeof(DNodeQ);
         if (getenv("LR_VERBOSE")) fprintf(stderr, "[lr] bvh4: %u nodes (%u in shared memory), worst-case stack %u entries (%u in shared memory), %zu B of shared memory per block\n",
                                           c->bvh4_nodes, c->trace_n_smem, sc.bvh4_stack, c->trace_sd, c->trace_smem);
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
-        LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) c->trace_smem));
+        // the attribute belongs to the function on this device, not to the context: it is only ever raised, so that an earlier context
+        // with a larger tree can still launch after a later context has uploaded a smaller one
+        static size_t s_trace_smem_set[64] = {0};
+        size_t &cur = s_trace_smem_set[c->device & 63];
+        if (c->trace_smem > cur) {
+            const int v = (int) c->trace_smem;
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, v));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, v));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2, short>, cudaFuncAttributeMaxDynamicSharedMemorySize, v));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<0, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, v));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<1, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, v));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_trace<2, int>, cudaFuncAttributeMaxDynamicSharedMemorySize, v));
+            cur = c->trace_smem;
+        }
     }
 
     // ---- bitmap textures (reflectance / bump maps) ----
@@ -308,11 +316,10 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
     if (begin == end) return LR_OK;
     c->wf_launches = 0; c->wf_tracking_ms = 0; c->wf_tracking_launches = 0;
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_PRBVOLPATH) {        // primal prbvolpath (INTEGRATOR_MAPPING renders)
-        if (int r = wf_prepare(c, (end - begin))) return r;
-        c->wf_tracking_ms = 0; c->wf_tracking_launches = 0; WFPrbArgs pa{};
+        if (int r = wv_prepare(c, (end - begin))) return r;
         if (p.n_passes != 1) LR_FAIL(c, LR_ERR_UNSUPPORTED, "prbvolpath: W*H*spp exceeds 2^32 lanes");
-        if (lanes_out) return c->film_channels == 5 ? wavefront_prb_pass<5, false, false>(c, a, pa) : wavefront_prb_pass<4, false, false>(c, a, pa);
-        return c->film_channels == 5 ? wavefront_prb_pass<5, true, false>(c, a, pa) : wavefront_prb_pass<4, true, false>(c, a, pa);
+        if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false, 1>(c, a) : wavefront_render_t<4, false, 1>(c, a);
+        return c->film_channels == 5 ? wavefront_render_t<5, true, 1>(c, a) : wavefront_render_t<4, true, 1>(c, a);
     }
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATH) {
         if (int r = wv_prepare(c, (end - begin))) return r;

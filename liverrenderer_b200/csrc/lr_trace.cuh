@@ -43,10 +43,22 @@ LR_DEV bool trace_walking(const TraceRay &r) { return r.node < TR_DONE; }
 
 LR_DEV void trace_begin(const DScene &sc, TraceRay &r, V3 o, V3 d, float maxt) {
     r.o = o; r.d = d; r.tmax = maxt;
-    r.inv = mk3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    // 1 / d, kept FINITE: the quantized slab test forms t = f * A + B with A ~ inv and B ~ -o * inv - A, and with inv = inf (a direction
+    // component that is exactly 0: an isotropic phase sample at u = 0 gives d = (0, 0, 1), one ray in ~1e7) every plane of that axis
+    // evaluates to inf - inf = NaN, fmaxf / fminf drop it, and the axis stops culling: such a ray visited every box that overlaps it along
+    // its one live axis -- thousands of nodes, one lane wide, 15 ms at the tail of a launch on the 20 k-triangle sphere.  With |inv|
+    // capped the planes are huge finite numbers of the right sign and the slabs cull exactly as they do for fp32 boxes.
+    const float kInvMax = 1e25f;
+    r.inv = mk3(copysignf(fminf(fabsf(1.f / d.x), kInvMax), d.x), copysignf(fminf(fabsf(1.f / d.y), kInvMax), d.y), copysignf(fminf(fabsf(1.f / d.z), kInvMax), d.z));
     r.ood = mk3(-o.x * r.inv.x, -o.y * r.inv.y, -o.z * r.inv.z);
     r.h.t = LR_INF; r.h.prim = 0xffffffffu; r.h.u = r.h.v = 0.f;
     r.sp = 0; r.node = sc.n_tris ? 0 : TR_DONE;
+    // A ray with a non-finite origin or direction (a degenerate BSDF / phase sample, about one path in 1e7) hits nothing in any
+    // traversal here -- every comparison of its slab test is false in the two-wide walk.  In the wide walk fmaxf / fminf DROP the NaNs,
+    // no box would cull, and the ray would visit the whole tree one lane wide (20 k triangles: tens of milliseconds at the tail of a
+    // launch): it is finished as a miss at once.
+    // The same goes for a null direction (inv = inf on every axis => every slab interval is inf - inf).
+    if (!isfinite((o.x + o.y + o.z) + (d.x + d.y + d.z)) || maxt != maxt || (d.x == 0.f && d.y == 0.f && d.z == 0.f)) r.node = TR_DONE;
 }
 
 // The traversal stack: the first `sd` entries of a lane live in shared memory (column `stack`, stride `stride` elements),

@@ -38,8 +38,9 @@ namespace lr {
 //   hit { t, prim, u, v }   lane { lane lo/hi, film sample position }           16-byte records
 //   n0  { shadow ray origin, max_dist | shadow ray direction, ds.dist }         NEE (volpath.cpp:400-554)
 //   n1  { throughput * (phase | bsdf) value * MIS weight * emitter value, walk medium | closest hit along the shadow ray }
+//   adj { dLoss / dRadiance of the lane }                                      16 bytes, touched by the prbvolpath adjoint only
 struct WVPlanes {
-    float4 *h0, *h1, *h2, *hit_, *lane_, *n0, *n1;
+    float4 *h0, *h1, *h2, *hit_, *lane_, *n0, *n1, *adj_;
     LR_DEV ulonglong2 &rng(uint32_t s) const { return reinterpret_cast<ulonglong2 *>(h0)[2 * (size_t) s]; }
     LR_DEV float4 &thr(uint32_t s) const { return h0[2 * (size_t) s + 1]; }
     LR_DEV float4 &o(uint32_t s) const { return h1[2 * (size_t) s]; }
@@ -52,8 +53,9 @@ struct WVPlanes {
     LR_DEV float4 &nd(uint32_t s) const { return n0[2 * (size_t) s + 1]; }
     LR_DEV float4 &nw(uint32_t s) const { return n1[2 * (size_t) s]; }
     LR_DEV float4 &nhit(uint32_t s) const { return n1[2 * (size_t) s + 1]; }
+    LR_DEV float4 &adj(uint32_t s) const { return adj_[s]; }          // prbvolpath adjoint: delta L of the lane (lr_wavefront_prb.cuh)
 };
-#define WV_N_PLANES 12                  // 16-byte units per slot
+#define WV_N_PLANES 13                  // 16-byte units per slot
 
 struct WVQueues {                      // device-side counters of one pool
     uint32_t n_trace, n_track, n_scatter, n_escape, n_shadow, n_nee, n_regen;

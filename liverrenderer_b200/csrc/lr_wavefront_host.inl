@@ -5,38 +5,8 @@
 
 static const int WF_RING = 8, WF_LAG = 3;
 
-// ---- legacy AoS pool of the wavefront prbvolpath ----
-static int wf_alloc(lr_ctx *c, WavefrontBuffers *&wp, uint64_t want) {
-    if (!wp) wp = new WavefrontBuffers();
-    WavefrontBuffers &w = *wp;
-    if (w.cap < want) {
-        w.cap = (uint32_t) want;
-        LR_CUDA(c, w.states.alloc((size_t) w.cap * sizeof(WState)));
-        LR_CUDA(c, w.queues.alloc((size_t) w.cap * 4 * (5 + WF_N_SURF)));
-        LR_CUDA(c, w.counters.alloc(sizeof(WQueues)));
-    }
-    if (!w.live_host) {
-        LR_CUDA(c, cudaHostAlloc((void **) &w.live_host, WF_RING * sizeof(uint32_t), cudaHostAllocDefault));
-        w.ring_ev.resize(WF_RING);
-        for (auto &e : w.ring_ev) LR_CUDA(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    }
-    return LR_OK;
-}
-static int wf_prepare(lr_ctx *c, uint64_t n_lanes) {
-    uint64_t want = std::min<uint64_t>(c->wf_pool_slots, (n_lanes + 31) & ~31ull);
-    want = std::max<uint64_t>(want, 1024);
-    return wf_alloc(c, c->wf, want);
-}
-static void wf_bind(WFArgs &a, WavefrontBuffers &w) {
-    a.st = w.states.as<WState>(); a.q = w.counters.as<WQueues>(); a.cap = w.cap;
-    uint32_t *qb = w.queues.as<uint32_t>();
-    a.q_active[0] = qb; a.q_active[1] = qb + w.cap; a.q_scatter = qb + 2 * (size_t) w.cap; a.q_regen = qb + 3 * (size_t) w.cap;
-    for (int b = 0; b < WF_N_SURF; ++b) a.q_surf[b] = qb + (4 + b) * (size_t) w.cap;
-    a.q_nee = qb + (4 + WF_N_SURF) * (size_t) w.cap;
-}
-
 // ---------------------------------------------------------------------------------------------
-// forward wavefront (kernels: lr_wavefront.cuh)
+// wavefront pools and host loop (kernels: lr_wavefront.cuh, lr_wavefront_prb.cuh)
 // ---------------------------------------------------------------------------------------------
 // stage kinds of the per-stage profile (lr_profile_get)
 enum { ST_GEN = 0, ST_TRACE_C, ST_TRACK, ST_SHADE_A_MED, ST_SHADE_A_SURF, ST_ESCAPE, ST_TRACE_S, ST_NEE, ST_SHADE_B_MED, ST_SHADE_B_SURF, ST_REGEN, ST_OTHER, ST_COUNT };
@@ -87,7 +57,7 @@ static int wv_prepare(lr_ctx *c, uint64_t n_lanes) {
 static void wv_bind(WVArgs &a, WVPool &w) {
     char *pb = (char *) w.planes.p; const size_t u = (size_t) w.cap * 16;           // 16-byte units per slot: h0 2, h1 2, h2 2, hit 1, lane 1, n0 2, n1 2
     a.p.h0 = (float4 *) pb; a.p.h1 = (float4 *) (pb + 2 * u); a.p.h2 = (float4 *) (pb + 4 * u); a.p.hit_ = (float4 *) (pb + 6 * u); a.p.lane_ = (float4 *) (pb + 7 * u);
-    a.p.n0 = (float4 *) (pb + 8 * u); a.p.n1 = (float4 *) (pb + 10 * u);
+    a.p.n0 = (float4 *) (pb + 8 * u); a.p.n1 = (float4 *) (pb + 10 * u); a.p.adj_ = (float4 *) (pb + 12 * u);
     a.q = w.counters.as<WVQueues>(); a.cap = w.cap;
     uint32_t *qb = w.queues.as<uint32_t>(); const size_t qs = w.cap;
     a.q_trace = qb; a.q_track = qb + qs; a.q_scatter = qb + 2 * qs; a.q_escape = qb + 3 * qs; a.q_shadow = qb + 4 * qs; a.q_nee = qb + 5 * qs; a.q_regen = qb + 6 * qs;
@@ -106,8 +76,11 @@ struct WvRun {
 // are filled by the others.  All batches draw their lanes from one device-side cursor; lanes are independent, so results do not
 // depend on the batching.  The host never waits for an iteration it has just enqueued: the live count of iteration i is written
 // to mapped pinned memory by the iteration itself and checked WF_LAG iterations later.
-template <int C, bool TO_FILM>
-static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
+// MODE 0: volpath (lr_wavefront.cuh); 1: prbvolpath primal, 2: prbvolpath adjoint replay (lr_wavefront_prb.cuh) -- the same stage
+// sequence, queues, pools and TRACE kernels; the stage kernels differ.
+template <int C, bool TO_FILM, int MODE = 0>
+static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs pa = WFPrbArgs{}) {
+    constexpr bool ADJ = MODE == 2;
     const uint64_t cap = c->wv[0]->cap, n_lanes = ra.lane_end - ra.lane_begin;
     const bool prof = c->profile_on;
     WvRun runs[4]; int n_runs = 0;
@@ -160,7 +133,8 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
         // GEN hands out lanes while n_alloc + slack <= cap; slack = 32 slots per resident warp of the GEN grid bounds the overshoot
         r.gen_grid = (int) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) grid, a.cap / 512)); a.slack = (uint32_t) r.gen_grid * 256u;
         k_wv_init<<<1, 1, 0, r.s>>>(a.q); ++launches;
-        launch(r, ST_GEN, [&] { k_wv_gen<C, TO_FILM><<<r.gen_grid, 256, 0, r.s>>>(c->sc, a); });
+        launch(r, ST_GEN, [&] { if constexpr (MODE == 0) k_wv_gen<C, TO_FILM><<<r.gen_grid, 256, 0, r.s>>>(c->sc, a);
+                                else k_wvp_gen<C, TO_FILM, ADJ><<<r.gen_grid, 256, 0, r.s>>>(c->sc, a, pa); });
         r.iter = 0; r.busy = true;
         return readback(r);
     };
@@ -172,19 +146,22 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
             if (w.ring_host[slot].lane_next >= n_lanes) lanes_done = true;
             if (w.ring_host[slot].live == 0 || *c->cancel_host) { r.busy = false; return 1; }
         }
-        launch(r, ST_TRACK, [&] { if (c->all_media_dda) k_wv_track_dda<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
-        launch(r, ST_SHADE_A_MED, [&] { k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); });
-        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] { k_wv_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); });
-        launch(r, ST_ESCAPE, [&] { k_wv_escape<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+        launch(r, ST_TRACK, [&] { if constexpr (MODE != 0) k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a);
+                                  else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+        launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_shade_a_medium<ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
+        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] {
+            if constexpr (MODE == 0) k_wv_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); else k_wvp_shade_a_surface<C, TO_FILM, ADJ><<<grid128, 128, 0, s>>>(c->sc, a, b); });
+        if (MODE != 2) launch(r, ST_ESCAPE, [&] { if constexpr (MODE == 0) k_wv_escape<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_escape<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         launch(r, ST_TRACE_S, [&] {
             if (shadow_mode == 1) { if (stk16) k_wv_trace<1, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<1, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); }
             else { if (stk16) k_wv_trace<2, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<2, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); } });
-        launch(r, ST_NEE, [&] { k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });
-        launch(r, ST_SHADE_B_MED, [&] { k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
-        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_B_SURF, [&] { k_wv_shade_b_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); });
+        launch(r, ST_NEE, [&] { if constexpr (MODE == 0) k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); else k_wvp_nee<ADJ><<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });
+        launch(r, ST_SHADE_B_MED, [&] { if constexpr (MODE == 0) k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_shade_b_medium<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
+        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_B_SURF, [&] {
+            if constexpr (MODE == 0) k_wv_shade_b_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); else k_wvp_shade_b_surface<C, TO_FILM, ADJ><<<grid128, 128, 0, s>>>(c->sc, a, b); });
         k_wv_mid_iteration<<<1, 1, 0, s>>>(a.q, d_items, sids); ++launches;
         launch(r, ST_TRACE_C, [&] { if (stk16) k_wv_trace<0, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<0, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); });
-        if (multipass) launch(r, ST_REGEN, [&] { k_wv_regen<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+        if constexpr (MODE == 0) { if (multipass) launch(r, ST_REGEN, [&] { k_wv_regen<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); }); }
         return readback(r);
     };
     for (bool any = true; any;) {
@@ -219,64 +196,25 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// wavefront prbvolpath (kernels: lr_wavefront_prb.cuh): the same iteration structure; ADJ selects the adjoint replay
+// render_backward as two wavefront passes per lane chunk (kernels: lr_wavefront_prb.cuh): primal radiance per lane -> buffer,
+// then the adjoint replay of the same streams
 // ---------------------------------------------------------------------------------------------
-template <int C, bool TO_FILM, bool ADJ>
-static int wavefront_prb_pass(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs &pa) {
-    WavefrontBuffers &w = *c->wf; cudaStream_t s = c->stream;
-    WFArgs a{}; wf_bind(a, w);
-    a.tris_gid = ra.tris_gid; a.film = ra.film; a.lanes_out = ra.lanes_out; a.lane_begin = ra.lane_begin; a.lane_end = ra.lane_end; a.map = ra.map;
-    a.seed = ra.seed; a.spp_per_pass = ra.spp_per_pass; a.n_passes = 1; a.stats = ra.stats;
-    uint32_t surf_mask = 1u | c->surf_bucket_mask;
-    const int grid = c->n_sm * 8;
-    uint64_t launches = 0; size_t kev_used = 0;
-    auto timed = [&]() -> cudaEvent_t * {
-        if (kev_used + 2 > w.kev.size()) { size_t n0 = w.kev.size(); w.kev.resize(n0 + 512); for (size_t i = n0; i < w.kev.size(); ++i) cudaEventCreate(&w.kev[i]); }
-        kev_used += 2; return &w.kev[kev_used - 2];
-    };
-    k_wf_init<<<(w.cap + 255) / 256, 256, 0, s>>>(a.q, a.q_regen, w.cap, a.st);
-    a.cur = 0; k_wfp_gen<ADJ><<<grid, 256, 0, s>>>(c->sc, a, pa); a.cur = 1; launches += 2;
-    LR_CUDA(c, cudaGetLastError());
-    for (uint64_t iter = 0;; ++iter) {
-        if (iter >= (uint64_t) WF_LAG) {
-            int slot = (int) ((iter - WF_LAG) % WF_RING);
-            LR_CUDA(c, cudaEventSynchronize(w.ring_ev[slot]));
-            if (w.live_host[slot] == 0 || *c->cancel_host) break;
-        }
-        k_wf_begin_iteration<<<1, 1, 0, s>>>(a.q, a.cur);
-        { cudaEvent_t *e = timed(); cudaEventRecord(e[0], s); k_wfp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); cudaEventRecord(e[1], s); }
-        k_wfp_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); launches += 3;
-        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) { k_wfp_shade_a_surface<C, TO_FILM, ADJ><<<grid, 128, 0, s>>>(c->sc, a, b); ++launches; }
-        { cudaEvent_t *e = timed(); cudaEventRecord(e[0], s); k_wfp_nee<ADJ><<<grid, 256, 0, s>>>(c->sc, a, surf_mask); cudaEventRecord(e[1], s); }
-        k_wfp_shade_b_medium<<<grid, 256, 0, s>>>(c->sc, a); launches += 2;
-        for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) { k_wfp_shade_b_surface<C, TO_FILM, ADJ><<<grid, 128, 0, s>>>(c->sc, a, b); ++launches; }
-        k_wfp_gen<ADJ><<<grid, 256, 0, s>>>(c->sc, a, pa); ++launches;
-        a.cur ^= 1;
-        int slot = (int) (iter % WF_RING);
-        LR_CUDA(c, cudaMemcpyAsync(&w.live_host[slot], &a.q->n_active[a.cur], 4, cudaMemcpyDeviceToHost, s));
-        LR_CUDA(c, cudaEventRecord(w.ring_ev[slot], s));
-        LR_CUDA(c, cudaGetLastError());
-    }
-    LR_CUDA(c, cudaStreamSynchronize(s));
-    double ms = 0; uint64_t n = 0;
-    for (size_t i = 0; i + 1 < kev_used; i += 2) { float t = 0.f; if (cudaEventElapsedTime(&t, w.kev[i], w.kev[i + 1]) == cudaSuccess) { ms += t; ++n; } }
-    c->wf_launches += launches; c->wf_tracking_ms += ms; c->wf_tracking_launches += n;
-    return LR_OK;
-}
-
-// render_backward as two wavefront passes per lane chunk: primal radiance per lane -> buffer, then the adjoint replay
 static int wavefront_prb_backward(lr_ctx *c, RenderArgs ra, const float *grad_dev, uint32_t grad_channels) {
-    const uint64_t chunk = 1ull << 25;                                  // 32 Mi lanes: 512 MiB of per-lane radiance
+    const uint64_t chunk = 1ull << 27;                                  // 128 Mi lanes: 2 GiB of per-lane radiance
     uint64_t n = ra.lane_end - ra.lane_begin;
-    if (int r = wf_prepare(c, std::min(n, chunk))) return r;
+    if (int r = wv_prepare(c, std::min(n, chunk))) return r;
     size_t need = (size_t) std::min(n, chunk) * 16;
     if (c->prb_L.bytes < need) LR_CUDA(c, c->prb_L.alloc(need));
-    c->wf_launches = 0; c->wf_tracking_ms = 0; c->wf_tracking_launches = 0;
+    uint64_t launches = 0; double t_ms = 0; uint64_t t_n = 0;
     WFPrbArgs pa{}; pa.grad_in = grad_dev; pa.weight_img = c->weight_img.as<float>(); pa.grad_channels = grad_channels; pa.primal_L = c->prb_L.as<float>();
     for (uint64_t b = ra.lane_begin; b < ra.lane_end; b += chunk) {
         RenderArgs r1 = ra; r1.lane_begin = b; r1.lane_end = std::min(ra.lane_end, b + chunk); r1.lanes_out = c->prb_L.as<float>(); r1.film = nullptr;
-        if (int r = wavefront_prb_pass<4, false, false>(c, r1, pa)) return r;
-        if (int r = wavefront_prb_pass<4, false, true>(c, r1, pa)) return r;
+        if (int r = wavefront_render_t<4, false, 1>(c, r1, pa)) return r;
+        launches += c->wf_launches; t_ms += c->wf_tracking_ms; t_n += c->wf_tracking_launches;
+        r1.lanes_out = nullptr;
+        if (int r = wavefront_render_t<4, false, 2>(c, r1, pa)) return r;
+        launches += c->wf_launches; t_ms += c->wf_tracking_ms; t_n += c->wf_tracking_launches;
     }
+    c->wf_launches = launches; c->wf_tracking_ms = t_ms; c->wf_tracking_launches = t_n;
     return LR_OK;
 }

@@ -74,3 +74,14 @@ def test_sample_split_film_and_gradient_two_devices():
     if _n_devices() < 2:
         pytest.skip("needs two CUDA devices")
     _check_split([0, 1])
+
+
+def test_two_contexts_with_different_trees_share_the_trace_kernels():
+    """The dynamic shared-memory limit of the TRACE kernels is a per-function attribute: uploading a scene with a SMALL tree in a second
+    context must not stop the first context (larger tree, more shared memory) from rendering."""
+    big = mi.Context(0).upload(mi.load_dict(scenes.sphere_liver_inverse(res=32, spp=4, grid_res=16, tracking="dda")))      # 20 480 triangles
+    a = big.render(seed=1, spp=4)
+    small = mi.Context(0).upload(mi.load_dict(scenes.cornell_box_fog(res=32, spp=4)))                                      # a few dozen
+    small.render(seed=1, spp=4)
+    b = big.render(seed=1, spp=4)
+    assert np.allclose(a, b, rtol=1e-5, atol=1e-7)                     # the same lanes; film atomics in another order

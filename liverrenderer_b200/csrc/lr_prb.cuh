@@ -25,13 +25,16 @@ LR_DEV void grid_grad_scatter(const DGrid &g, const GridTap &tap, float gval, bo
 #pragma unroll
     for (int k = 0; k < 8; ++k) c[k] = gval * tap.w[k];
     if (peers != (1u << me)) {
-        // segmented reduction over the peer set: every peer adds into the leader
-        unsigned rest = peers & ~(1u << leader);
+        // segmented butterfly over the peer set (ranks within `peers`): in round `step` the peer of rank r, r a multiple of 2 * step,
+        // adds the partial sum of rank r + step; after ceil(log2 n) rounds rank 0 = the leader holds the total.  (The loop this
+        // replaces had every peer walk the whole set: n - 1 rounds of 8 shuffles.)
+        const int n = __popc(peers), rank = __popc(peers & ((1u << me) - 1u));
+        for (int step = 1; step < n; step <<= 1) {
+            const unsigned src = __fns(peers, (unsigned) me, step + 1);                 // lane of rank + step, 0xffffffff beyond the set
+            const bool take = (rank & (2 * step - 1)) == 0 && src != 0xffffffffu;
+            const int from = src != 0xffffffffu ? (int) src : me;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            float acc = c[k]; unsigned r = rest;
-            while (r) { int src = __ffs(r) - 1; r &= r - 1; float v = __shfl_sync(peers, c[k], src); if (me == leader) acc += v; }
-            c[k] = acc;
+            for (int k = 0; k < 8; ++k) { const float v = __shfl_sync(peers, c[k], from); if (take) c[k] += v; }
         }
     }
     if (me == leader) {

@@ -146,7 +146,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
             if (w.ring_host[slot].lane_next >= n_lanes) lanes_done = true;
             if (w.ring_host[slot].live == 0 || *c->cancel_host) { r.busy = false; return 1; }
         }
-        launch(r, ST_TRACK, [&] { if constexpr (MODE != 0) k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a);
+        launch(r, ST_TRACK, [&] { if constexpr (MODE != 0) { if (c->all_media_dda && !getenv("LR_PRB_TRACK_SIMPLE")) k_wvp_track_dda<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); }
                                   else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_shade_a_medium<ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] {

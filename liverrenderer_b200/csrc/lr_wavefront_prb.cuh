@@ -216,6 +216,116 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track(const __grid_const
     flush_counters(cnt, 0, a.stats);
 }
 
+// TRACK for scenes whose media all use the majorant DDA (production mode): the per-item work of k_wvp_track as a persistent
+// "while-while" loop with the refill scheme of k_wv_track_dda -- a lane whose item has finished parks, and once half of the warp is
+// parked the parked lanes are written out and pull the next queue entries.  After a null collision the walk CONTINUES in its DDA state
+// (k_wvp_track restarts it from the collision point: the same cell, the same majorant); draw order per lane is unchanged: optical
+// depth, then per tentative collision (null test, roulette of the next loop iteration, next optical depth).
+template <int C, bool TO_FILM, bool ADJ>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+    const WVPlanes &p = a.p;
+    const uint32_t n_items = a.q->n_track;
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    uint32_t slot = 0, depth = 0, f = 0; int event = -2;                  // -2 idle, -1 walking, 0 end of path, 1 scatter, 2 boundary
+    Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f; V3 thr = mk3(0.f), Lcur = mk3(0.f), dL = mk3(0.f);
+    float hit_t = 0.f, t = 0.f, tau = 0.f, t_end = 0.f, eta = 1.f; int grid_id = 0, medium = 0; DDA dd{};
+    Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
+    bool exhausted = false;
+    for (;;) {
+        const unsigned walking = __ballot_sync(0xffffffffu, event == -1);
+        if (__popc(walking) <= LR_TRACK_REFILL) {
+            // ---- write finished items out and queue them (converged: the pushes use warp ballots) ----
+            if (__any_sync(0xffffffffu, event >= 0)) {
+                if (event >= 0) wv_rng_store(p, slot, smp);
+                if (event > 0) {
+                    p.o(slot) = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
+                    p.thr(slot) = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
+                    p.hit(slot).x = hit_t;
+                }
+                wvp_finish<C, TO_FILM, ADJ>(sc, a, slot, event == 0, f);
+                const bool esc = event == 2 && !hit_valid(h0);
+                const uint32_t b = (event == 2 && !esc) ? wv_bucket(sc, h0) : 0xffu;
+                wf_push(a.q_scatter, &a.q->n_scatter, slot, event == 1);
+                wf_push(a.q_escape, &a.q->n_escape, slot, esc);
+#pragma unroll
+                for (uint32_t k = 0; k < WF_N_SURF; ++k) wf_push(a.q_surf[k], &a.q->n_surf[k], slot, b == k);
+                if (event >= 0) event = -2;
+            }
+            if (!exhausted) {
+                const unsigned idle = ~walking; uint32_t base = 0;
+                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor[1], (uint32_t) __popc(idle));
+                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+                exhausted = base + (uint32_t) __popc(idle) >= n_items;
+                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+                if (event == -2 && qi < n_items) {
+                    slot = a.q_track[qi];
+                    smp = wv_rng(p, slot);
+                    float4 t4 = p.o(slot); ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+                    t4 = p.d(slot); ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
+                    t4 = p.thr(slot); thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
+                    h0 = wf_hit(p.hit(slot)); hit_t = h0.t;
+                    t4 = p.res(slot); eta = t4.w; Lcur = mk3(t4.x, t4.y, t4.z);
+                    if (ADJ) { t4 = p.adj(slot); dL = mk3(t4.x, t4.y, t4.z); }
+                    medium = wf_medium(f); const DMedium &m = sc.media[medium]; grid_id = m.m.sigma_t_grid; const DGrid &g = sc.grids[grid_id];
+                    event = 2;
+                    float mint, maxt;
+                    if (medium_clip(g, ray, mint, maxt)) {
+                        t_end = fminf(maxt, hit_t);
+                        if (mint < t_end) { dda_init(g, ray, mint, dd); t = mint; tau = -logf(1.f - smp.next_1d()); event = -1; }
+                    }
+                }
+            }
+        }
+        // ---- walk: bring every walking lane to its next tentative collision (or the end of its segment) ----
+        bool collide = false; float mu = 0.f;
+        if (event == -1) {
+            const DGrid &g = sc.grids[grid_id]; const float mu_scale = sc.media[medium].m.scale * kPrbMajorantSlack;
+#pragma unroll 1
+            for (int k = 0; k < LR_TRACK_STEPS; ++k) {
+                mu = mu_scale * dda_majorant(g, dd);
+                const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
+                const float dtau = mu * (t_exit - t);
+                if (dtau >= tau && mu > 0.f) { t = fminf(t + tau / mu, t_exit); collide = true; break; }
+                tau -= dtau; t = t_exit;
+                if (t_exit >= t_end) { event = 2; break; }
+                dda_advance(g, dd);
+            }
+        }
+        // ---- tentative collisions, evaluated together (prbvolpath.py:181-204) ----
+        if (collide) {
+            const DGrid &g = sc.grids[grid_id]; const DMedium &m = sc.media[medium];
+            cnt.collisions++;
+            const V3 pt = ray_at(ray, t);
+            GridTap tap; const V3 sigma_t = grid_eval<ADJ>(g, pt, &tap) * m.m.scale, ce = mk3(mu), sigma_n = ce - sigma_t;
+            V3 weight = mk3(1.f / mu), dweight;
+            float scatter_prob = 1.f; bool null_c = false;
+            if (sc.prb_handle_null) { scatter_prob = hmean(sigma_t / ce); null_c = smp.next_1d() >= scatter_prob; }
+            if (null_c) {
+                const V3 A = weight; weight *= sigma_n / (1.f - scatter_prob); dweight = A * (-m.m.scale / (1.f - scatter_prob));
+                thr *= weight;
+                if (ADJ) wvp_scatter_main(sc, m, tap, dL, Lcur, weight, dweight);
+                if (!(depth < sc.max_depth)) event = 0;                      // :189-190
+                else if (!wvp_rr(sc, smp, thr, eta, depth)) event = 0;       // roulette of the next loop iteration
+                else tau = -logf(1.f - smp.next_1d());
+            } else {
+                depth += 1; cnt.real_scatters++;
+                { float *lp = reinterpret_cast<float *>(&p.lsp(slot)); lp[0] = pt.x; lp[1] = pt.y; lp[2] = pt.z; }
+                if (!(depth < sc.max_depth)) { thr *= weight; event = 0; }
+                else {
+                    const V3 A = weight; const V3 albedo = medium_albedo(sc, m, pt);
+                    weight *= (sigma_t * albedo) / scatter_prob; dweight = A * albedo * (m.m.scale / scatter_prob);
+                    thr *= weight;
+                    if (ADJ) wvp_scatter_main(sc, m, tap, dL, Lcur, weight, dweight);
+                    ray.o = pt; hit_t = hit_t - t; event = 1;
+                }
+            }
+        }
+        if (exhausted && !__any_sync(0xffffffffu, event != -2)) break;
+    }
+    flush_counters(cnt, 0, a.stats);
+}
+
 // ------------------------------------------------------------------------------------------
 // SHADE_A: emitter sampling (prbvolpath.py:354-378).  The shadow ray goes to the NEE planes; TRACE_S / NEE finish the estimate.
 // `nw` holds sgn * throughput * (phase | bsdf) value * MIS weight * emitter value: +1 primal, -1 adjoint (contributions are subtracted).

@@ -4,6 +4,7 @@
 #include "lr_kernels.cuh"
 #include "lr_lanes.h"
 #include <cub/device/device_radix_sort.cuh>
+#include <nvtx3/nvToolsExt.h>          // header-only: ranges are no-ops unless a tool (nsys / ncu --nvtx) is attached
 #include <vector>
 #include <string>
 #include <algorithm>
@@ -36,6 +37,8 @@ struct WVPool {
 
 struct lr_ctx {
     int device = 0; cudaStream_t stream = nullptr; bool own_stream = false;
+    int smaj_grid = -1; uint32_t smaj_floats = 0;         // majorant super-grid staged in shared memory by k_wv_track_dda (0: none)
+    bool nvtx_open = false; bool nvtx = getenv("LR_NVTX") != nullptr;      // per-stage / per-call NVTX ranges (include/mitsuba/core/profiler.h:20-49 has ITT / NVTX scopes per phase)
     LaneMap lane_map{0, 0, 0};                      // lr_set_lane_map: strided lane set of the following render / backward calls
     void *noalloc_ptr = nullptr;                    // device address of g_noalloc_scratch on `device` (lr_noalloc.inl)
     std::string err; bool has_scene = false;

@@ -189,7 +189,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         d.filter = g.filter; d.wrap = g.wrap; d.differentiable = g.differentiable;
         d.cell = s->integrator.majorant_cell ? (int) s->integrator.majorant_cell : 8;
         d.mx = (d.rx + d.cell - 1) / d.cell; d.my = (d.ry + d.cell - 1) / d.cell; d.mz = (d.rz + d.cell - 1) / d.cell;
-        DevBuf *bm = c->newbuf(); LR_CUDA(c, bm->alloc((size_t) d.mx * d.my * d.mz * 4)); d.maj = bm->as<float>();
+        DevBuf *bm = c->newbuf(); LR_CUDA(c, bm->alloc((((size_t) d.mx * d.my * d.mz + 3) & ~(size_t) 3) * 4)); d.maj = bm->as<float>();   // rounded to 16 B: bulk copies move whole 16-byte units
         if (g.channels == 1 && g.filter == LR_FILTER_TRILINEAR && g.wrap == LR_WRAP_CLAMP && getenv("LR_NO_FAT") == nullptr) {      // fat-voxel copy: 32 B per record
             DevBuf *bf = c->newbuf(); LR_CUDA(c, bf->alloc((size_t) (d.rx + 1) * (d.ry + 1) * (d.rz + 1) * 32)); d.fat = bf->as<float4>();
         }
@@ -243,6 +243,20 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     c->surf_bucket_mask = surf_mask;
     c->all_media_dda = s->integrator.tracking == LR_TRACKING_DDA && getenv("LR_TRACK_REFILL_OFF") == nullptr;   // persistent TRACK (k_wf_track_dda)
     for (uint32_t i = 0; i < s->n_media; ++i) if (s->media[i].kind != LR_MEDIUM_HETEROGENEOUS) c->all_media_dda = false;
+    // majorant super-grid staged in shared memory by the persistent TRACK (TMA bulk copy at kernel start): the grid of the first medium, if it fits
+    c->smaj_grid = -1; c->smaj_floats = 0;
+    if (c->all_media_dda && s->n_media && getenv("LR_NO_SMAJ") == nullptr) {
+        const int gi = s->media[0].sigma_t_grid; const DGrid &g = c->h_grids[gi];
+        const size_t n = ((size_t) g.mx * g.my * g.mz + 3) & ~(size_t) 3;
+        if (n * 4 <= 200 * 1024) {
+            c->smaj_grid = gi; c->smaj_floats = (uint32_t) n;
+            const int lim = 200 * 1024 + 64;
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_track_dda<4, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_track_dda<4, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_track_dda<5, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+            LR_CUDA(c, cudaFuncSetAttribute(k_wv_track_dda<5, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, lim));
+        }
+    }
     c->has_scene = true; memset(&c->st, 0, sizeof c->st);
     return LR_OK;
 }
@@ -275,6 +289,7 @@ static int launch_render_lanes(lr_ctx *c, const RenderArgs &a, bool to_film) {
 static int begin_call(lr_ctx *c, const char *what) {
     if (!c) { g_last_error = std::string(what) + ": NULL context"; return LR_ERR_INVALID_ARG; }
     if (!c->has_scene) LR_FAIL(c, LR_ERR_NO_SCENE, "%s: no scene uploaded", what);
+    if (c->nvtx) { nvtxRangePushA(what); c->nvtx_open = true; }
     LR_CUDA(c, cudaSetDevice(c->device));
     *c->cancel_host = 0;
     LR_CUDA(c, cudaMemsetAsync(c->work_counter.p, 0, 8, c->stream));
@@ -283,6 +298,7 @@ static int begin_call(lr_ctx *c, const char *what) {
     return LR_OK;
 }
 static int end_call(lr_ctx *c, uint64_t launches, bool tracking) {
+    if (c->nvtx_open) { nvtxRangePop(); c->nvtx_open = false; }
     LR_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     unsigned long long h[4]; LR_CUDA(c, cudaMemcpyAsync(h, c->stats.p, 32, cudaMemcpyDeviceToHost, c->stream));
     LR_CUDA(c, cudaStreamSynchronize(c->stream));

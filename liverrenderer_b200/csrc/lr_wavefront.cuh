@@ -25,6 +25,7 @@
 #pragma once
 #include "lr_wf_common.cuh"
 #include "lr_trace.cuh"
+#include "lr_tma.cuh"
 #include <cuda_pipeline.h>
 
 namespace lr {
@@ -472,8 +473,26 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
 #ifndef LR_TRACK_STEPS
 #define LR_TRACK_STEPS 6              // super-voxel steps per lane between two converged points
 #endif
-template <int C, bool TO_FILM>
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+// SMAJ: the majorant super-grid of grid `smaj_grid` (`smaj_floats` values, a multiple of 4) is staged in shared memory by ONE bulk
+// asynchronous copy through the TMA unit at kernel start (lr_tma.cuh) -- every DDA step then reads its majorant with an LDS instead of a
+// dependent global load (the walk is a chain of such loads: the kernel is latency-bound, ncu long-scoreboard).  128 KiB for the 256^3
+// grid at cell 8, so the block is 1024 threads, one per SM (same resident threads as 4 x 256).  Grids whose super-grid does not fit
+// (C3-XL: 1 MiB) and scenes with several grids use the global-memory form.
+struct TrackSmaj { int grid; uint32_t floats; };
+template <int C, bool TO_FILM, bool SMAJ>
+__global__ void __launch_bounds__(SMAJ ? 1024 : 256, SMAJ ? 1 : LR_WF_OCC) k_wv_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a, const TrackSmaj sm) {
+    extern __shared__ __align__(16) float s_maj[];
+    if (SMAJ) {
+        __shared__ __align__(8) uint64_t bar;
+        if (threadIdx.x == 0) tma_bar_init(&bar, 1);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const uint32_t bytes = sm.floats * 4u; tma_bar_expect(&bar, bytes);
+            const char *src = reinterpret_cast<const char *>(sc.grids[sm.grid].maj); char *dst = reinterpret_cast<char *>(s_maj);
+            for (uint32_t off = 0; off < bytes; off += 32768u) tma_load_1d(dst + off, src + off, min(32768u, bytes - off), &bar);
+        }
+        tma_bar_wait(&bar, 0);
+    }
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     const WVPlanes &p = a.p;
     const uint32_t n_items = a.q->n_track;
@@ -521,7 +540,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_dda(const __grid_co
             const DGrid &g = sc.grids[grid_id];
 #pragma unroll 1
             for (int k = 0; k < LR_TRACK_STEPS; ++k) {
-                mu = mu_scale * dda_majorant(g, dd);
+                mu = mu_scale * ((SMAJ && grid_id == sm.grid) ? s_maj[((size_t) dd.iz * g.my + dd.iy) * g.mx + dd.ix] : dda_majorant(g, dd));
                 const float t_exit = fminf(fminf(dd.tnx, dd.tny), fminf(dd.tnz, t_end));
                 const float dtau = mu * (t_exit - t);
                 if (dtau >= tau && mu > 0.f) { t = fminf(t + tau / mu, t_exit); collide = true; break; }

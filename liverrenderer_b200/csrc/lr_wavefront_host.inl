@@ -112,7 +112,9 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
             if (kev_used + 2 > kev.size()) { size_t n0 = kev.size(); kev.resize(n0 + 1024); for (size_t i = n0; i < kev.size(); ++i) cudaEventCreate(&kev[i]); }
             e = &kev[kev_used]; kev_used += 2; kev_kind.push_back(kind); cudaEventRecord(e[0], r.s);
         }
+        if (c->nvtx) nvtxRangePushA(kStageNames[kind]);                // NVTX range per stage launch (LR_NVTX=1), like the reference's ProfilerPhase scopes
         fn(); ++launches;
+        if (c->nvtx) nvtxRangePop();
         if (prof) cudaEventRecord(e[1], r.s);
         if (dbg_sync) {                                                // LR_WF_SYNC=1: find the stage a device fault comes from
             cudaError_t err = cudaStreamSynchronize(r.s);
@@ -147,7 +149,8 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
             if (w.ring_host[slot].live == 0 || *c->cancel_host) { r.busy = false; return 1; }
         }
         launch(r, ST_TRACK, [&] { if constexpr (MODE != 0) { if (c->all_media_dda && !getenv("LR_PRB_TRACK_SIMPLE")) k_wvp_track_dda<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); }
-                                  else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+                                  else if (c->all_media_dda && c->smaj_floats) k_wv_track_dda<C, TO_FILM, true><<<c->n_sm, 1024, (size_t) c->smaj_floats * 4, s>>>(c->sc, a, TrackSmaj{c->smaj_grid, c->smaj_floats});
+                                  else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM, false><<<grid, 256, 0, s>>>(c->sc, a, TrackSmaj{-1, 0u}); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_shade_a_medium<ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] {
             if constexpr (MODE == 0) k_wv_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b); else k_wvp_shade_a_surface<C, TO_FILM, ADJ><<<grid128, 128, 0, s>>>(c->sc, a, b); });

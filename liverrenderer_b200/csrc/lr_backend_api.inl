@@ -193,13 +193,16 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         if (g.channels == 1 && g.filter == LR_FILTER_TRILINEAR && g.wrap == LR_WRAP_CLAMP && getenv("LR_NO_FAT") == nullptr) {      // fat-voxel copy: 32 B per record
             DevBuf *bf = c->newbuf(); LR_CUDA(c, bf->alloc((size_t) (d.rx + 1) * (d.ry + 1) * (d.rz + 1) * 32)); d.fat = bf->as<float4>();
         }
-        if (g.differentiable && g.channels != 1 && s->integrator.kind == LR_INTEGRATOR_PRBVOLPATH)
-            LR_FAIL(c, LR_ERR_UNSUPPORTED, "grid %u: a differentiable gridvolume must have 1 channel (the per-channel gradient of an rgb sigma_t / albedo grid is not "
-                                           "implemented; the adjoint would silently return zeros)", i);
         if (g.differentiable) { DevBuf *bg = c->newbuf(); LR_CUDA(c, bg->alloc(n * 4)); LR_CUDA(c, cudaMemsetAsync(bg->p, 0, n * 4, c->stream)); d.grad = bg->as<float>(); }
     }
     c->h_media.resize(s->n_media);
     for (uint32_t i = 0; i < s->n_media; ++i) {
+        if (s->integrator.kind == LR_INTEGRATOR_PRBVOLPATH && s->media[i].kind == LR_MEDIUM_HETEROGENEOUS && s->media[i].sigma_t_grid >= 0) {
+            const lr_grid &sg = s->grids[s->media[i].sigma_t_grid];
+            if (sg.differentiable && sg.channels != 1)
+                LR_FAIL(c, LR_ERR_UNSUPPORTED, "medium %u: a differentiable sigma_t gridvolume must have 1 channel (the per-channel gradient of an rgb sigma_t grid is not "
+                                               "implemented; the adjoint would silently return zeros).  Albedo grids may have 1 or 3 channels.", i);
+        }
         c->h_media[i].m = s->media[i]; c->h_media[i].max_density = 0.f;
         const lr_medium &m = s->media[i];
         if (m.kind == LR_MEDIUM_HETEROGENEOUS && (m.sigma_t_grid < 0 || (uint32_t) m.sigma_t_grid >= s->n_grids))

@@ -43,6 +43,27 @@ LR_DEV void grid_grad_scatter(const DGrid &g, const GridTap &tap, float gval, bo
     }
 }
 
+// Gradient w.r.t. an ALBEDO grid: sigma_s = sigma_t * albedo (heterogeneous.cpp:189-195), so at a real scatter
+// d weight_c / d albedo_c = A_c * sigma_t_c / scatter_prob (prbvolpath.py:202-204 back-propagated through mei.sigma_s).
+// `gv`: per channel dL * (L / weight) * d weight / d albedo.  1- or 3-channel grid; real scatters are ~1/10 of the tentative collisions, so
+// the 8 x ch atomics are issued directly.
+LR_DEV void albedo_grad_scatter(const DScene &sc, const DMedium &m, V3 p, V3 gv) {
+    if (m.m.albedo_grid < 0) return;
+    const DGrid &g = sc.grids[m.m.albedo_grid];
+    if (!g.differentiable || (gv.x == 0.f && gv.y == 0.f && gv.z == 0.f)) return;
+    GridTap tap; (void) grid_eval<true>(g, p, &tap);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        if (tap.w[k] == 0.f) continue;
+        if (g.ch == 1) atomicAdd(g.grad + tap.idx[k], (gv.x + gv.y + gv.z) * tap.w[k]);
+        else { float *d = g.grad + (size_t) tap.idx[k] * 3; atomicAdd(d, gv.x * tap.w[k]); atomicAdd(d + 1, gv.y * tap.w[k]); atomicAdd(d + 2, gv.z * tap.w[k]); }
+    }
+}
+LR_DEV V3 albedo_grad_value(V3 dL, V3 L, V3 weight, V3 dweight_albedo) {
+    return mk3((dL.x * (L.x / fmaxf(1e-8f, weight.x))) * dweight_albedo.x, (dL.y * (L.y / fmaxf(1e-8f, weight.y))) * dweight_albedo.y,
+               (dL.z * (L.z / fmaxf(1e-8f, weight.z))) * dweight_albedo.z);
+}
+
 // PRBVolpathIntegrator.sample_emitter (:354-444).  ADJ: replay with adj_emitted / dL.
 template <bool ADJ>
 LR_DEV V3 sample_emitter_prb(const DScene &sc, const DTri *tris_gid, V3 ref_p, V3 ref_n, const SurfaceInteraction *ref_si, Sampler &smp,
@@ -152,6 +173,7 @@ LR_DEV LaneResult sample_prb(const DScene &sc, const DTri *tris_gid, Sampler &sm
             const DMedium &m = sc.media[mei.medium];
             V3 A = weight; weight *= mei.sigma_s / scatter_prob;
             dweight = A * medium_albedo(sc, m, mei.p) * (m.m.scale / scatter_prob);
+            if (!PRIMAL) albedo_grad_scatter(sc, m, mei.p, albedo_grad_value(dL, L, weight, A * mei.sigma_t / scatter_prob));
         }
         throughput *= weight;
         if (!PRIMAL) {

@@ -195,6 +195,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track(const __grid_const
                     weight *= (sigma_t * albedo) / scatter_prob; dweight = A * albedo * (m.m.scale / scatter_prob);
                     thr *= weight;
                     if (ADJ && hetero) wvp_scatter_main(sc, m, tap, dL, Lcur, weight, dweight);
+                    if (ADJ) albedo_grad_scatter(sc, m, pt, albedo_grad_value(dL, Lcur, weight, A * sigma_t / scatter_prob));
                 }
                 ray.o = pt; hit_t = hit_t - t_c; event = 1; break;
             }
@@ -316,7 +317,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track_dda(const __grid_c
                     const V3 A = weight; const V3 albedo = medium_albedo(sc, m, pt);
                     weight *= (sigma_t * albedo) / scatter_prob; dweight = A * albedo * (m.m.scale / scatter_prob);
                     thr *= weight;
-                    if (ADJ) wvp_scatter_main(sc, m, tap, dL, Lcur, weight, dweight);
+                    if (ADJ) { wvp_scatter_main(sc, m, tap, dL, Lcur, weight, dweight); albedo_grad_scatter(sc, m, pt, albedo_grad_value(dL, Lcur, weight, A * sigma_t / scatter_prob)); }
                     ray.o = pt; hit_t = hit_t - t; event = 1;
                 }
             }

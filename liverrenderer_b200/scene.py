@@ -107,6 +107,7 @@ class Scene:
         self.sensor = None; self.integrator = None
         self.spp = 4
         self._named = {k: v for k, v in d.items() if isinstance(v, dict)}
+        self._integrator_type = next((v.get("type") for v in self._named.values() if v.get("type") in ("path", "volpath", "prbvolpath")), "path")
         # first pass: named BSDFs / media so that {'type':'ref','id':...} resolves
         for name, v in self._named.items():
             t = v.get("type")
@@ -330,7 +331,8 @@ class Scene:
             if isinstance(val, dict) and val.get("type") == "gridvolume":
                 if t == "homogeneous":
                     raise RuntimeError("homogeneous medium: grid volumes are not supported, use 'heterogeneous'")
-                gi = self._add_grid(val, differentiable=(key == "sigma_t"))
+                # both grids are differentiable parameters of the medium (heterogeneous.cpp:177-186: "albedo", "sigma_t")
+                gi = self._add_grid(val, differentiable=(key == "sigma_t" or self._integrator_type == "prbvolpath"))
                 setattr(m, dst_grid, gi)
                 self.param_keys[f"{name}.{key}.data"] = gi
             elif isinstance(val, dict) and val.get("type") == "constvolume":

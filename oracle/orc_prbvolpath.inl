@@ -30,6 +30,24 @@ void grid_grad_add(const MediumInteraction &mei, double g) {
     }
 }
 
+/* gradient w.r.t. an ALBEDO grid value: sigma_s = sigma_t * albedo (heterogeneous.cpp:189-195), so at a real scatter
+   d weight_c / d albedo_c = A_c * sigma_t_c / scatter_prob (prbvolpath.py:202-204 back-propagated through `mei.sigma_s`).
+   `g`: per-channel dL * (L / weight) * d weight / d albedo. */
+void albedo_grad_add(const MediumInteraction &mei, V3 g) {
+    const Medium &m = sc.media[mei.medium];
+    if (m.m.albedo_grid < 0) return;
+    Grid &gr = const_cast<Grid &>(sc.grids[m.m.albedo_grid]);
+    if (!gr.differentiable) return;
+    float o[3]; uint32_t cidx[8]; float cw[8]; gr.eval(mei.p, o, cidx, cw);
+    for (int k = 0; k < 8; ++k)
+        for (uint32_t c = 0; c < 3; ++c) {
+            double v = (double) g[c] * (double) cw[k];
+            std::atomic_ref<double> a(gr.grad[(size_t) cidx[k] * gr.ch + (gr.ch == 1 ? 0 : c)]);
+            double old = a.load(std::memory_order_relaxed);
+            while (!a.compare_exchange_weak(old, old + v, std::memory_order_relaxed)) {}
+        }
+}
+
 /* PRBVolpathIntegrator.sample_emitter (:354-444).  adj != nullptr => adjoint
  * replay with adj_emitted = *adj and the lane's dL. */
 V3 sample_emitter_prb(const Interaction &ref, const SurfaceInteraction *ref_si, Sampler &smp, int medium, uint32_t channel,
@@ -108,6 +126,7 @@ LaneResult sample_prb(bool primal, Sampler &smp, Ray ray, V3 dL, V3 state_in) {
         bool active_medium = medium >= 0, active_surface = !active_medium;
         MediumInteraction mei; V3 weight(1.f); bool escaped_medium = false, act_null_scatter = false, act_medium_scatter = false;
         V3 dweight(0.f);      /* d weight_c / d grid value at mei.p */
+        V3 dweight_albedo(0.f); /* d weight_c / d albedo_c at mei.p (real scatters) */
         float scatter_prob = 1.f;
         if (active_medium) {
             const Medium &m = sc.media[medium];
@@ -147,6 +166,7 @@ LaneResult sample_prb(bool primal, Sampler &smp, Ray ray, V3 dL, V3 state_in) {
             V3 albedo = m.m.albedo_grid >= 0 ? sc.grids[m.m.albedo_grid].eval3(mei.p)
                                              : V3(m.m.albedo_const[0], m.m.albedo_const[1], m.m.albedo_const[2]);
             dweight = A * albedo * (m.m.scale / scatter_prob);
+            dweight_albedo = A * mei.sigma_t / scatter_prob;
         }
         throughput *= weight;
         if (!primal && (active_medium || escaped_medium) && (act_null_scatter || act_medium_scatter)) {
@@ -154,6 +174,11 @@ LaneResult sample_prb(bool primal, Sampler &smp, Ray ray, V3 dL, V3 state_in) {
             double g = 0.0;
             for (int c = 0; c < 3; ++c) g += (double) (dL[c] * (L[c] / std::max(1e-8f, weight[c]))) * (double) dweight[c];
             grid_grad_add(mei, g);
+            if (act_medium_scatter) {
+                V3 ga;
+                for (int c = 0; c < 3; ++c) ga[c] = (dL[c] * (L[c] / std::max(1e-8f, weight[c]))) * dweight_albedo[c];
+                albedo_grad_add(mei, ga);
+            }
         }
         Phase phase = act_medium_scatter ? phase_of(mei.medium) : Phase{LR_PHASE_ISOTROPIC, 0.f};
 

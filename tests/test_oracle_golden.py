@@ -100,3 +100,44 @@ def test_lane_split_equals_whole_render():
     o = orc.OracleScene(sc); whole = o.render(seed=5, spp=4)
     o.film_clear(); o.render_lanes(5, 4, 0, n // 2); o.render_lanes(5, 4, n // 2, n)
     assert np.allclose(o.film_develop(), whole, rtol=1e-5, atol=1e-7)
+
+
+def _albedo_grid_scene(res, spp, tracking="reference"):
+    """A scattering cube whose ALBEDO is an rgb gridvolume (heterogeneous.cpp:177-186 exposes `albedo` and `sigma_t` as differentiable)."""
+    rng = np.random.default_rng(4)
+    alb = (0.3 + 0.6 * rng.random((4, 4, 4, 3))).astype(np.float32); sig = (0.4 + 0.6 * rng.random((4, 4, 4, 1))).astype(np.float32)
+    T = mi.T
+    return {"type": "scene", "integrator": {"type": "prbvolpath", "max_depth": 6, "rr_depth": 64, "tracking": tracking},
+            "sensor": {"type": "perspective", "fov": 30.0, "near_clip": 0.01, "far_clip": 100.0,
+                       "to_world": T().look_at(origin=[0.3, 0.4, -4.0], target=[0, 0, 0], up=[0, 1, 0]),
+                       "sampler": {"type": "independent", "sample_count": spp},
+                       "film": {"type": "hdrfilm", "width": res, "height": res, "rfilter": {"type": "box"}, "pixel_format": "rgb"}},
+            "cube": {"type": "cube", "to_world": T().scale(0.5), "bsdf": {"type": "null"},
+                     "interior": {"type": "heterogeneous", "scale": 6.0,
+                                  "sigma_t": {"type": "gridvolume", "grid": sig, "max_value": 1.5, "to_world": T().translate([-0.5, -0.5, -0.5])},
+                                  "albedo": {"type": "gridvolume", "grid": alb, "to_world": T().translate([-0.5, -0.5, -0.5])}}},
+            "env": {"type": "constant", "radiance": {"type": "rgb", "value": [1, 1, 1]}}}
+
+
+def test_albedo_grid_gradient_against_finite_differences():
+    """d loss / d albedo-grid (d weight_c / d a_c = s * sigma_t / P_s; prbvolpath.py:202-204 through sigma_s = sigma_t * albedo).
+    The albedo never enters a sampling decision (roulette off), so for fixed PCG32 streams the image is a POLYNOMIAL of the albedo
+    values: central differences with the same seed carry no Monte-Carlo noise, only the O(eps^2) curvature term."""
+    res, spp = 12, 64
+    sc = mi.load_dict(_albedo_grid_scene(res, spp)); o = orc.OracleScene(sc)
+    ga = sc.param_keys["cube.interior_medium.albedo.data"]; assert sc.grids[ga].differentiable == 1 and sc.grids[ga].channels == 3
+    rng = np.random.default_rng(9); w = rng.random((res, res, 3)).astype(np.float32)
+    o.grid_grad_zero(ga); o.render_backward(w, seed=21, spp=spp); grad = o.grid_grad_read(ga).reshape(4, 4, 4, 3).astype(np.float64)
+    assert np.abs(grad).max() > 0
+    base = np.array(sc.grid_arrays[ga], dtype=np.float32)
+    def loss(a):
+        o.grid_update(ga, a); return float((o.render(seed=21, spp=spp).astype(np.float64) * w).sum())
+    eps = 2e-2
+    for c in range(3):                                               # a uniform shift of one channel
+        d = np.zeros_like(base); d[..., c] = eps
+        fd = (loss(base + d) - loss(base - d)) / (2 * eps)
+        assert abs(fd - grad[..., c].sum()) <= 2e-3 * abs(fd) + 1e-6, (c, fd, grad[..., c].sum())
+    d = np.zeros_like(base); d[1, 2, 1, 0] = eps                     # a single voxel
+    fd = (loss(base + d) - loss(base - d)) / (2 * eps)
+    assert abs(fd - grad[1, 2, 1, 0]) <= 5e-3 * abs(fd) + 1e-6, (fd, grad[1, 2, 1, 0])
+    o.grid_update(ga, base)

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define LR_API_VERSION 3
+#define LR_API_VERSION 4
 
 typedef enum lr_status {
     LR_OK                = 0,
@@ -46,7 +46,11 @@ typedef enum lr_status {
 typedef enum lr_integrator_kind {
     LR_INTEGRATOR_PATH       = 0,  /* src/integrators/path.cpp:95-349            */
     LR_INTEGRATOR_VOLPATH    = 1,  /* src/integrators/volpath.cpp:93-554         */
-    LR_INTEGRATOR_PRBVOLPATH = 2   /* src/python/python/ad/integrators/prbvolpath.py:96-444 */
+    LR_INTEGRATOR_PRBVOLPATH = 2,  /* src/python/python/ad/integrators/prbvolpath.py:96-444 */
+    LR_INTEGRATOR_BIOVOLPATH = 3   /* the fork's src/integrators/biovolpath.cpp:95-551: volpath with the tissue media below
+                                      (accumulated tissue depth, one-hot channel transmittance); needs every medium of the
+                                      scene to be one of the tissue kinds, as the base Medium's five-argument
+                                      sample_interaction throws (src/render/medium.cpp:84-90) */
 } lr_integrator_kind;
 
 typedef enum lr_tracking_mode {
@@ -83,7 +87,12 @@ typedef enum lr_sampler_kind {
 
 typedef enum lr_medium_kind {
     LR_MEDIUM_HOMOGENEOUS   = 0,  /* src/media/homogeneous.cpp:137-181         */
-    LR_MEDIUM_HETEROGENEOUS = 1   /* src/media/heterogeneous.cpp:155-201       */
+    LR_MEDIUM_HETEROGENEOUS = 1,  /* src/media/heterogeneous.cpp:155-201       */
+    /* the fork's tissue media (biovolpath only): per-element exponential free paths drawn from an inner PCG32
+       seeded with the bit pattern of the integrator's sample */
+    LR_MEDIUM_LIVER         = 2,  /* src/media/liver.cpp:133-574: capsule layers by tissue depth, parenchyma below   */
+    LR_MEDIUM_GLISSON       = 3,  /* src/media/glissonCapsule.cpp:134-414: capsule layers only                      */
+    LR_MEDIUM_PARENCHYMA    = 4   /* src/media/parenchyma.cpp:134-393: parenchyma elements only, hard-coded sigma_t  */
 } lr_medium_kind;
 
 typedef enum lr_emitter_kind {
@@ -201,6 +210,16 @@ typedef struct lr_medium {
     float    albedo_const[3];
     uint32_t sample_emitters;       /* default 1 (src/render/medium.cpp:31)     */
     uint32_t has_spectral_extinction; /* default 1 (heterogeneous.cpp:161)      */
+    /* tissue media only (ignored for the other kinds).  Values AS THE PLUGIN STORES THEM: the constructors read the
+       "_B" property into the G slot and "_G" into B for every collagen layer and for elastin layers 1-2
+       (liver.cpp:149-150,...,174-175; glissonCapsule.cpp the same) -- the host loader reproduces that swap.
+       sigma_t_const / albedo_const / scale above keep their meaning (constant volumes only; parenchyma ignores
+       them, parenchyma.cpp:164,182-183). */
+    float    layer_limit[4];        /* layer1Limit..layer4Limit (liver.cpp:144-147)                      */
+    float    sigma_collagen[4][3];  /* m_sigma_collagen_layer1..4                                        */
+    float    sigma_elastin[4][3];   /* m_sigma_elastin_layer1..4                                         */
+    float    sigma_blood[3], sigma_bile[3], sigma_lipid_water[3];   /* constant volumes (liver.cpp:189-193) */
+    float    sigma_hepatocity;
 } lr_medium;
 
 typedef struct lr_emitter {
@@ -377,6 +396,11 @@ int  lr_kat_grid_eval(lr_ctx *ctx, uint32_t grid, const float *p, uint64_t n, fl
 int  lr_kat_emitter_sample(lr_ctx *ctx, const float *ref_p_u, uint64_t n, float *out);
 /* environment emitter of the scene: d[n][3] = direction of travel -> out[n][4] = radiance rgb, pdf_direction(d) */
 int  lr_kat_env_eval_pdf(lr_ctx *ctx, const float *d, uint64_t n, float *out);
+/* tissue media (liver.cpp:229-547 computeDistance + sample_interaction along the ray o = 0, d = +z):
+   in[n][5] = sample, tissue depth, maxt, channel (uint32 bits), active mask (uint32 bits) ->
+   out[n][8] = sampled distance, element type (bits: 0 absorber, 1 attenuator, 2 both), mei.t, mei.transmittance rgb,
+               sigma_t[channel], combined_extinction[channel]                                                        */
+int  lr_kat_tissue(lr_ctx *ctx, const lr_medium *medium, const float *in, uint64_t n, float *out);
 
 /* ---- control ------------------------------------------------------------ */
 int  lr_cancel(lr_ctx *ctx);                    /* async-signal-safe             */

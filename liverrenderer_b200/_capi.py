@@ -14,17 +14,17 @@ c_uint32_p = C.POINTER(C.c_uint32)
 
 # ---- enums (values mirror lr_api.h) -----------------------------------------
 LR_OK = 0
-LR_API_VERSION = 3
+LR_API_VERSION = 4
 LR_ERR = {-1: "invalid argument", -2: "no CUDA device (this backend has no CPU path)", -3: "CUDA error",
           -4: "unsupported plugin/option", -5: "no scene uploaded", -6: "cancelled", -7: "out of memory"}
 
-INTEGRATOR_PATH, INTEGRATOR_VOLPATH, INTEGRATOR_PRBVOLPATH = 0, 1, 2
+INTEGRATOR_PATH, INTEGRATOR_VOLPATH, INTEGRATOR_PRBVOLPATH, INTEGRATOR_BIOVOLPATH = 0, 1, 2, 3
 TRACKING_REFERENCE, TRACKING_DDA = 0, 1
 SAMPLER_INDEPENDENT, SAMPLER_LD = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHDIELECTRIC, BSDF_PRINCIPLED, BSDF_NULL, BSDF_DIELECTRIC = 0, 1, 2, 3, 4
 MF_BECKMANN, MF_GGX = 0, 1
 PHASE_ISOTROPIC, PHASE_HG = 0, 1
-MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS = 0, 1
+MEDIUM_HOMOGENEOUS, MEDIUM_HETEROGENEOUS, MEDIUM_LIVER, MEDIUM_GLISSON, MEDIUM_PARENCHYMA = 0, 1, 2, 3, 4
 EMITTER_AREA, EMITTER_CONSTANT, EMITTER_ENVMAP = 0, 1, 2
 RFILTER_BOX, RFILTER_GAUSSIAN, RFILTER_TENT = 0, 1, 2
 FILTER_NEAREST, FILTER_TRILINEAR = 0, 1
@@ -69,7 +69,11 @@ class lr_grid(C.Structure):
 class lr_medium(C.Structure):
     _fields_ = [("kind", C.c_uint32), ("phase", C.c_uint32), ("phase_g", C.c_float), ("scale", C.c_float),
                 ("sigma_t_grid", C.c_int32), ("albedo_grid", C.c_int32), ("sigma_t_const", C.c_float * 3),
-                ("albedo_const", C.c_float * 3), ("sample_emitters", C.c_uint32), ("has_spectral_extinction", C.c_uint32)]
+                ("albedo_const", C.c_float * 3), ("sample_emitters", C.c_uint32), ("has_spectral_extinction", C.c_uint32),
+                # tissue media (liver / glissonCapsule / parenchyma), values as the plugins store them
+                ("layer_limit", C.c_float * 4), ("sigma_collagen", (C.c_float * 3) * 4), ("sigma_elastin", (C.c_float * 3) * 4),
+                ("sigma_blood", C.c_float * 3), ("sigma_bile", C.c_float * 3), ("sigma_lipid_water", C.c_float * 3),
+                ("sigma_hepatocity", C.c_float)]
 
 
 class lr_emitter(C.Structure):
@@ -118,6 +122,7 @@ API_SYMBOLS = [
     "lr_grid_grad_device_ptr", "lr_grid_size", "lr_set_lane_map", "lr_ray_intersect", "lr_ray_intersect_noalloc", "lr_noalloc_max_rays", "lr_cancel", "lr_stats_get", "lr_set_stream",
     "lr_profile_enable", "lr_profile_get", "lr_stage_name",
     "lr_kat_bsdf_eval_pdf", "lr_kat_bsdf_sample", "lr_kat_phase", "lr_kat_grid_eval", "lr_kat_emitter_sample", "lr_kat_env_eval_pdf",
+    "lr_kat_tissue",
 ]
 
 _LIB = None
@@ -171,6 +176,7 @@ def load_library(path: str | None = None):
     lib.lr_kat_grid_eval.argtypes = [vp, C.c_uint32, vp, C.c_uint64, vp, C.c_int]; lib.lr_kat_grid_eval.restype = C.c_int
     lib.lr_kat_emitter_sample.argtypes = [vp, vp, C.c_uint64, vp]; lib.lr_kat_emitter_sample.restype = C.c_int
     lib.lr_kat_env_eval_pdf.argtypes = [vp, vp, C.c_uint64, vp]; lib.lr_kat_env_eval_pdf.restype = C.c_int
+    lib.lr_kat_tissue.argtypes = [vp, C.POINTER(lr_medium), vp, C.c_uint64, vp]; lib.lr_kat_tissue.restype = C.c_int
     if path is None:
         _LIB = lib
     return lib

@@ -43,6 +43,17 @@ def _ptr(a, n: int, what: str, convert: bool = False):
     raise TypeError(f"{what}: expected a numpy array or a torch tensor, got {type(a).__name__}")
 
 
+def tissue_probe_input(sample, depth, maxt, channel, active=None):
+    """in[n][5] of lr_kat_tissue / orc_kat_tissue: sample, tissue depth, maxt as floats; channel, active mask as uint32 bit patterns."""
+    sample = np.asarray(sample, dtype=np.float32).reshape(-1); n = sample.shape[0]
+    a = np.empty((n, 5), dtype=np.float32)
+    a[:, 0] = sample; a[:, 1] = np.broadcast_to(np.asarray(depth, dtype=np.float32), (n,)); a[:, 2] = np.broadcast_to(np.asarray(maxt, dtype=np.float32), (n,))
+    a[:, 3] = np.broadcast_to(np.asarray(channel, dtype=np.uint32), (n,)).view(np.float32) if np.ndim(channel) else np.full(n, channel, np.uint32).view(np.float32)
+    act = np.ones(n, np.uint32) if active is None else np.broadcast_to(np.asarray(active, dtype=np.uint32), (n,)).copy()
+    a[:, 4] = act.view(np.float32)
+    return np.ascontiguousarray(a)
+
+
 class Context:
     def __init__(self, device: int = 0, lib_path: str | None = None):
         self.lib = K.load_library(lib_path)
@@ -212,6 +223,12 @@ class Context:
         d = self._f32(d, 3); out = np.empty((d.shape[0], 4), dtype=np.float32)
         self._chk(self.lib.lr_kat_env_eval_pdf(self.ctx, C.c_void_p(d.ctypes.data), d.shape[0], C.c_void_p(out.ctypes.data)), "lr_kat_env_eval_pdf")
         return out[:, :3], out[:, 3]
+
+    def kat_tissue(self, medium, sample, depth, maxt, channel, active=None):
+        """Tissue media probe: (distance, element type, mei.t, transmittance, sigma_t[ch], combined_extinction[ch]) per query."""
+        a = tissue_probe_input(sample, depth, maxt, channel, active); out = np.empty((a.shape[0], 8), dtype=np.float32)
+        self._chk(self.lib.lr_kat_tissue(self.ctx, C.byref(medium), C.c_void_p(a.ctypes.data), a.shape[0], C.c_void_p(out.ctypes.data)), "lr_kat_tissue")
+        return out
 
     def cancel(self):
         self.lib.lr_cancel(self.ctx)

@@ -72,7 +72,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     if (s->api_version != LR_API_VERSION) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_scene_upload: api_version %u != %u", s->api_version, LR_API_VERSION);
     if (s->n_bsdfs > LR_MAX_BSDFS || s->n_media > LR_MAX_MEDIA || s->n_grids > LR_MAX_GRIDS || s->n_emitters > LR_MAX_EMITTERS)
         LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: too many bsdfs/media/grids/emitters");
-    if (s->integrator.kind > LR_INTEGRATOR_PRBVOLPATH) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: unknown integrator kind %u", s->integrator.kind);
+    if (s->integrator.kind > LR_INTEGRATOR_BIOVOLPATH) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: unknown integrator kind %u", s->integrator.kind);
     LR_CUDA(c, cudaSetDevice(c->device));
     c->free_scene();
     DScene &sc = c->sc; memset(&sc, 0, sizeof sc);
@@ -205,6 +205,15 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
         }
         c->h_media[i].m = s->media[i]; c->h_media[i].max_density = 0.f;
         const lr_medium &m = s->media[i];
+        if (m.kind > LR_MEDIUM_PARENCHYMA) LR_FAIL(c, LR_ERR_UNSUPPORTED, "medium %u: unknown medium kind %u", i, m.kind);
+        // the tissue media only implement the five-argument sample_interaction biovolpath calls, and the base class's version of
+        // that overload throws (src/render/medium.cpp:84-90): the two always come together
+        const bool tissue = m.kind >= LR_MEDIUM_LIVER, bio = s->integrator.kind == LR_INTEGRATOR_BIOVOLPATH;
+        if (tissue != bio)
+            LR_FAIL(c, LR_ERR_UNSUPPORTED, "medium %u: %s", i, bio ? "biovolpath needs liver / glissonCapsule / parenchyma media (Medium::sample_interaction with a tissue depth is "
+                                                                     "not implemented by the other media)"
+                                                                   : "liver / glissonCapsule / parenchyma media are only sampled by biovolpath");
+        if (tissue && (m.sigma_t_grid >= 0 || m.albedo_grid >= 0)) LR_FAIL(c, LR_ERR_UNSUPPORTED, "medium %u: tissue media take constant sigma_t / albedo only", i);
         if (m.kind == LR_MEDIUM_HETEROGENEOUS && (m.sigma_t_grid < 0 || (uint32_t) m.sigma_t_grid >= s->n_grids))
             LR_FAIL(c, LR_ERR_INVALID_ARG, "medium %u: heterogeneous medium needs a sigma_t grid", i);
         if (m.kind == LR_MEDIUM_HETEROGENEOUS) sc.prb_handle_null = 1; else sc.prb_nee_homogeneous = 1;

@@ -46,6 +46,19 @@ __global__ void k_kat_env_eval_pdf(const __grid_constant__ DScene sc, const floa
     out[4 * i] = e.x; out[4 * i + 1] = e.y; out[4 * i + 2] = e.z; out[4 * i + 3] = pdf;
 }
 
+// tissue media probe (lr_biovolpath.cuh): in[n][5] = sample, tissue depth, maxt, channel (bits), active (bits) ->
+// out[n][8] = distance, element type (bits), mei.t, transmittance(3), sigma_t[channel], combined_extinction[channel]; ray o = 0, d = +z
+__global__ void k_kat_tissue(const lr_medium *m, const float *in, uint64_t n, float *out) {
+    uint64_t i = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; if (i >= n) return;
+    const float *q = in + 5 * i; float *o = out + 8 * i; const uint32_t ch = __float_as_uint(q[3]);
+    Ray ray; ray.o = mk3(0.f); ray.d = mk3(0.f, 0.f, 1.f); ray.maxt = LR_INF;
+    int bt; o[0] = bio_compute_distance(*m, ch, q[0], q[1], bt); o[1] = __uint_as_float((uint32_t) bt);
+    uint32_t cnt = 0;
+    BioInteraction mei = bio_sample_interaction(*m, ray, q[2], q[0], ch, q[1], __float_as_uint(q[4]) != 0u, cnt);
+    o[2] = mei.t; o[3] = mei.transmittance.x; o[4] = mei.transmittance.y; o[5] = mei.transmittance.z;
+    o[6] = mei.sigma_t_ch; o[7] = idx3(mei.combined_extinction, ch);
+}
+
 // host -> device staging of the probe arrays; `outs` floats come back into `out`
 struct KatIO {
     lr_ctx *c; std::vector<DevBuf *> bufs;
@@ -109,6 +122,15 @@ int lr_kat_emitter_sample(lr_ctx *c, const float *ref_p_u, uint64_t n, float *ou
     if (!din || !dout) LR_FAIL(c, LR_ERR_OOM, "lr_kat_emitter_sample: device allocation failed");
     k_kat_emitter_sample<<<blocks, 128, 0, c->stream>>>(c->sc, din, n, dout);
     LR_KAT_END(dout, 7)
+}
+int lr_kat_tissue(lr_ctx *c, const lr_medium *m, const float *in, uint64_t n, float *out) {
+    LR_KAT_BEGIN("lr_kat_tissue", false)
+    if (!m || !in || !out) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_kat_tissue: NULL argument");
+    if (m->kind < LR_MEDIUM_LIVER || m->kind > LR_MEDIUM_PARENCHYMA) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_kat_tissue: not a tissue medium");
+    const lr_medium *dm = io.in(m, 1); const float *din = io.in(in, n * 5); float *dout = io.out(n * 8);
+    if (!dm || !din || !dout) LR_FAIL(c, LR_ERR_OOM, "lr_kat_tissue: device allocation failed");
+    k_kat_tissue<<<blocks, 128, 0, c->stream>>>(dm, din, n, dout);
+    LR_KAT_END(dout, 8)
 }
 int lr_kat_env_eval_pdf(lr_ctx *c, const float *d, uint64_t n, float *out) {
     LR_KAT_BEGIN("lr_kat_env_eval_pdf", true)

@@ -2,6 +2,7 @@
 #pragma once
 #include "lr_integrators.cuh"
 #include "lr_prb.cuh"
+#include "lr_biovolpath.cuh"
 
 namespace lr {
 
@@ -132,6 +133,7 @@ template <int KIND>
 LR_DEV LaneResult run_lane(const DScene &sc, const DTri *tris_gid, LaneSetup &L, Counters &cnt) {
     if (KIND == LR_INTEGRATOR_PATH) return sample_path(sc, tris_gid, L.smp, L.ray, cnt);
     if (KIND == LR_INTEGRATOR_VOLPATH) return sample_volpath(sc, tris_gid, L.smp, L.ray, sc.sensor.medium, cnt);
+    if (KIND == LR_INTEGRATOR_BIOVOLPATH) return sample_biovolpath(sc, tris_gid, L.smp, L.ray, sc.sensor.medium, cnt);
     return sample_prb<true>(sc, tris_gid, L.smp, L.ray, mk3(0.f), mk3(0.f), cnt);
 }
 

@@ -18,6 +18,9 @@ from .volume_io import read_vol
 from .image_io import read_texture, texture_from_pixels
 
 
+_TISSUE_MEDIA = {"liver": K.MEDIUM_LIVER, "glissonCapsule": K.MEDIUM_GLISSON, "parenchyma": K.MEDIUM_PARENCHYMA}
+
+
 def _rgb(v, default=None):
     if v is None:
         v = default
@@ -107,7 +110,7 @@ class Scene:
         self.sensor = None; self.integrator = None
         self.spp = 4
         self._named = {k: v for k, v in d.items() if isinstance(v, dict)}
-        self._integrator_type = next((v.get("type") for v in self._named.values() if v.get("type") in ("path", "volpath", "prbvolpath")), "path")
+        self._integrator_type = next((v.get("type") for v in self._named.values() if v.get("type") in ("path", "volpath", "prbvolpath", "biovolpath")), "path")
         # first pass: named BSDFs / media so that {'type':'ref','id':...} resolves
         for name, v in self._named.items():
             t = v.get("type")
@@ -115,6 +118,8 @@ class Scene:
                 self._bsdf_ids[name] = self._add_bsdf(v)
             elif t in ("homogeneous", "heterogeneous"):
                 self._medium_ids[name] = self._add_medium(v, name)
+            elif t in _TISSUE_MEDIA:
+                self._medium_ids[name] = self._add_tissue_medium(v, name)
         for name, v in self._named.items():
             t = v.get("type")
             if t in ("rectangle", "cube", "obj", "sphere", "mesh"):
@@ -123,18 +128,19 @@ class Scene:
                 self._add_env(v)
             elif t == "perspective":
                 self._sensor_dict = v
-            elif t in ("path", "volpath", "prbvolpath"):
+            elif t in ("path", "volpath", "prbvolpath", "biovolpath"):
                 self._integrator_dict = v
-            elif t in ("biovolpath", "biovolpath06", "volpathmis", "direct", "aov", "moment", "ptracer", "stokes", "depth",
+            elif t in ("biovolpath06", "volpathmis", "direct", "aov", "moment", "ptracer", "stokes", "depth",
                        "prb", "prbvolpath_basic", "direct_projective", "prb_projective"):
-                raise NotImplementedError(f"integrator plugin '{t}' is outside the hot path (path, volpath, prbvolpath)")
-            elif t in ("diffuse", "roughdielectric", "principled", "null", "dielectric", "bumpmap", "homogeneous", "heterogeneous"):
+                raise NotImplementedError(f"integrator plugin '{t}' is outside the hot path (path, volpath, prbvolpath, biovolpath)")
+            elif t in ("diffuse", "roughdielectric", "principled", "null", "dielectric", "bumpmap", "homogeneous", "heterogeneous") or t in _TISSUE_MEDIA:
                 pass                                  # named BSDFs / media: handled by the first pass
             else:
                 # anything else would silently vanish from the render (a `point` emitter, a `ply` shape, a `plastic` BSDF ...)
                 raise NotImplementedError(f"plugin '{t}' (object '{name}') is outside the hot path; supported top-level plugins: "
-                                          "perspective, path/volpath/prbvolpath, rectangle/cube/sphere/obj/mesh, constant/envmap, "
-                                          "diffuse/roughdielectric/principled/null/dielectric/bumpmap, homogeneous/heterogeneous")
+                                          "perspective, path/volpath/prbvolpath/biovolpath, rectangle/cube/sphere/obj/mesh, constant/envmap, "
+                                          "diffuse/roughdielectric/principled/null/dielectric/bumpmap, homogeneous/heterogeneous, "
+                                          "liver/glissonCapsule/parenchyma")
         if not hasattr(self, "_sensor_dict"):
             raise ValueError("scene has no 'perspective' sensor")
         self._build_sensor(self._sensor_dict)
@@ -347,11 +353,54 @@ class Scene:
         self.media.append(m)
         return len(self.media) - 1
 
+    def _add_tissue_medium(self, v, name="medium"):
+        """The fork's tissue media: liver.cpp:139-201, glissonCapsule.cpp:138-186, parenchyma.cpp:139-152.  The POD carries the
+        values as the constructors store them, including their property-name mix-up: G is read from "..._B" and B from
+        "..._G" for every collagen layer and for elastin layers 1 and 2 (liver.cpp:149-150 ... 174-175)."""
+        m = K.lr_medium(); t = v["type"]
+        m.kind = _TISSUE_MEDIA[t]
+        m.scale = _flt(v.get("scale"), 1.0)
+        m.sample_emitters = 1 if v.get("sample_emitters", t != "parenchyma") else 0          # unused by biovolpath
+        m.has_spectral_extinction = 1 if v.get("has_spectral_extinction", t != "parenchyma") else 0   # parenchyma.cpp:150
+        ph = v.get("phase", {"type": "isotropic"})
+        if ph["type"] == "isotropic":
+            m.phase = K.PHASE_ISOTROPIC
+        elif ph["type"] == "hg":
+            m.phase = K.PHASE_HG; m.phase_g = _flt(ph.get("g"), 0.8)
+        else:
+            raise NotImplementedError(f"phase function '{ph['type']}' is outside the hot path")
+        m.sigma_t_grid = -1; m.albedo_grid = -1
+        for key, default in (("sigma_t", 1.0), ("albedo", 0.75)):
+            val = v.get(key, default)
+            if isinstance(val, dict):
+                if val.get("type") != "constvolume":
+                    raise NotImplementedError(f"{t} medium: '{key}' must be constant (the fork's scenes use none)")
+                val = val.get("value")
+            setattr(m, key + "_const", _f3(_rgb(val, default)))
+        lim = [_flt(v.get(f"layer{i}Limit"), d) for i, d in zip((1, 2, 3, 4), (0.0065, 0.0072, 0.0083, 0.01))]
+        m.layer_limit = (C.c_float * 4)(*lim)
+        for L in range(4):
+            for arr, nm, swapped in ((m.sigma_collagen, "collagen", True), (m.sigma_elastin, "elastin", L < 2)):
+                r = _flt(v.get(f"sigma_{nm}{L + 1}_R"), 1.0); g = _flt(v.get(f"sigma_{nm}{L + 1}_G"), 1.0); b = _flt(v.get(f"sigma_{nm}{L + 1}_B"), 1.0)
+                arr[L][0], arr[L][1], arr[L][2] = (r, b, g) if swapped else (r, g, b)
+        for key in ("sigma_blood", "sigma_bile", "sigma_lipid_water"):
+            val = v.get(key, 1.0)
+            if isinstance(val, dict):
+                if val.get("type") not in ("constvolume", "rgb"):
+                    raise NotImplementedError(f"{t} medium: '{key}' must be constant")
+                val = val.get("value")
+            setattr(m, key, _f3(_rgb(val, 1.0)))
+        m.sigma_hepatocity = _flt(v.get("sigma_hepatocity"), 1.0)
+        self.media.append(m)
+        return len(self.media) - 1
+
     def _resolve_medium(self, v, name):
         if v is None:
             return -1
         if v.get("type") == "ref":
             return self._medium_ids[v["id"]]
+        if v.get("type") in _TISSUE_MEDIA:
+            return self._add_tissue_medium(v, name)
         return self._add_medium(v, name)
 
     # ---- shapes ---------------------------------------------------------------
@@ -459,7 +508,8 @@ class Scene:
 
     def _build_integrator(self, v):
         i = K.lr_integrator()
-        i.kind = {"path": K.INTEGRATOR_PATH, "volpath": K.INTEGRATOR_VOLPATH, "prbvolpath": K.INTEGRATOR_PRBVOLPATH}[v["type"]]
+        i.kind = {"path": K.INTEGRATOR_PATH, "volpath": K.INTEGRATOR_VOLPATH, "prbvolpath": K.INTEGRATOR_PRBVOLPATH,
+                  "biovolpath": K.INTEGRATOR_BIOVOLPATH}[v["type"]]
         md = int(v.get("max_depth", 6 if v["type"] == "prbvolpath" else -1))
         if md < 0 and md != -1:
             raise RuntimeError('"max_depth" must be set to -1 (infinite) or a value >= 0')

@@ -167,3 +167,56 @@ def sphere_liver_inverse(res: int = 512, spp: int = 64, grid_res: int = 128, den
                        "film": {"type": "hdrfilm", "width": res, "height": res, "rfilter": {"type": "box"},
                                 "pixel_format": "rgb", "component_format": "float32"}},
             "sphere": sphere, "floor": floor, "env": {"type": "constant", "radiance": {"type": "rgb", "value": [1, 1, 1]}}}
+
+
+# ---- the fork's own scenes: biovolpath + tissue media ------------------------------------------------
+# property values of scenes/Liver-SingleMesh/mitsuba3/scene.xml:51-82 (the MultiMesh file carries the same numbers, :53-89)
+_CAPSULE_PROPS = {
+    "sigma_collagen1_R": 3.146124563777685, "sigma_collagen1_G": 2.2189004838302524, "sigma_collagen1_B": 1.5741115169422308,
+    "sigma_collagen2_R": 2.6853117983771604, "sigma_collagen2_G": 1.8938982001080131, "sigma_collagen2_B": 1.3435514528168673,
+    "sigma_collagen3_R": 0.0033151997510829138, "sigma_collagen3_G": 0.002338145926059276, "sigma_collagen3_B": 0.0016587054973047745,
+    "sigma_collagen4_R": 0.023206398257580394, "sigma_collagen4_G": 0.01636702148241493, "sigma_collagen4_B": 0.01161093848113342,
+    "sigma_elastin1_R": 0.1062817070956702, "sigma_elastin1_G": 0.29006947548901363, "sigma_elastin1_B": 0.7164288436612656,
+    "sigma_elastin2_R": 0.3938675027663073, "sigma_elastin2_G": 1.074963350341639, "sigma_elastin2_B": 2.6550010088623375,
+    "sigma_elastin3_R": 0.5293245804372595, "sigma_elastin3_G": 1.4446597406707737, "sigma_elastin3_B": 3.5680965939208136,
+    "sigma_elastin4_R": 0.18130408857496683, "sigma_elastin4_G": 0.49482439936361144, "sigma_elastin4_B": 1.2221433215398063,
+}
+_PARENCHYMA_PROPS = {
+    "sigma_blood": {"type": "rgb", "value": [0.004611074674964207, 0.20900034649954347, 0.24625187839886722]},
+    "sigma_bile": {"type": "rgb", "value": [0.002160333333333333, 0.0030312499999999997, 0.025356499999999997]},
+    "sigma_hepatocity": 269.26180490217416,
+    "sigma_lipid_water": {"type": "rgb", "value": [0.004632281950333333, 0.00048109802439999993, 0.00106273247395]},
+}
+
+
+def _bump_dielectric():
+    return {"type": "bumpmap", "scale": 0.005, "texture": {"type": "bitmap", "bitmap": tissue_texture(), "raw": True},
+            "bsdf": {"type": "dielectric", "int_ior": 1.38, "ext_ior": 1.0}}
+
+
+def liver_single_mesh_bio(res: int = 1080, spp: int = 256, max_depth: int = 12, sampler: str = "independent"):
+    """Liver-SingleMesh as the fork ships it (scenes/Liver-SingleMesh/mitsuba3/scene.xml): `biovolpath`, one `liver` medium
+    inside the bump-mapped dielectric organ, the cavity environment map.  Mesh, bump texture and environment map are this
+    repository's synthetic stand-ins (the fork's assets are not redistributable here)."""
+    mesh = _liver_mesh("liver2"); mesh["to_world"] = _LIVER_T
+    mesh["bsdf"] = _bump_dielectric()
+    mesh["interior"] = {"type": "liver", "scale": 1.0, "phase": {"type": "isotropic"}, **_CAPSULE_PROPS, **_PARENCHYMA_PROPS}
+    sensor = _liver_sensor(res, spp); sensor["sampler"]["type"] = sampler
+    return {"type": "scene", "integrator": {"type": "biovolpath", "max_depth": max_depth, "rr_depth": 5},
+            "sensor": sensor, "liver": mesh, "env": _liver_env()}
+
+
+def liver_multi_mesh_bio(res: int = 1080, spp: int = 256, max_depth: int = 12, sampler: str = "ldsampler"):
+    """Liver-MultiMesh as its (partly commented-out) scene file lays it out: the capsule shell `liver1` filled with the
+    `glissonCapsule` medium around the `liver2` organ filled with `parenchyma` (scene.xml:53-110), `ldsampler` (:18)."""
+    outer = _liver_mesh("liver1"); outer["to_world"] = T().translate([-5.05, 5.05, -5.05]).scale(1.05)
+    inner = _liver_mesh("liver2"); inner["to_world"] = _LIVER_T
+    outer["bsdf"] = _bump_dielectric(); outer["interior"] = {"type": "ref", "id": "capsule"}
+    inner["bsdf"] = {"type": "dielectric", "int_ior": 1.38, "ext_ior": 1.0}
+    inner["interior"] = {"type": "ref", "id": "parenchyma"}; inner["exterior"] = {"type": "ref", "id": "capsule"}
+    sensor = _liver_sensor(res, spp); sensor["sampler"]["type"] = sampler
+    return {"type": "scene", "integrator": {"type": "biovolpath", "max_depth": max_depth, "rr_depth": 5},
+            "sensor": sensor,
+            "capsule": {"type": "glissonCapsule", "scale": 1.0, "phase": {"type": "isotropic"}, **_CAPSULE_PROPS},
+            "parenchyma": {"type": "parenchyma", "scale": 1.0, "phase": {"type": "isotropic"}, **_PARENCHYMA_PROPS},
+            "outer": outer, "inner": inner, "env": _liver_env()}

@@ -129,6 +129,7 @@ static LaneResult run_lane(Integrator &in, LaneSetup &L) {
     switch (sc.integ.kind) {
         case LR_INTEGRATOR_PATH: return in.sample_path(L.smp, L.ray);
         case LR_INTEGRATOR_VOLPATH: return in.sample_volpath(L.smp, L.ray, sc.sensor.medium);
+        case LR_INTEGRATOR_BIOVOLPATH: return in.sample_biovolpath(L.smp, L.ray, sc.sensor.medium);
         default: return in.sample_prb(true, L.smp, L.ray, V3(0.f), V3(0.f));
     }
 }
@@ -315,6 +316,24 @@ float orc_kat_env_pdf(void *h, const float *d) {
 float orc_kat_erfinv(float x) { return erfinv_(x); }
 
 /* generic probe with the same function ids as oracle/_ref/libref_kat.so (the reference's own headers): kat_fn.h */
+/* tissue media probe: in[n][5] = sample, tissue depth, maxt, channel (bits), active (bits);
+   out[n][8] = distance, element type (bits), mei.t, transmittance(3), sigma_t[channel], combined_extinction[channel].
+   Ray: o = 0, d = +z.  Same layout as the backend's lr_kat_tissue. */
+int orc_kat_tissue(const lr_medium *m, const float *in, uint64_t n, float *out) {
+    auto bits = [](float f) { uint32_t u; memcpy(&u, &f, 4); return u; };
+    auto fbits = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };
+    Scene sc; Medium md; md.m = *m; sc.media.push_back(md); Integrator integ(sc);
+    Ray ray; ray.o = V3(0.f); ray.d = V3(0.f, 0.f, 1.f); ray.maxt = Inf;
+    for (uint64_t i = 0; i < n; ++i) {
+        const float *q = in + 5 * i; float *o = out + 8 * i; uint32_t ch = bits(q[3]);
+        int bt; o[0] = Integrator::bio_compute_distance(*m, ch, q[0], q[1], bt); o[1] = fbits((uint32_t) bt);
+        auto mei = integ.bio_sample_interaction(0, ray, q[2], q[0], ch, q[1], bits(q[4]) != 0);
+        o[2] = mei.t; o[3] = mei.transmittance.x; o[4] = mei.transmittance.y; o[5] = mei.transmittance.z;
+        o[6] = index_spectrum(mei.sigma_t, ch); o[7] = index_spectrum(mei.combined_extinction, ch);
+    }
+    return 0;
+}
+
 int orc_kat_fn(int fn, const float *in, float *out) {
     auto bits = [](float f) { uint32_t u; memcpy(&u, &f, 4); return u; };
     auto fbits = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };

@@ -109,7 +109,7 @@ struct Integrator {
 
     /* ===================== medium helpers ===================== */
     struct MediumInteraction : Interaction {
-        V3 wi, sigma_s, sigma_n, sigma_t, combined_extinction; float mint = 0.f; int medium = -1;
+        V3 wi, sigma_s, sigma_n, sigma_t, combined_extinction, transmittance; float mint = 0.f; int medium = -1;
         uint32_t cidx[8]; float cw[8]; float grid_val = 0.f;   /* trilinear footprint (adjoint) */
         Ray spawn_ray_m(V3 d) const { return {p, d, Largest}; }  /* n = 0 => no offset (interaction.h:165-169) */
     };
@@ -175,6 +175,7 @@ struct Integrator {
 
 #include "orc_volpath.inl"
 #include "orc_prbvolpath.inl"
+#include "orc_biovolpath.inl"
 };
 
 } // namespace orc

@@ -88,6 +88,7 @@ def _bind(L):
     L.orc_kat_env_eval.argtypes = [vp, vp, vp]; L.orc_kat_env_sample.argtypes = [vp, vp, C.c_float, C.c_float, vp]
     L.orc_kat_env_pdf.argtypes = [vp, vp]; L.orc_kat_env_pdf.restype = C.c_float
     L.orc_kat_erfinv.argtypes = [C.c_float]; L.orc_kat_erfinv.restype = C.c_float
+    L.orc_kat_tissue.argtypes = [C.POINTER(K.lr_medium), vp, C.c_uint64, vp]
     return L
 
 
@@ -109,6 +110,14 @@ def bump_frame(bsdf, tex, n, sh_n, sh_s, dp_du, dp_dv, wi, uv):
     """BumpMap::frame for a synthetic interaction -> rows n, s, t of the perturbed frame."""
     si = np.concatenate([n, sh_n, sh_s, dp_du, dp_dv, wi, uv]).astype(np.float32); out = np.empty(9, dtype=np.float32)
     lib().orc_kat_bump_frame(C.byref(bsdf), C.byref(tex), _p(si), _p(out)); return out.reshape(3, 3)
+
+
+def tissue_probe(medium, sample, depth, maxt, channel, active=None):
+    """orc_kat_tissue: same in/out layout as Backend.kat_tissue."""
+    from liverrenderer_b200.backend import tissue_probe_input
+    a = tissue_probe_input(sample, depth, maxt, channel, active); out = np.empty((a.shape[0], 8), dtype=np.float32)
+    lib().orc_kat_tissue(C.byref(medium), _p(a), a.shape[0], _p(out))
+    return out
 
 
 class OracleScene:

@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 24
     for n in names:
         assert hasattr(lib, n), f"liblr_b200.so does not export {n}"
-    assert lib.lr_api_version() == K.LR_API_VERSION == 3
+    assert lib.lr_api_version() == K.LR_API_VERSION == 4
 
 
 def test_no_torch_or_cxx_types_in_header():

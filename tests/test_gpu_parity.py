@@ -26,7 +26,7 @@ def path_match_fraction(gpu, cpu, tol):
 
 def test_library_loaded_and_device():
     ctx = mi.Context(0)
-    assert ctx.lib.lr_api_version() == K.LR_API_VERSION == 3
+    assert ctx.lib.lr_api_version() == K.LR_API_VERSION == 4
 
 
 def test_no_scene_error():

@@ -1,0 +1,259 @@
+"""SURVEY.md 8(f) rank 2 -- the fork's tissue media (liver / glissonCapsule / parenchyma) and biovolpath: the oracle's
+restatement (oracle/orc_biovolpath.inl) against an independent numpy restatement of computeDistance and against the
+behaviours the source text pins down (layer selection, element types, one-hot transmittance, the G/B property mix-up),
+plus the host loader.  PARITY UNPINNED for this row: the fork's media do not compile against the vendored headers and the
+reference ships no test or golden image for them."""
+import os
+import textwrap
+
+import numpy as np
+import pytest
+
+from tests import orc
+from liverrenderer_b200 import _capi as K
+from liverrenderer_b200 import scenes
+from liverrenderer_b200.scene import Scene
+from liverrenderer_b200.xml_loader import load_file
+
+F = np.float32
+MASK64 = (1 << 64) - 1
+
+
+def _medium(kind="liver", **over):
+    d = {"type": kind, "phase": {"type": "isotropic"}, **scenes._CAPSULE_PROPS, **scenes._PARENCHYMA_PROPS}
+    d.update(over)
+    sc = Scene({"type": "scene", "integrator": {"type": "biovolpath"},
+                "sensor": {"type": "perspective", "film": {"type": "hdrfilm", "width": 4, "height": 4}},
+                "shape": {"type": "cube", "interior": d, "bsdf": {"type": "dielectric"}}, "env": {"type": "constant"}})
+    return sc.media[0]
+
+
+class _PCG32:
+    """dr::PCG32 (ext/drjit/include/drjit/random.h): seed(initstate, default stream), next_float32."""
+    MULT, INC = 0x5851f42d4c957f2d, ((0xda3e39cb94b95bdb << 1) | 1) & MASK64
+
+    def __init__(self, initstate):
+        self.state = 0; self.next_u32(); self.state = (self.state + initstate) & MASK64; self.next_u32()
+
+    def next_u32(self):
+        old = self.state; self.state = (old * self.MULT + self.INC) & MASK64
+        xs = (((old >> 18) ^ old) >> 27) & 0xffffffff; rot = old >> 59
+        return ((xs >> rot) | (xs << ((-rot) & 31))) & 0xffffffff
+
+    def next_f32(self):
+        return np.array([(self.next_u32() >> 9) | 0x3f800000], np.uint32).view(F)[0] - F(1)
+
+
+def _py_distance(m, channel, sample, depth):
+    """computeDistance (liver.cpp:229-481) written independently of the oracle: float32 numpy arithmetic, Python-int PCG32."""
+    rng = _PCG32(int(np.array([sample], F).view(np.uint32)[0]))
+    lim = [F(x) for x in m.layer_limit]; depth = F(depth)
+    layer = 4
+    if m.kind != K.MEDIUM_PARENCHYMA:
+        layer = 0
+        for i in range(4):
+            if depth <= lim[i]:
+                layer = i
+        if depth > lim[3]:
+            layer = 4
+    dist, elem = F(np.inf), 0
+    if layer < 4:
+        for i, arr in enumerate((m.sigma_collagen, m.sigma_elastin)):
+            r = rng.next_f32(); r = F(0.5) if r == 0 else r
+            aux = F(-(F(1) / F(arr[layer][channel]))) * np.log(r, dtype=F)
+            if i == 0 or aux < dist:
+                dist, elem = aux, i
+        return dist, 1
+    if m.kind == K.MEDIUM_GLISSON:
+        return dist, 1
+    for i in range(4):
+        r = rng.next_f32(); r = F(0.5) if r == 0 else r
+        att = F((m.sigma_blood, m.sigma_bile, m.sigma_lipid_water)[i][channel]) if i < 3 else F(m.sigma_hepatocity)
+        if att > 0:
+            aux = F(-(F(1) / att)) * np.log(r, dtype=F)
+            if i == 3:
+                aux = -(F(np.log2(att + F(1), dtype=F) * (F(1) / np.log2(F(10), dtype=F))) * np.log(r, dtype=F))
+            if i == 0 or aux < dist:
+                dist, elem = aux, i
+    return dist, (2 if elem == 3 else 0)
+
+
+@pytest.mark.parametrize("kind", ["liver", "glissonCapsule", "parenchyma"])
+def test_compute_distance_matches_independent_restatement(kind):
+    m = _medium(kind); rng = np.random.default_rng(3)
+    n = 600
+    sample = rng.random(n, dtype=F); depth = np.where(rng.random(n) < 0.5, rng.random(n) * 0.012, rng.random(n) * 2).astype(F)
+    channel = rng.integers(0, 3, n).astype(np.uint32)
+    out = orc.tissue_probe(m, sample, depth, np.full(n, np.inf, F), channel)
+    for i in range(n):
+        d, bt = _py_distance(m, int(channel[i]), sample[i], depth[i])
+        assert out[i, 1:2].view(np.uint32)[0] == bt, i
+        if np.isinf(d):
+            assert np.isinf(out[i, 0])
+        else:
+            assert abs(out[i, 0] - d) <= 4e-7 * abs(d), (i, out[i, 0], d)     # numpy's float32 log vs libm's: 1-2 ulp
+
+
+def test_layer_selection_later_assignment_wins():
+    """liver.cpp:248-253: the masked assignments are sequential, so every depth <= layer4Limit lands in layer 3 (index)."""
+    over = {}
+    for L in range(4):
+        for c in "RGB":
+            over[f"sigma_collagen{L + 1}_{c}"] = 10.0 ** L; over[f"sigma_elastin{L + 1}_{c}"] = 1e-9
+    m = _medium("liver", **over)
+    sample = np.linspace(0.05, 0.95, 64, dtype=F)
+    for depth in (0.0, 0.0065, 0.007, 0.008, 0.01):
+        out = orc.tissue_probe(m, sample, depth, np.inf, 0)
+        exp = np.array([_py_distance(m, 0, s, depth)[0] for s in sample], F)
+        np.testing.assert_allclose(out[:, 0], exp, rtol=4e-7)
+        # collagen of layer index 3 (sigma 1000) wins over elastin (1e-9): mean free path ~ 1e-3
+        assert out[:, 0].max() < 0.05
+    out = orc.tissue_probe(m, sample, 0.0101, np.inf, 0)                    # beyond layer4Limit: the parenchyma elements
+    assert set(out[:, 1].view(np.uint32)) <= {0, 2}
+
+
+def test_element_types_and_transmittance_liver():
+    m = _medium("liver"); rng = np.random.default_rng(5); n = 4000
+    sample = rng.random(n, dtype=F); ch = rng.integers(0, 3, n).astype(np.uint32)
+    # capsule layer (depth 0): attenuators only -> one-hot wherever the distance falls inside the segment
+    out = orc.tissue_probe(m, sample, 0.0, 0.5, ch)
+    inside = (out[:, 0] > 0) & (out[:, 0] < 0.5)
+    assert inside.any() and (~inside).any()
+    assert np.all(out[:, 1].view(np.uint32) == 1)
+    tr = out[:, 3:6]
+    assert np.all(tr[inside].sum(1) == 1) and np.all(tr[inside, ch[inside]] == 1)          # one-hot in the lane's channel
+    assert np.all(tr[~inside] == 1) and np.all(np.isinf(out[~inside, 2]))                  # boundary reached: t = inf, transmittance 1
+    assert np.all(out[inside, 2] == out[inside, 0])
+    # parenchyma depth: blood / bile / lipid absorb (transmittance 0), hepatocytes attenuate unless closer than 0.0025
+    out = orc.tissue_probe(m, sample, 1.0, np.inf, ch)
+    bt = out[:, 1].view(np.uint32); tr = out[:, 3:6]
+    assert set(bt) == {0, 2}
+    assert np.all(tr[bt == 0] == 0)
+    hep = bt == 2; near = hep & (out[:, 0].astype(np.float64) < 0.0025)
+    assert near.any() and np.all(tr[near] == 0)
+    far = hep & ~near
+    assert np.all(tr[far].sum(1) == 1) and np.all(tr[far, ch[far]] == 1)
+    # sigma_t & valid_mi, majorant & active (liver.cpp:206-217, :496-497)
+    assert np.all(out[:, 6] == 1) and np.all(out[:, 7] == 1)
+    dead = orc.tissue_probe(m, sample, 1.0, np.inf, ch, active=0)
+    assert np.all(dead[:, 6] == 0) and np.all(dead[:, 7] == 0)
+    # a dying lane (mask argument false): an attenuating hepatocyte hit no longer switches `active` on -> transmittance 0
+    assert np.all(dead[:, 3:6][far] == 0)
+    cap = orc.tissue_probe(m, sample, 0.0, 0.5, ch, active=0)                                # EAttenuator sets active = true (:514)
+    assert np.array_equal(cap[:, 3:6], orc.tissue_probe(m, sample, 0.0, 0.5, ch)[:, 3:6])
+
+
+def test_parenchyma_and_glisson_follow_the_jit_branch_chains():
+    """`if (any_or<true>(..)) .. else if ..` executes its first branch only in the JIT variants (parenchyma.cpp:333-356,
+    glissonCapsule.cpp:370-380): an absorbed parenchyma lane keeps transmittance 1, the hepatocyte-diameter test never runs."""
+    rng = np.random.default_rng(6); n = 3000
+    sample = rng.random(n, dtype=F); ch = rng.integers(0, 3, n).astype(np.uint32)
+    p = _medium("parenchyma")
+    out = orc.tissue_probe(p, sample, 0.0, np.inf, ch)                     # tissue depth is ignored (parenchyma.cpp:193)
+    assert np.array_equal(out, orc.tissue_probe(p, sample, 5.0, np.inf, ch))
+    bt = out[:, 1].view(np.uint32); tr = out[:, 3:6]
+    assert np.all(tr[bt == 0] == 1)                                         # absorbed, but only the first branch ran
+    assert np.all(tr[bt == 2].sum(1) == 1)                                  # hepatocytes: one-hot, however close
+    assert np.all(np.isfinite(out[:, 2]))                                   # maxt = inf: every distance is inside the segment
+    np.testing.assert_allclose(out[:, 6], np.array([77.2 / 255, 105.0 / 255, 149.0 / 255], F)[ch], rtol=1e-7)   # parenchyma.cpp:182
+    g = _medium("glissonCapsule")
+    out = orc.tissue_probe(g, sample, 0.5, np.inf, ch)                      # below the capsule: nothing to hit
+    assert np.all(np.isinf(out[:, 0])) and np.all(np.isinf(out[:, 2])) and np.all(out[:, 3:6] == 1)
+    out = orc.tissue_probe(g, sample, 0.005, np.inf, ch)
+    lv = orc.tissue_probe(_medium("liver"), sample, 0.005, np.inf, ch)
+    assert np.array_equal(out, lv)                                           # inside the capsule the two plugins agree
+
+
+def test_loader_reproduces_the_constructor_property_mixup():
+    """liver.cpp:149-150 ... 174-175: G <- "..._B", B <- "..._G" for every collagen layer and elastin layers 1-2 only."""
+    m = _medium("liver", sigma_collagen2_R=1.0, sigma_collagen2_G=2.0, sigma_collagen2_B=3.0,
+                sigma_elastin2_R=4.0, sigma_elastin2_G=5.0, sigma_elastin2_B=6.0,
+                sigma_elastin3_R=7.0, sigma_elastin3_G=8.0, sigma_elastin3_B=9.0, layer4Limit=0.02)
+    assert list(m.sigma_collagen[1]) == [1.0, 3.0, 2.0]
+    assert list(m.sigma_elastin[1]) == [4.0, 6.0, 5.0]
+    assert list(m.sigma_elastin[2]) == [7.0, 8.0, 9.0]
+    np.testing.assert_allclose(list(m.layer_limit), [0.0065, 0.0072, 0.0083, 0.02], rtol=1e-7)
+    assert m.kind == K.MEDIUM_LIVER and m.has_spectral_extinction == 1
+    assert _medium("parenchyma").has_spectral_extinction == 0               # parenchyma.cpp:150
+    with pytest.raises(NotImplementedError):
+        _medium("liver", sigma_t={"type": "gridvolume", "grid": np.ones((2, 2, 2), F)})
+
+
+def test_xml_scene_with_liver_medium(tmp_path):
+    """The fork's scene layout (scenes/Liver-SingleMesh/mitsuba3/scene.xml:2-9, :51-92) through the XML loader."""
+    xml = textwrap.dedent("""\
+        <scene version="3.6.0">
+            <default name="integrator" value="biovolpath"/>
+            <default name="spp" value="4"/>
+            <integrator type="$integrator"><integer name="max_depth" value="12"/></integrator>
+            <sensor type="perspective">
+                <float name="fov" value="45"/>
+                <transform name="to_world"><lookat origin="0, 0, 4" target="0, 0, 0" up="0, 1, 0"/></transform>
+                <sampler type="independent"><integer name="sample_count" value="$spp"/></sampler>
+                <film type="hdrfilm"><integer name="width" value="16"/><integer name="height" value="16"/><rfilter type="box"/></film>
+            </sensor>
+            <bsdf type="dielectric" id="ParenchymaBSDF"><float name="int_ior" value="1.38"/><float name="ext_ior" value="1"/></bsdf>
+            <medium id="LiverMedium" type="liver">
+                <float name="sigma_collagen1_R" value="3.146124563777685"/>
+                <float name="sigma_collagen1_G" value="2.2189004838302524"/>
+                <float name="sigma_collagen1_B" value="1.5741115169422308"/>
+                <rgb name="sigma_blood" value="0.004611074674964207, 0.20900034649954347, 0.24625187839886722"/>
+                <float name="sigma_hepatocity" value="269.26180490217416"/>
+                <float name="scale" value="1"/>
+                <phase type="isotropic"/>
+            </medium>
+            <shape type="cube"><ref id="ParenchymaBSDF"/><ref name="interior" id="LiverMedium"/></shape>
+            <emitter type="constant"><rgb name="radiance" value="1.0, 1.0, 1.0"/></emitter>
+        </scene>""")
+    p = tmp_path / "scene.xml"; p.write_text(xml)
+    sc = load_file(str(p))
+    assert sc.integrator.kind == K.INTEGRATOR_BIOVOLPATH and sc.integrator.max_depth == 12
+    m = sc.media[0]
+    assert m.kind == K.MEDIUM_LIVER
+    np.testing.assert_allclose(list(m.sigma_collagen[0]), [3.146124563777685, 1.5741115169422308, 2.2189004838302524], rtol=1e-7)
+    np.testing.assert_allclose(list(m.sigma_blood), [0.004611074674964207, 0.20900034649954347, 0.24625187839886722], rtol=1e-7)
+    assert list(m.sigma_bile) == [1.0, 1.0, 1.0] and abs(m.sigma_hepatocity - 269.2618) < 1e-3
+    L = orc.OracleScene(sc).sample_lanes(0, 4, 0, 16 * 16 * 4)
+    assert np.isfinite(L).all() and L[:, 3].all() and 0.3 < L[:, :3].mean() <= 1.0       # unit environment; tissue only removes energy
+
+
+def _scene(builder, res=24, spp=8, **kw):
+    return Scene(builder(res=res, spp=spp, **kw))
+
+
+@pytest.mark.parametrize("builder", [scenes.liver_single_mesh_bio, scenes.liver_multi_mesh_bio])
+def test_biovolpath_lane_properties(builder):
+    sc = _scene(builder); o = orc.OracleScene(sc); n = 24 * 24 * 8
+    L = o.sample_lanes(0, 8, 0, n)
+    assert np.array_equal(L, orc.OracleScene(sc, threads=1).sample_lanes(0, 8, 0, n))     # lanes are independent
+    assert np.isfinite(L).all() and np.all(L[:, :3] >= 0) and np.all(L[:, 3] == 1)
+    st = o.stats()
+    assert st["real_scatters"] > 0 and st["collisions"] >= st["real_scatters"]
+    # a path that scattered in tissue carries a one-hot throughput from then on and has the other channels of its
+    # accumulated radiance cleared each iteration (biovolpath.cpp:304): a lane ends with three live channels (never
+    # interacted), one (its own channel) or none (absorbed / cleared in the iteration it died in) -- never two
+    live = (L[:, :3] > 0).sum(1)
+    assert (live == 2).sum() == 0 and (live == 1).mean() > 0.03 and (live == 0).mean() > 0.05 and (live == 3).mean() > 0.3
+
+
+def test_biovolpath_uses_the_stale_surface_distance():
+    """biovolpath.cpp:222 hands sample_interaction Ray3f(ray, si.t): the segment length is the PREVIOUS intersection's
+    distance.  With the camera inside the medium the first iteration therefore samples against maxt = inf."""
+    d = scenes.liver_single_mesh_bio(res=8, spp=4)
+    d["sensor"]["medium"] = dict(d["liver"]["interior"])
+    sc = Scene(d)
+    if sc.sensor.medium < 0:
+        pytest.skip("sensor media are not wired through the dict loader")
+    L = orc.OracleScene(sc).sample_lanes(0, 4, 0, 8 * 8 * 4)
+    assert np.isfinite(L).all()
+
+
+def test_max_depth_one_zeroes_everything():
+    """Lanes die at the top of iteration 2 (depth 1 = max_depth) outside any medium: `mei` is zeros there, so :304 clears the
+    radiance the first iteration gathered from the emitter the lane looked at through a smooth surface -- and keeps what an
+    escaping lane collected, because a lane that leaves the scene ends its loop in the iteration that added the radiance."""
+    d = scenes.liver_single_mesh_bio(res=16, spp=4, max_depth=1)
+    L = orc.OracleScene(Scene(d)).sample_lanes(0, 4, 0, 16 * 16 * 4)
+    assert np.isfinite(L).all()
+    hit = (L[:, :3] == 0).all(1)
+    assert 0.05 < hit.mean() < 0.8                                         # organ lanes are black, background lanes are not

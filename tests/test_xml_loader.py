@@ -132,8 +132,8 @@ def test_default_parameters_and_errors(tmp_path):
     (tmp_path / "bad.xml").write_text(XML.replace('<default name="spp" value="16"/>', ""))
     with pytest.raises(RuntimeError, match=r"undefined parameter"):
         mi.load_file(str(tmp_path / "bad.xml"))
-    (tmp_path / "bio.xml").write_text(XML.replace('<integrator type="volpath">', '<integrator type="biovolpath">'))
-    with pytest.raises(NotImplementedError, match="biovolpath"):
+    (tmp_path / "bio.xml").write_text(XML.replace('<integrator type="volpath">', '<integrator type="biovolpath06">'))
+    with pytest.raises(NotImplementedError, match="biovolpath06"):
         mi.load_file(str(tmp_path / "bio.xml"))
     # <include>: the shared part of a scene in its own file (resources/data/tests/scenes/participating_media/include/*.xml)
     head, tail = XML.split("<emitter", 1)

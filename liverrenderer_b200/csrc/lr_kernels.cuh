@@ -153,9 +153,11 @@ __global__ void __launch_bounds__(128) k_render(const __grid_constant__ DScene s
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0; unsigned long long nsamples = 0;
     const uint32_t lane_id = threadIdx.x & 31;
     const bool box = sc.sensor.rfilter == LR_RFILTER_BOX, coalesce = a.spp_per_pass >= 4;
-    for (;;) {
+    for (uint32_t it = 0;; ++it) {
         unsigned long long base = 0;
-        if (lane_id == 0) base = (*a.cancel) ? ~0ull : atomicAdd(a.work_counter, 32ull);
+        // the cancel flag lives in mapped host memory: one read costs a PCIe round trip, so a warp looks at it when it starts and
+        // then every 64th batch (a read per batch capped the whole kernel at ~1 M batches/s)
+        if (lane_id == 0) base = ((it & 63u) == 0u && *a.cancel) ? ~0ull : atomicAdd(a.work_counter, 32ull);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base == ~0ull || a.lane_begin + base >= a.lane_end) break;
         const uint64_t li = a.lane_begin + base + lane_id;
@@ -228,9 +230,11 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene
     const uint32_t lane_id = threadIdx.x & 31;
     const bool box = sc.sensor.rfilter == LR_RFILTER_BOX, coalesce = a.spp_per_pass >= 4;
     const int W = (int) sc.sensor.film_width, H = (int) sc.sensor.film_height;
-    for (;;) {
+    for (uint32_t it = 0;; ++it) {
         unsigned long long base = 0;
-        if (lane_id == 0) base = (*a.cancel) ? ~0ull : atomicAdd(a.work_counter, 32ull);
+        // the cancel flag lives in mapped host memory: one read costs a PCIe round trip, so a warp looks at it when it starts and
+        // then every 64th batch (a read per batch capped the whole kernel at ~1 M batches/s)
+        if (lane_id == 0) base = ((it & 63u) == 0u && *a.cancel) ? ~0ull : atomicAdd(a.work_counter, 32ull);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (base == ~0ull || a.lane_begin + base >= a.lane_end) break;
         const uint64_t li = a.lane_begin + base + lane_id;

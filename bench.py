@@ -392,6 +392,28 @@ def run_b200(args):
             xl["roofline"] = {"bound": "hbm", "achieved": b, "peak": hbm_peak, "unit": "GB/s", "frac": b / hbm_peak, "traffic": None,
                               "note": "32 B per collision over the WHOLE step time (tracking is one stage of several), so a lower bound on the tracking kernels' own rate"}
             extras["c3xl"] = xl
+            # the fork's own rendering model -- biovolpath + tissue media -- on the two scenes whose wall-clock the
+            # reference tree records (unstated hardware and variant, so a ratio to them is context, not a comparison)
+            def bio(builder, label, published, cpu_res=135):
+                spp_b = 256
+                c2 = mi.Context(local).upload(mi.load_dict(builder(res=args.res, spp=spp_b))); c2.set_stream(stream.cuda_stream)
+                ms, st2 = timed_render(torch, c2, stream, barrier, 7, spp_b, 2); c2.close()
+                e = {"value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "spp": spp_b, "mrays_per_s": st2["rays"] / (ms * 1e-3) / 1e6,
+                     "rays_per_sample": st2["rays"] / max(st2["samples"], 1), "kernel": "k_render<biovolpath> (one lane per thread, persistent grid)", "note": label,
+                     "published_reference": {"value": published, "unit": UNIT, "source": "BASELINE.md (1920x1080, 256 spp; hardware and variant not stated)"}}
+                try:
+                    from tests import orc
+                    o = orc.OracleScene(mi.load_dict(builder(res=cpu_res, spp=64)), threads=0, fast=True)
+                    t0 = time.perf_counter(); o.render(seed=0, spp=64); dt = time.perf_counter() - t0
+                    e["cpu_baseline"] = {"value": cpu_res * cpu_res * 64 / dt, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "port",
+                                         "sample": f"the same frame at {cpu_res}x{cpu_res}, 64 spp ({cpu_res * cpu_res * 64} samples, {dt:.1f} s), oracle/ -O3 -march=native, std::thread"}
+                except Exception as ex:                                   # the oracle is the checker, never a dependency of the measured arm
+                    e["cpu_baseline"] = {"unavailable": str(ex)[:120]}
+                return e
+            extras["biovolpath_liver_single_mesh"] = bio(_sc.liver_single_mesh_bio, "Liver-SingleMesh as the fork ships it: biovolpath, `liver` medium, bumpmap over dielectric 1.38, "
+                                                         "envmap, independent sampler (scenes/Liver-SingleMesh/mitsuba3/scene.xml)", 3.30e6)
+            extras["biovolpath_liver_multi_mesh"] = bio(_sc.liver_multi_mesh_bio, "Liver-MultiMesh as its scene file lays it out: capsule shell with `glissonCapsule`, organ with "
+                                                        "`parenchyma`, ldsampler (scenes/Liver-MultiMesh/mitsuba3/scene.xml)", 11.9e6)
     return dict(extras=extras, weak=weak, torch=torch, dist=dist, mi=mi, multi=multi, ctx=ctx, sc=sc, dev=dev, stream=stream, world=world, rank=rank, local=local,
                 spp=spp, name=name, W=W, H=H, run=main_run, table=table, rooflines=rooflines, roofline=roofline, barrier=barrier, flush=flush, hbm_peak=hbm_peak,
                 set_partition=set_partition, film=film)

@@ -47,6 +47,7 @@ typedef enum lr_integrator_kind {
     LR_INTEGRATOR_PATH       = 0,  /* src/integrators/path.cpp:95-349            */
     LR_INTEGRATOR_VOLPATH    = 1,  /* src/integrators/volpath.cpp:93-554         */
     LR_INTEGRATOR_PRBVOLPATH = 2,  /* src/python/python/ad/integrators/prbvolpath.py:96-444 */
+    LR_INTEGRATOR_VOLPATHMIS = 4,  /* src/integrators/volpathmis.cpp:97-700 (lr_integrator.spectral_mis = use_spectral_mis) */
     LR_INTEGRATOR_BIOVOLPATH = 3   /* the fork's src/integrators/biovolpath.cpp:95-551: volpath with the tissue media below
                                       (accumulated tissue depth, one-hot channel transmittance); needs every medium of the
                                       scene to be one of the tissue kinds, as the base Medium's five-argument
@@ -264,6 +265,7 @@ typedef struct lr_integrator {
     uint32_t base_seed;             /* independent sampler `seed`               */
     uint32_t majorant_cell;         /* DDA super-voxel edge in voxels (0 => default 8) */
     uint32_t sampler;               /* lr_sampler_kind: the sensor's sampler plugin */
+    uint32_t spectral_mis;          /* volpathmis: use_spectral_mis (default 1, volpathmis.cpp:79) */
 } lr_integrator;
 
 typedef struct lr_scene {

@@ -18,7 +18,7 @@ LR_API_VERSION = 4
 LR_ERR = {-1: "invalid argument", -2: "no CUDA device (this backend has no CPU path)", -3: "CUDA error",
           -4: "unsupported plugin/option", -5: "no scene uploaded", -6: "cancelled", -7: "out of memory"}
 
-INTEGRATOR_PATH, INTEGRATOR_VOLPATH, INTEGRATOR_PRBVOLPATH, INTEGRATOR_BIOVOLPATH = 0, 1, 2, 3
+INTEGRATOR_PATH, INTEGRATOR_VOLPATH, INTEGRATOR_PRBVOLPATH, INTEGRATOR_BIOVOLPATH, INTEGRATOR_VOLPATHMIS = 0, 1, 2, 3, 4
 TRACKING_REFERENCE, TRACKING_DDA = 0, 1
 SAMPLER_INDEPENDENT, SAMPLER_LD = 0, 1
 BSDF_DIFFUSE, BSDF_ROUGHDIELECTRIC, BSDF_PRINCIPLED, BSDF_NULL, BSDF_DIELECTRIC = 0, 1, 2, 3, 4
@@ -93,7 +93,8 @@ class lr_sensor(C.Structure):
 
 class lr_integrator(C.Structure):
     _fields_ = [("kind", C.c_uint32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("hide_emitters", C.c_uint32),
-                ("tracking", C.c_uint32), ("base_seed", C.c_uint32), ("majorant_cell", C.c_uint32), ("sampler", C.c_uint32)]
+                ("tracking", C.c_uint32), ("base_seed", C.c_uint32), ("majorant_cell", C.c_uint32), ("sampler", C.c_uint32),
+                ("spectral_mis", C.c_uint32)]
 
 
 class lr_scene(C.Structure):

@@ -72,7 +72,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     if (s->api_version != LR_API_VERSION) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_scene_upload: api_version %u != %u", s->api_version, LR_API_VERSION);
     if (s->n_bsdfs > LR_MAX_BSDFS || s->n_media > LR_MAX_MEDIA || s->n_grids > LR_MAX_GRIDS || s->n_emitters > LR_MAX_EMITTERS)
         LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: too many bsdfs/media/grids/emitters");
-    if (s->integrator.kind > LR_INTEGRATOR_BIOVOLPATH) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: unknown integrator kind %u", s->integrator.kind);
+    if (s->integrator.kind > LR_INTEGRATOR_VOLPATHMIS) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: unknown integrator kind %u", s->integrator.kind);
     LR_CUDA(c, cudaSetDevice(c->device));
     c->free_scene();
     DScene &sc = c->sc; memset(&sc, 0, sizeof sc);

@@ -3,6 +3,7 @@
 #include "lr_integrators.cuh"
 #include "lr_prb.cuh"
 #include "lr_biovolpath.cuh"
+#include "lr_volpathmis.cuh"
 
 namespace lr {
 
@@ -129,11 +130,14 @@ LR_DEV void lane_next_ray(const DScene &sc, LaneSetup &L) {
     L.ray = camera_ray(sc, adjusted);
 }
 
+#define LR_KIND_VOLPATHMIS_PLAIN 5      // kernel instantiation only: volpathmis with use_spectral_mis = false
 template <int KIND>
 LR_DEV LaneResult run_lane(const DScene &sc, const DTri *tris_gid, LaneSetup &L, Counters &cnt) {
     if (KIND == LR_INTEGRATOR_PATH) return sample_path(sc, tris_gid, L.smp, L.ray, cnt);
     if (KIND == LR_INTEGRATOR_VOLPATH) return sample_volpath(sc, tris_gid, L.smp, L.ray, sc.sensor.medium, cnt);
     if (KIND == LR_INTEGRATOR_BIOVOLPATH) return sample_biovolpath(sc, tris_gid, L.smp, L.ray, sc.sensor.medium, cnt);
+    if (KIND == LR_INTEGRATOR_VOLPATHMIS) return sample_volpathmis<true>(sc, tris_gid, L.smp, L.ray, sc.sensor.medium, cnt);
+    if (KIND == LR_KIND_VOLPATHMIS_PLAIN) return sample_volpathmis<false>(sc, tris_gid, L.smp, L.ray, sc.sensor.medium, cnt);
     return sample_prb<true>(sc, tris_gid, L.smp, L.ray, mk3(0.f), mk3(0.f), cnt);
 }
 

@@ -1,4 +1,4 @@
-// lr_lanes.cu -- the one-lane-per-thread kernels (k_render: 4 integrators x 2 film layouts x {film, per-lane output};
+// lr_lanes.cu -- the one-lane-per-thread kernels (k_render: 5 integrators x 2 film layouts x {film, per-lane output};
 // k_backward: per-lane prbvolpath adjoint) in their own translation unit.  They are the parity probes
 // (lr_sample_lanes) and the LR_MEGAKERNEL=1 A/B path, and take half of the build time; the production wavefront
 // kernels live in lr_backend.cu.  No relocatable device code: each TU links its own device image.
@@ -25,6 +25,8 @@ template <int C, bool TO_FILM> static cudaError_t launch_render_k(int n_sm, cuda
         case LR_INTEGRATOR_PATH: return launch_render_t<LR_INTEGRATOR_PATH, C, TO_FILM>(n_sm, s, sc, a);
         case LR_INTEGRATOR_VOLPATH: return launch_render_t<LR_INTEGRATOR_VOLPATH, C, TO_FILM>(n_sm, s, sc, a);
         case LR_INTEGRATOR_BIOVOLPATH: return launch_render_t<LR_INTEGRATOR_BIOVOLPATH, C, TO_FILM>(n_sm, s, sc, a);
+        case LR_INTEGRATOR_VOLPATHMIS: return sc.integ.spectral_mis ? launch_render_t<LR_INTEGRATOR_VOLPATHMIS, C, TO_FILM>(n_sm, s, sc, a)
+                                                                     : launch_render_t<LR_KIND_VOLPATHMIS_PLAIN, C, TO_FILM>(n_sm, s, sc, a);
         default: return launch_render_t<LR_INTEGRATOR_PRBVOLPATH, C, TO_FILM>(n_sm, s, sc, a);
     }
 }

@@ -110,7 +110,7 @@ class Scene:
         self.sensor = None; self.integrator = None
         self.spp = 4
         self._named = {k: v for k, v in d.items() if isinstance(v, dict)}
-        self._integrator_type = next((v.get("type") for v in self._named.values() if v.get("type") in ("path", "volpath", "prbvolpath", "biovolpath")), "path")
+        self._integrator_type = next((v.get("type") for v in self._named.values() if v.get("type") in ("path", "volpath", "prbvolpath", "biovolpath", "volpathmis")), "path")
         # first pass: named BSDFs / media so that {'type':'ref','id':...} resolves
         for name, v in self._named.items():
             t = v.get("type")
@@ -128,17 +128,17 @@ class Scene:
                 self._add_env(v)
             elif t == "perspective":
                 self._sensor_dict = v
-            elif t in ("path", "volpath", "prbvolpath", "biovolpath"):
+            elif t in ("path", "volpath", "prbvolpath", "biovolpath", "volpathmis"):
                 self._integrator_dict = v
-            elif t in ("biovolpath06", "volpathmis", "direct", "aov", "moment", "ptracer", "stokes", "depth",
+            elif t in ("biovolpath06", "direct", "aov", "moment", "ptracer", "stokes", "depth",
                        "prb", "prbvolpath_basic", "direct_projective", "prb_projective"):
-                raise NotImplementedError(f"integrator plugin '{t}' is outside the hot path (path, volpath, prbvolpath, biovolpath)")
+                raise NotImplementedError(f"integrator plugin '{t}' is outside the hot path (path, volpath, volpathmis, prbvolpath, biovolpath)")
             elif t in ("diffuse", "roughdielectric", "principled", "null", "dielectric", "bumpmap", "homogeneous", "heterogeneous") or t in _TISSUE_MEDIA:
                 pass                                  # named BSDFs / media: handled by the first pass
             else:
                 # anything else would silently vanish from the render (a `point` emitter, a `ply` shape, a `plastic` BSDF ...)
                 raise NotImplementedError(f"plugin '{t}' (object '{name}') is outside the hot path; supported top-level plugins: "
-                                          "perspective, path/volpath/prbvolpath/biovolpath, rectangle/cube/sphere/obj/mesh, constant/envmap, "
+                                          "perspective, path/volpath/volpathmis/prbvolpath/biovolpath, rectangle/cube/sphere/obj/mesh, constant/envmap, "
                                           "diffuse/roughdielectric/principled/null/dielectric/bumpmap, homogeneous/heterogeneous, "
                                           "liver/glissonCapsule/parenchyma")
         if not hasattr(self, "_sensor_dict"):
@@ -509,7 +509,8 @@ class Scene:
     def _build_integrator(self, v):
         i = K.lr_integrator()
         i.kind = {"path": K.INTEGRATOR_PATH, "volpath": K.INTEGRATOR_VOLPATH, "prbvolpath": K.INTEGRATOR_PRBVOLPATH,
-                  "biovolpath": K.INTEGRATOR_BIOVOLPATH}[v["type"]]
+                  "biovolpath": K.INTEGRATOR_BIOVOLPATH, "volpathmis": K.INTEGRATOR_VOLPATHMIS}[v["type"]]
+        i.spectral_mis = 1 if v.get("use_spectral_mis", True) else 0                          # volpathmis.cpp:79
         md = int(v.get("max_depth", 6 if v["type"] == "prbvolpath" else -1))
         if md < 0 and md != -1:
             raise RuntimeError('"max_depth" must be set to -1 (infinite) or a value >= 0')

@@ -130,6 +130,7 @@ static LaneResult run_lane(Integrator &in, LaneSetup &L) {
         case LR_INTEGRATOR_PATH: return in.sample_path(L.smp, L.ray);
         case LR_INTEGRATOR_VOLPATH: return in.sample_volpath(L.smp, L.ray, sc.sensor.medium);
         case LR_INTEGRATOR_BIOVOLPATH: return in.sample_biovolpath(L.smp, L.ray, sc.sensor.medium);
+        case LR_INTEGRATOR_VOLPATHMIS: return in.sample_volpathmis(L.smp, L.ray, sc.sensor.medium);
         default: return in.sample_prb(true, L.smp, L.ray, V3(0.f), V3(0.f));
     }
 }

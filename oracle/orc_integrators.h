@@ -176,6 +176,7 @@ struct Integrator {
 #include "orc_volpath.inl"
 #include "orc_prbvolpath.inl"
 #include "orc_biovolpath.inl"
+#include "orc_volpathmis.inl"
 };
 
 } // namespace orc

@@ -410,6 +410,18 @@ def run_b200(args):
                 except Exception as ex:                                   # the oracle is the checker, never a dependency of the measured arm
                     e["cpu_baseline"] = {"unavailable": str(ex)[:120]}
                 return e
+            # SURVEY.md 8(f) rank 4 (first half): volpathmis on the C3 frame.  One lane per thread, global-majorant tracking in the reference's
+            # draw order; the comparable volpath figure is extras.reference_order_tracking (wavefront).  16 spp: the kernel is ~30x slower.
+            def mis(spectral):
+                dd = _sc.liver_single_mesh(res=args.res, spp=16, grid_res=256, tracking="reference")
+                dd["integrator"] = {"type": "volpathmis", "max_depth": 12, "rr_depth": 5, "use_spectral_mis": spectral}
+                c2 = mi.Context(local).upload(mi.load_dict(dd)); c2.set_stream(stream.cuda_stream)
+                ms, st2 = timed_render(torch, c2, stream, barrier, 7, 16, 1); c2.close()
+                return {"value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "spp": 16, "collisions_per_sample": st2["collisions"] / max(st2["samples"], 1),
+                        "collisions_per_s": st2["collisions"] / (ms * 1e-3), "kernel": "k_render<volpathmis> (one lane per thread: a warp waits for its longest path)",
+                        "note": f"C3 frame under volpathmis, use_spectral_mis = {str(spectral).lower()} (volpathmis.cpp:79)"}
+            extras["volpathmis_c3"] = mis(True)
+            extras["volpathmis_c3_plain_mis"] = mis(False)
             extras["biovolpath_liver_single_mesh"] = bio(_sc.liver_single_mesh_bio, "Liver-SingleMesh as the fork ships it: biovolpath, `liver` medium, bumpmap over dielectric 1.38, "
                                                          "envmap, independent sampler (scenes/Liver-SingleMesh/mitsuba3/scene.xml)", 3.30e6)
             extras["biovolpath_liver_multi_mesh"] = bio(_sc.liver_multi_mesh_bio, "Liver-MultiMesh as its scene file lays it out: capsule shell with `glissonCapsule`, organ with "

@@ -178,37 +178,49 @@ LR_DEV void bio_apply_transmittance(const BioInteraction &mei, int medium, V3 &r
 //  (2) in the iteration in which a lane dies at the top (Russian roulette / max_depth), lanes inside a medium still get a
 //      fresh interaction -- from the sampler's NEXT value, which a masked next_1d returns without consuming it, and with
 //      active = false -- and :304 zeroes `result` per channel where that interaction's transmittance is 0.
-LR_DEV LaneResult sample_biovolpath(const DScene &sc, const DTri *tris_gid, Sampler &smp, Ray ray, int initial_medium, Counters &cnt) {
-    bool valid_ray = !sc.hide_emitters && sc.env >= 0;
-    float eta = 1.f; V3 throughput = mk3(1.f), result = mk3(0.f);
-    int medium = initial_medium; BioInteraction mei = bio_zeros();
-    bool specular_chain = !sc.hide_emitters; uint32_t depth = 0;
-    const uint32_t channel = (uint32_t) fminf(smp.next_1d() * 3.f, 2.f);
-    SurfaceInteraction si = invalid_si(); bool needs_intersection = true;
-    V3 last_scatter_p = mk3(0.f); float last_scatter_direction_pdf = 1.f, tissue_depth = 0.f;
-    bool active = true;
-    while (active) {
-        active &= any_nonzero(throughput);
+// The loop is written as a resumable path: init() + one step() per iteration of the reference's loop (the unit a wavefront port
+// would cut at).  Handing a finished lane a new path between steps was tried and bought nothing (0.98x / 0.88x on the two liver
+// scenes): the idle lanes of k_render<biovolpath> -- 8 of 32 threads active per instruction, profiles/r2_kernel_metrics_single.txt --
+// sit inside a step (BVH walks and shadow walks of different lengths), not behind a long path.
+struct BioPath {
+    Sampler smp; Ray ray; V3 throughput, result, last_scatter_p;
+    float eta, last_scatter_direction_pdf, tissue_depth, si_t;            // si_t: the previous intersection's distance (what :222 passes as maxt)
+    int medium; uint32_t depth, channel; bool valid_ray, specular_chain;
+
+    LR_DEV void init(const DScene &sc, const Sampler &s, const Ray &r, int initial_medium) {
+        smp = s; ray = r; valid_ray = !sc.hide_emitters && sc.env >= 0;
+        eta = 1.f; throughput = mk3(1.f); result = mk3(0.f); medium = initial_medium;
+        specular_chain = !sc.hide_emitters; depth = 0;
+        channel = (uint32_t) fminf(smp.next_1d() * 3.f, 2.f);
+        si_t = LR_INF; last_scatter_p = mk3(0.f); last_scatter_direction_pdf = 1.f; tissue_depth = 0.f;
+    }
+    LR_DEV LaneResult finish() const { LaneResult out; out.L = result; out.valid = valid_ray; return out; }
+
+    // one iteration of the loop; false: the lane's loop has ended.  `needs_intersection` is true at the top of every iteration
+    // (every event spawns a new ray, and a null collision -- the only thing that keeps a hit -- cannot happen: sigma_n = 0).
+    LR_DEV bool step(const DScene &sc, const DTri *tris_gid, Counters &cnt) {
+        bool active = any_nonzero(throughput);
         float q = fminf(hmax(throughput) * sqr(eta), .95f);
         bool perform_rr = depth > (uint32_t) sc.rr_depth;
         if (active) { float u = smp.next_1d(); active &= (u < q) || !perform_rr; }
         if (perform_rr) throughput *= 1.f / q;
         active &= depth < sc.max_depth;
+        BioInteraction mei;
         if (!active) {                                                                 // note (2)
-            if (medium >= 0) { Sampler peek = smp; mei = bio_sample_interaction(sc.media[medium].m, ray, si.t, peek.next_1d(), channel, tissue_depth, false, cnt.collisions); }
+            if (medium >= 0) { Sampler peek = smp; mei = bio_sample_interaction(sc.media[medium].m, ray, si_t, peek.next_1d(), channel, tissue_depth, false, cnt.collisions); }
             else mei = bio_zeros();
             bio_apply_transmittance(mei, medium, result, throughput);
-            break;
+            return false;
         }
-
+        SurfaceInteraction si = invalid_si(); si.t = si_t; bool needs_intersection = true;
         bool active_medium = medium >= 0, active_surface = !active_medium;
-        bool act_null_scatter = false, act_medium_scatter = false, escaped_medium = false, is_spectral = false;
+        bool act_medium_scatter = false, escaped_medium = false, is_spectral = false;
         if (active_medium) {
             const lr_medium &m = sc.media[medium].m;
             is_spectral = m.has_spectral_extinction != 0;
             mei = bio_sample_interaction(m, ray, si.t, smp.next_1d(), channel, tissue_depth, true, cnt.collisions);   // :222
             if (bio_valid(mei)) ray.maxt = mei.t;
-            if (needs_intersection) si = intersect(sc, tris_gid, ray, cnt);
+            si = intersect(sc, tris_gid, ray, cnt);
             needs_intersection = false;
             if (si.t < mei.t) mei.t = LR_INF;
             if (is_spectral) {                                                         // :231-235, medium.cpp:95-104
@@ -220,16 +232,16 @@ LR_DEV LaneResult sample_biovolpath(const DScene &sc, const DTri *tris_gid, Samp
             }
             escaped_medium = !bio_valid(mei); active_medium = bio_valid(mei);
             if (active_medium) {
-                const float ce = idx3(mei.combined_extinction, channel);
-                bool null_scatter = smp.next_1d() >= mei.sigma_t_ch / ce;              // :241
-                act_null_scatter = null_scatter; act_medium_scatter = !null_scatter;
-                if (is_spectral && act_null_scatter) throughput *= mk3(0.f) * ce / 0.f;   // sigma_n * ce / sigma_n[ch], sigma_n = 0 (:245-248)
+                // :241 null_scatter = u >= sigma_t[ch] / combined_extinction[ch]: the two are the same number whenever the interaction is valid
+                // (valid_mi follows from 0 < distance < maxt), so the quotient is 1 -- or NaN for a zero / infinite sigma_t -- and u < 1: never true.
+                // The draw is still made.
+                (void) smp.next_1d();
+                act_medium_scatter = true;
                 if (act_medium_scatter) { depth += 1; last_scatter_p = mei.p; cnt.real_scatters++; }
             }
         } else mei = bio_zeros();                                                      // note (1)
         active &= depth < sc.max_depth;
         act_medium_scatter &= active;
-        if (act_null_scatter) { ray.o = mei.p; si.t = si.t - mei.t; }
 
         if (act_medium_scatter) {
             throughput *= mei.transmittance;                                           // :266-275
@@ -271,7 +283,6 @@ LR_DEV LaneResult sample_biovolpath(const DScene &sc, const DTri *tris_gid, Samp
             V3 bsdf_val; BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_val);
             throughput *= bsdf_val; eta *= bs.eta;
             ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
-            needs_intersection = true;
             bool non_null = !(bs.sampled_type & F_NULL);
             if (non_null) { depth += 1; last_scatter_p = si.p; last_scatter_direction_pdf = bs.pdf; }
             valid_ray |= non_null;
@@ -279,9 +290,17 @@ LR_DEV LaneResult sample_biovolpath(const DScene &sc, const DTri *tris_gid, Samp
             specular_chain &= !(bs.sampled_type & F_SMOOTH);
             if (mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
         }
+        si_t = si.t;
         active &= (active_surface || active_medium);
+        return active;
     }
-    LaneResult out; out.L = result; out.valid = valid_ray; return out;
+};
+
+LR_DEV LaneResult sample_biovolpath(const DScene &sc, const DTri *tris_gid, Sampler &smp, Ray ray, int initial_medium, Counters &cnt) {
+    BioPath p; p.init(sc, smp, ray, initial_medium);
+    while (p.step(sc, tris_gid, cnt)) { }
+    smp = p.smp;
+    return p.finish();
 }
 
 } // namespace lr

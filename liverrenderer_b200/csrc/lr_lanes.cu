@@ -6,6 +6,7 @@
 #include "lr_kernels.cuh"
 #include "lr_lanes.h"
 #include <algorithm>
+#include <cstdlib>
 
 namespace lr {
 

@@ -138,19 +138,28 @@ LR_DEV V3 sample_emitter_mis(const DScene &sc, const DTri *tris_gid, V3 ref_p, V
     return emitter_val;
 }
 
-// VolpathMisIntegratorImpl::sample (volpathmis.cpp:120-463)
+// VolpathMisIntegratorImpl::sample (volpathmis.cpp:120-463) as a resumable path: init() + one step() per iteration of the reference's
+// loop.  Refilling finished lanes between steps does not help (1.04x on the C3 frame): 2.4 of 32 threads are active per instruction
+// (profiles/r2_kernel_metrics_mis.txt) because a step contains the emitter-sampling walk -- tens of global-majorant collisions for one
+// lane while its neighbours wait.  The fix is the wavefront cut at collision granularity that volpath already has (lr_wavefront.cuh).
 template <bool SPECTRAL>
-LR_DEV LaneResult sample_volpathmis(const DScene &sc, const DTri *tris_gid, Sampler &smp, Ray ray, int initial_medium, Counters &cnt) {
-    bool valid_ray = !sc.hide_emitters && sc.env >= 0;
-    float eta = 1.f; V3 result = mk3(0.f);
-    int medium = initial_medium; MediumInteraction mei; mei.t = LR_INF; mei.medium = -1;
-    bool specular_chain = !sc.hide_emitters; uint32_t depth = 0;
-    MisW<SPECTRAL> p_over_f = misw_ones<SPECTRAL>(), p_over_f_nee = misw_ones<SPECTRAL>();
-    const uint32_t channel = (uint32_t) fminf(smp.next_1d() * 3.f, 2.f);
-    SurfaceInteraction si = invalid_si(); bool needs_intersection = true, last_event_was_null = false;
-    V3 last_scatter_p = mk3(0.f);
-    bool active = true;
-    while (active) {
+struct MisPath {
+    Sampler smp; Ray ray; SurfaceInteraction si; V3 result, last_scatter_p; float eta;
+    MisW<SPECTRAL> p_over_f, p_over_f_nee;
+    int medium; uint32_t depth, channel; bool valid_ray, specular_chain, needs_intersection, last_event_was_null;
+
+    LR_DEV void init(const DScene &sc, const Sampler &s, const Ray &r, int initial_medium) {
+        smp = s; ray = r; valid_ray = !sc.hide_emitters && sc.env >= 0;
+        eta = 1.f; result = mk3(0.f); medium = initial_medium;
+        specular_chain = !sc.hide_emitters; depth = 0;
+        p_over_f = misw_ones<SPECTRAL>(); p_over_f_nee = misw_ones<SPECTRAL>();
+        channel = (uint32_t) fminf(smp.next_1d() * 3.f, 2.f);
+        si = invalid_si(); needs_intersection = true; last_event_was_null = false; last_scatter_p = mk3(0.f);
+    }
+    LR_DEV LaneResult finish() const { LaneResult out; out.L = result; out.valid = valid_ray; return out; }
+
+    LR_DEV bool step(const DScene &sc, const DTri *tris_gid, Counters &cnt) {
+        bool active = true;
         const V3 mis_throughput = mis_weight1<SPECTRAL>(p_over_f);                 // :222-234
         const float q = fminf(hmax(mis_throughput) * sqr(eta), .95f);
         const bool perform_rr = !last_event_was_null && depth > (uint32_t) sc.rr_depth;
@@ -159,8 +168,9 @@ LR_DEV LaneResult sample_volpathmis(const DScene &sc, const DTri *tris_gid, Samp
         last_event_was_null = false;
         active &= depth < sc.max_depth;
         active &= any_nonzero(mis_weight1<SPECTRAL>(p_over_f));
-        if (!active) break;
+        if (!active) return false;
 
+        MediumInteraction mei; mei.t = LR_INF; mei.medium = -1;
         bool active_medium = medium >= 0, active_surface = !active_medium;
         bool act_null_scatter = false, act_medium_scatter = false, escaped_medium = false, is_spectral = false, not_spectral = false;
         if (active_medium) {
@@ -263,11 +273,6 @@ LR_DEV LaneResult sample_volpathmis(const DScene &sc, const DTri *tris_gid, Samp
             V3 bsdf_weight; BSDFSample bs = bsdf.sample(si.wi, s1, s2, bsdf_weight);
             const bool invalid_bsdf_sample = bs.pdf == 0.f;
             active_surface &= bs.pdf > 0.f;
-            if (active_surface) {
-                eta *= bs.eta;
-                ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
-                needs_intersection = true;
-            }
             const bool non_null = active_surface && !(bs.sampled_type & F_NULL);
             valid_ray |= non_null || invalid_bsdf_sample;
             specular_chain |= non_null && (bs.sampled_type & F_DELTA);
@@ -275,11 +280,24 @@ LR_DEV LaneResult sample_volpathmis(const DScene &sc, const DTri *tris_gid, Samp
             if (non_null) { depth += 1; last_scatter_p = si.p; p_over_f_nee = p_over_f; }
             update_weights<SPECTRAL>(p_over_f, mk3(bs.pdf), bsdf_weight * bs.pdf, channel, active_surface);
             update_weights<SPECTRAL>(p_over_f_nee, mk3(1.f), bsdf_weight * bs.pdf, channel, non_null);
-            if (active_surface && mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
+            if (active_surface) {
+                eta *= bs.eta;
+                ray = spawn_ray(si.p, si.n, si.sh.to_world(bs.wo));
+                needs_intersection = true;
+                if (mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
+            }
         }
         active &= (active_surface || active_medium);
+        return active;
     }
-    LaneResult out; out.L = result; out.valid = valid_ray; return out;
+};
+
+template <bool SPECTRAL>
+LR_DEV LaneResult sample_volpathmis(const DScene &sc, const DTri *tris_gid, Sampler &smp, Ray ray, int initial_medium, Counters &cnt) {
+    MisPath<SPECTRAL> p; p.init(sc, smp, ray, initial_medium);
+    while (p.step(sc, tris_gid, cnt)) { }
+    smp = p.smp;
+    return p.finish();
 }
 
 } // namespace lr

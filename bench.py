@@ -399,7 +399,7 @@ def run_b200(args):
                 c2 = mi.Context(local).upload(mi.load_dict(builder(res=args.res, spp=spp_b))); c2.set_stream(stream.cuda_stream)
                 ms, st2 = timed_render(torch, c2, stream, barrier, 7, spp_b, 2); c2.close()
                 e = {"value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "spp": spp_b, "mrays_per_s": st2["rays"] / (ms * 1e-3) / 1e6,
-                     "rays_per_sample": st2["rays"] / max(st2["samples"], 1), "kernel": "k_render<biovolpath> (one lane per thread, persistent grid)", "note": label,
+                     "rays_per_sample": st2["rays"] / max(st2["samples"], 1), "kernel": "wavefront biovolpath (lr_wavefront_bio.cuh: GEN, TRACE, k_bio_track / shade_a / nee / shade_b over queues)", "launches": st2.get("launches"), "note": label,
                      "published_reference": {"value": published, "unit": UNIT, "source": "BASELINE.md (1920x1080, 256 spp; hardware and variant not stated)"}}
                 try:
                     from tests import orc

@@ -77,6 +77,7 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     c->free_scene();
     DScene &sc = c->sc; memset(&sc, 0, sizeof sc);
     sc.sensor = s->sensor; sc.integ = s->integrator;
+    if (sc.integ.kind == LR_INTEGRATOR_BIOVOLPATH || sc.integ.kind == LR_INTEGRATOR_VOLPATHMIS) sc.integ.tracking = LR_TRACKING_REFERENCE;   // no production-tracking variant of these two
     mat_copy(sc.cam_to_world, s->sensor.to_world); mat_copy(sc.sample_to_camera, s->sensor.sample_to_camera);
     sc.max_depth = s->integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) s->integrator.max_depth;
     sc.rr_depth = s->integrator.rr_depth; sc.hide_emitters = s->integrator.hide_emitters;
@@ -348,6 +349,11 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
         if (p.n_passes != 1) LR_FAIL(c, LR_ERR_UNSUPPORTED, "prbvolpath: W*H*spp exceeds 2^32 lanes");
         if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false, 1>(c, a) : wavefront_render_t<4, false, 1>(c, a);
         return c->film_channels == 5 ? wavefront_render_t<5, true, 1>(c, a) : wavefront_render_t<4, true, 1>(c, a);
+    }
+    if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_BIOVOLPATH && !getenv("LR_BIO_PER_LANE")) {     // LR_BIO_PER_LANE=1: k_render<biovolpath>, the parity probe
+        if (int r = wv_prepare(c, (end - begin))) return r;
+        if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false, 3>(c, a) : wavefront_render_t<4, false, 3>(c, a);
+        return c->film_channels == 5 ? wavefront_render_t<5, true, 3>(c, a) : wavefront_render_t<4, true, 3>(c, a);
     }
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATH) {
         if (int r = wv_prepare(c, (end - begin))) return r;

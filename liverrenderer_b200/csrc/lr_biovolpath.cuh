@@ -107,16 +107,20 @@ LR_DEV BioInteraction bio_sample_interaction(const lr_medium &m, const Ray &ray,
     return mei;
 }
 
-// BioVolumetricPathIntegrator::sample_emitter (biovolpath.cpp:399-531)
-LR_DEV V3 sample_emitter_bio(const DScene &sc, const DTri *tris_gid, const SurfaceInteraction &ref, Sampler &smp, int medium,
-                             uint32_t channel, float tissue_depth, DirectionSample &ds, Counters &cnt) {
-    V3 transmittance = mk3(1.f), emitter_val;
-    ds = sample_emitter_direction(sc, ref.p, smp.next_2d(), emitter_val);
-    if (ds.pdf == 0.f) return mk3(0.f);
-    Ray ray = spawn_ray_to(ref.p, ref.n, ds.p);
+// The walk of BioVolumetricPathIntegrator::sample_emitter (biovolpath.cpp:444-528) along the shadow ray `ray` (maxt = max_dist).
+// `first_hit`: closest hit along the WHOLE shadow segment when a trace stage has already found it (wavefront), else nullptr.  The
+// reference shortens the ray to the sampled free path before it intersects (:476-480), so a hit beyond that distance is not seen
+// -- and, as no later iteration intersects again, never will be: the walk then runs through the boundary to the emitter.  With a
+// precomputed hit that is one comparison.
+LR_DEV V3 bio_nee_walk(const DScene &sc, const DTri *tris_gid, Ray ray, float ds_dist, int medium, uint32_t channel, float tissue_depth,
+                       const Hit *first_hit, Sampler &smp, Counters &cnt) {
+    V3 transmittance = mk3(1.f);
     const float max_dist = ray.maxt;
-    if (mesh_is_transition(sc, ref.mesh)) medium = target_medium(sc, ref, ray.d);
     float total_dist = 0.f; SurfaceInteraction si = invalid_si(); bool needs_intersection = true, active = true;
+    auto isect = [&](const Ray &r) {
+        if (first_hit) { Hit h = *first_hit; first_hit = nullptr; if (!(h.t <= r.maxt)) { h.t = LR_INF; h.prim = 0xffffffffu; } return compute_si(sc, r, h, tris_gid); }
+        return intersect(sc, tris_gid, r, cnt);
+    };
     while (active) {
         const float remaining_dist = max_dist - total_dist;
         ray.maxt = remaining_dist;
@@ -127,7 +131,7 @@ LR_DEV V3 sample_emitter_bio(const DScene &sc, const DTri *tris_gid, const Surfa
             const lr_medium &m = sc.media[medium].m;
             BioInteraction mei = bio_sample_interaction(m, ray, si.t, smp.next_1d(), channel, tissue_depth, true, cnt.collisions);
             if (bio_valid(mei)) ray.maxt = fminf(mei.t, remaining_dist);
-            if (needs_intersection) si = intersect(sc, tris_gid, ray, cnt);
+            if (needs_intersection) si = isect(ray);
             if (si.t < mei.t) mei.t = LR_INF;
             needs_intersection = false;
             if (m.has_spectral_extinction) {
@@ -137,7 +141,7 @@ LR_DEV V3 sample_emitter_bio(const DScene &sc, const DTri *tris_gid, const Surfa
                 float tr_pdf = idx3(ffp, channel);
                 transmittance *= tr_pdf > 0.f ? tr / tr_pdf : mk3(0.f);
             }
-            if (mei.t > remaining_dist && bio_valid(mei)) total_dist = ds.dist;
+            if (mei.t > remaining_dist && bio_valid(mei)) total_dist = ds_dist;
             if (mei.t > remaining_dist) mei.t = LR_INF;
             escaped_medium = !bio_valid(mei); active_medium = bio_valid(mei);
             if (active_medium) {
@@ -145,7 +149,7 @@ LR_DEV V3 sample_emitter_bio(const DScene &sc, const DTri *tris_gid, const Surfa
                 transmittance *= mei.transmittance;                                    // :501-504
             }
         }
-        if (active_surface && needs_intersection) { si = intersect(sc, tris_gid, ray, cnt); needs_intersection = false; }
+        if (active_surface && needs_intersection) { si = isect(ray); needs_intersection = false; }
         active_surface |= escaped_medium;
         if (active_surface) total_dist += si.t;
         active_surface &= si_valid(si) && !active_medium;
@@ -159,7 +163,18 @@ LR_DEV V3 sample_emitter_bio(const DScene &sc, const DTri *tris_gid, const Surfa
         active &= (active_medium || active_surface) && any_nonzero(transmittance);
         if (active_surface && mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
     }
-    return transmittance * emitter_val;
+    return transmittance;
+}
+
+// BioVolumetricPathIntegrator::sample_emitter (biovolpath.cpp:399-531)
+LR_DEV V3 sample_emitter_bio(const DScene &sc, const DTri *tris_gid, const SurfaceInteraction &ref, Sampler &smp, int medium,
+                             uint32_t channel, float tissue_depth, DirectionSample &ds, Counters &cnt) {
+    V3 emitter_val;
+    ds = sample_emitter_direction(sc, ref.p, smp.next_2d(), emitter_val);
+    if (ds.pdf == 0.f) return mk3(0.f);
+    const Ray ray = spawn_ray_to(ref.p, ref.n, ds.p);
+    if (mesh_is_transition(sc, ref.mesh)) medium = target_medium(sc, ref, ray.d);
+    return bio_nee_walk(sc, tris_gid, ray, ds.dist, medium, channel, tissue_depth, nullptr, smp, cnt) * emitter_val;
 }
 
 // biovolpath.cpp:304-305 for one lane: `mei` is the lane's loop-state MediumInteraction

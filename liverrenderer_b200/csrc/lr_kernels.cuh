@@ -271,4 +271,5 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene
 #ifndef LR_LANES_TU
 #include "lr_wavefront.cuh"
 #include "lr_wavefront_prb.cuh"
+#include "lr_wavefront_bio.cuh"
 #endif

@@ -211,6 +211,7 @@ LR_DEV void wv_start_paths(const DScene &sc, const WVArgs &a, bool have, uint64_
         p.res(slot) = make_float4(0.f, 0.f, 0.f, 1.f);
         p.lsp(slot) = make_float4(0.f, 0.f, 0.f, 1.f);
         p.lane(slot) = make_float4(__uint_as_float((uint32_t) lane), __uint_as_float((uint32_t) (lane >> 32)), fp.x, fp.y);
+        if (sc.integ.kind == LR_INTEGRATOR_BIOVOLPATH) p.adj(slot) = make_float4(LR_INF, 0.f, 0.f, 0.f);   // { previous si.t, tissue depth } (lr_wavefront_bio.cuh)
     }
     wv_route(sc, a, slot, keep, f, h);
 }

@@ -394,11 +394,23 @@ def run_b200(args):
             extras["c3xl"] = xl
             # the fork's own rendering model -- biovolpath + tissue media -- on the two scenes whose wall-clock the
             # reference tree records (unstated hardware and variant, so a ratio to them is context, not a comparison)
-            def bio(builder, label, published, cpu_res=135):
+            def bio(builder, label, published, cpu_res=540):
                 spp_b = 256
                 c2 = mi.Context(local).upload(mi.load_dict(builder(res=args.res, spp=spp_b))); c2.set_stream(stream.cuda_stream)
-                ms, st2 = timed_render(torch, c2, stream, barrier, 7, spp_b, 2); c2.close()
-                e = {"value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "spp": spp_b, "mrays_per_s": st2["rays"] / (ms * 1e-3) / 1e6,
+                ms, st2 = timed_render(torch, c2, stream, barrier, 7, spp_b, 2)
+                c2.profile(True); c2.film_clear(); c2.render_lanes(11, spp_b, 0, 0); prof = c2.stage_profile(); c2.profile(False); c2.close()
+                tot = sum(v["ms"] for v in prof.values()) or 1.0
+                stages = {k: {"ms": round(v["ms"], 3), "share": round(v["ms"] / tot, 4), "launches": v["launches"], "items": v["items"],
+                              "Mitems_per_s": round(v["items"] / (v["ms"] * 1e-3) / 1e6, 1) if v["ms"] else None} for k, v in prof.items() if v["launches"] or v["items"]}
+                tr_ms = sum(prof[k]["ms"] for k in ("trace_closest", "trace_shadow") if k in prof); tr_items = sum(prof[k]["items"] for k in ("trace_closest", "trace_shadow") if k in prof)
+                gbs = tr_items * TRACE_BYTES_PER_RAY / (tr_ms * 1e-3) / 1e9 if tr_ms else None
+                e = {"stages": stages, "stage_total_ms": round(tot, 3),
+                     "roofline": {"bound": "hbm", "limiter": "sm_issue", "kernel": "k_wv_trace<0> + k_wv_trace<2>", "share_of_step": round(tr_ms / tot, 4),
+                                  "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak if gbs else None, "traffic": None,
+                                  "algorithmic_bytes_per_unit": TRACE_BYTES_PER_RAY, "mrays_per_s": tr_items / (tr_ms * 1e-3) / 1e6 if tr_ms else None,
+                                  "note": "the TRACE stage is the one the volpath wavefront uses (BVH in shared memory; ncu figures under rooflines[trace_closest]); "
+                                          "per-launch times from CUDA events in profile mode (one batch in flight)"},
+                     "value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "spp": spp_b, "mrays_per_s": st2["rays"] / (ms * 1e-3) / 1e6,
                      "rays_per_sample": st2["rays"] / max(st2["samples"], 1), "kernel": "wavefront biovolpath (lr_wavefront_bio.cuh: GEN, TRACE, k_bio_track / shade_a / nee / shade_b over queues)", "launches": st2.get("launches"), "note": label,
                      "published_reference": {"value": published, "unit": UNIT, "source": "BASELINE.md (1920x1080, 256 spp; hardware and variant not stated)"}}
                 try:

@@ -194,12 +194,14 @@ def _bump_dielectric():
             "bsdf": {"type": "dielectric", "int_ior": 1.38, "ext_ior": 1.0}}
 
 
-def liver_single_mesh_bio(res: int = 1080, spp: int = 256, max_depth: int = 12, sampler: str = "independent"):
+def liver_single_mesh_bio(res: int = 1080, spp: int = 256, max_depth: int = 12, sampler: str = "independent", surface: str = "bumpmap"):
     """Liver-SingleMesh as the fork ships it (scenes/Liver-SingleMesh/mitsuba3/scene.xml): `biovolpath`, one `liver` medium
     inside the bump-mapped dielectric organ, the cavity environment map.  Mesh, bump texture and environment map are this
     repository's synthetic stand-ins (the fork's assets are not redistributable here)."""
     mesh = _liver_mesh("liver2"); mesh["to_world"] = _LIVER_T
     mesh["bsdf"] = _bump_dielectric()
+    if surface == "roughdielectric":      # not the fork's scene: a smooth lobe at the boundary, so that biovolpath's emitter sampling (and its shadow walk
+        mesh["bsdf"] = {"type": "roughdielectric", "int_ior": 1.38, "ext_ior": 1.0, "alpha": 0.3, "distribution": "beckmann"}   # through tissue) is exercised
     mesh["interior"] = {"type": "liver", "scale": 1.0, "phase": {"type": "isotropic"}, **_CAPSULE_PROPS, **_PARENCHYMA_PROPS}
     sensor = _liver_sensor(res, spp); sensor["sampler"]["type"] = sampler
     return {"type": "scene", "integrator": {"type": "biovolpath", "max_depth": max_depth, "rr_depth": 5},

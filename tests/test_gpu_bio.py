@@ -37,8 +37,14 @@ def test_tissue_free_path_sampler_matches_oracle(kind):
     assert same.mean() > 0.9995, same.mean()
 
 
+def _rough(**kw):
+    """Liver-SingleMesh with a rough dielectric boundary: a smooth lobe, so emitter sampling and the shadow walk through tissue run
+    (the fork's own boundaries are delta lobes: no emitter sampling anywhere in its scenes)."""
+    return scenes.liver_single_mesh_bio(surface="roughdielectric", **kw)
+
+
 @pytest.mark.parametrize("builder,sampler", [(scenes.liver_single_mesh_bio, "independent"), (scenes.liver_multi_mesh_bio, "ldsampler"),
-                                             (scenes.liver_multi_mesh_bio, "independent")])
+                                             (scenes.liver_multi_mesh_bio, "independent"), (_rough, "independent")])
 def test_biovolpath_per_path(builder, sampler):
     res, spp = 48, 16
     sc = mi.load_dict(builder(res=res, spp=spp, sampler=sampler)); n = res * res * spp
@@ -101,7 +107,7 @@ def test_biovolpath_lane_partition_is_exact():
     assert np.array_equal(whole, parts)
 
 
-@pytest.mark.parametrize("builder", [scenes.liver_single_mesh_bio, scenes.liver_multi_mesh_bio])
+@pytest.mark.parametrize("builder", [scenes.liver_single_mesh_bio, scenes.liver_multi_mesh_bio, _rough])
 def test_biovolpath_wavefront_equals_per_lane_kernel(builder, monkeypatch):
     """The production path (lr_wavefront_bio.cuh: stage kernels over queues, TRACE stage) and k_render<biovolpath> draw the same
     PCG32 streams in the same order: lane-for-lane equal radiance, equal event counts."""
@@ -130,3 +136,17 @@ def test_biovolpath_wavefront_small_pool_multi_batch(monkeypatch):
     monkeypatch.setenv("LR_WF_SLOTS", "8192")
     small = mi.Context(0).upload(sc).render(seed=2, spp=16)
     assert np.allclose(big, small, rtol=2e-4, atol=1e-6)
+
+
+def test_biovolpath_sample_index_split_adds_up():
+    """SURVEY 8(e) for this row: the frame split by sample index (lr_set_lane_map) -- two half-renders accumulate to the whole one."""
+    res, spp = 32, 16
+    sc = mi.load_dict(scenes.liver_single_mesh_bio(res=res, spp=spp))
+    ctx = mi.Context(0).upload(sc)
+    ctx.film_clear(); ctx.render_lanes(4, spp, 0, 0); whole = ctx.film_read()
+    ctx.film_clear()
+    for r in range(2):
+        ctx.set_lane_map(spp, r * spp // 2, spp // 2); ctx.render_lanes(4, spp, 0, 0)
+    parts = ctx.film_read(); ctx.set_lane_map(0, 0, 0)
+    np.testing.assert_allclose(parts[..., -1], whole[..., -1], rtol=0, atol=0)          # filter weights: exact
+    np.testing.assert_allclose(parts[..., :3], whole[..., :3], rtol=2e-5, atol=1e-6)    # radiance: fp32 atomics in another order

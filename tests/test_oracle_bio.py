@@ -221,9 +221,13 @@ def _scene(builder, res=24, spp=8, **kw):
     return Scene(builder(res=res, spp=spp, **kw))
 
 
-@pytest.mark.parametrize("builder", [scenes.liver_single_mesh_bio, scenes.liver_multi_mesh_bio])
+def _rough(**kw):
+    return scenes.liver_single_mesh_bio(surface="roughdielectric", **kw)
+
+
+@pytest.mark.parametrize("builder", [scenes.liver_single_mesh_bio, scenes.liver_multi_mesh_bio, _rough])
 def test_biovolpath_lane_properties(builder):
-    sc = _scene(builder); o = orc.OracleScene(sc); n = 24 * 24 * 8
+    sc = Scene(builder(res=24, spp=8)); o = orc.OracleScene(sc); n = 24 * 24 * 8
     L = o.sample_lanes(0, 8, 0, n)
     assert np.array_equal(L, orc.OracleScene(sc, threads=1).sample_lanes(0, 8, 0, n))     # lanes are independent
     assert np.isfinite(L).all() and np.all(L[:, :3] >= 0) and np.all(L[:, 3] == 1)
@@ -234,6 +238,8 @@ def test_biovolpath_lane_properties(builder):
     # interacted), one (its own channel) or none (absorbed / cleared in the iteration it died in) -- never two
     live = (L[:, :3] > 0).sum(1)
     assert (live == 2).sum() == 0 and (live == 1).mean() > 0.03 and (live == 0).mean() > 0.05 and (live == 3).mean() > 0.3
+    if builder is _rough:               # emitter sampling ran, and some shadow rays started inside the tissue (a draw per interaction)
+        assert st["collisions"] > st["real_scatters"] * 1.05
 
 
 def test_biovolpath_uses_the_stale_surface_distance():

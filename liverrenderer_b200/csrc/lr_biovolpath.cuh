@@ -195,7 +195,7 @@ LR_DEV void bio_apply_transmittance(const BioInteraction &mei, int medium, V3 &r
 //      active = false -- and :304 zeroes `result` per channel where that interaction's transmittance is 0.
 // The loop is written as a resumable path: init() + one step() per iteration of the reference's loop (the unit a wavefront port
 // would cut at).  Handing a finished lane a new path between steps was tried and bought nothing (0.98x / 0.88x on the two liver
-// scenes): the idle lanes of k_render<biovolpath> -- 8 of 32 threads active per instruction, profiles/r2_kernel_metrics_single.txt --
+// scenes): the idle lanes of k_render<biovolpath> -- 8 of 32 threads active per instruction, profiles/r2_kernel_metrics_bio_per_lane.txt --
 // sit inside a step (BVH walks and shadow walks of different lengths), not behind a long path.
 struct BioPath {
     Sampler smp; Ray ray; V3 throughput, result, last_scatter_p;

@@ -338,6 +338,10 @@ int  lr_render_lanes(lr_ctx *ctx, uint32_t seed, uint32_t spp,
    spp / N, offset = rank * len gives each of N devices spp / N samples of every pixel (perfectly balanced); PCG32 streams
    stay keyed by the global lane, so the sum of the devices' films is the single-device film.  len = 0 removes the map.   */
 int  lr_set_lane_map(lr_ctx *ctx, uint64_t period, uint64_t offset, uint64_t len);
+/* Render the uploaded scene through another of its sensors: the `sensor_index` argument of SamplingIntegrator::render
+   (src/render/integrator.cpp:33-44, include/mitsuba/render/integrator.h:89).  Replaces camera, film window, reconstruction filter and the
+   sensor's medium; everything else of the upload stays.  The film accumulator is re-created and zeroed.                                  */
+int  lr_sensor_set(lr_ctx *ctx, const lr_sensor *sensor);
 int  lr_film_channels(const lr_ctx *ctx);
 int  lr_film_read(lr_ctx *ctx, float *block, int is_device);
 int  lr_film_write(lr_ctx *ctx, const float *block, int is_device);

@@ -67,6 +67,9 @@ def render(scene: Scene, params=None, sensor=0, integrator=None, seed: int = 0, 
     if params is not None and hasattr(params, "update"):
         params.update()
     ctx = _context_for(scene, device)
+    if not isinstance(sensor, int):
+        raise NotImplementedError("mi.render: `sensor` is the index of one of the scene's sensors on this path")
+    ctx.set_sensor(sensor)
     return ctx.render(seed=seed, spp=spp or scene.spp, out=out)
 
 

@@ -120,7 +120,7 @@ API_SYMBOLS = [
     "lr_api_version", "lr_create", "lr_destroy", "lr_last_error", "lr_scene_upload", "lr_render", "lr_film_clear",
     "lr_render_lanes", "lr_film_channels", "lr_film_read", "lr_film_write", "lr_film_develop", "lr_film_device_ptr",
     "lr_sample_lanes", "lr_render_backward", "lr_grid_update", "lr_grid_grad_zero", "lr_grid_grad_read",
-    "lr_grid_grad_device_ptr", "lr_grid_size", "lr_set_lane_map", "lr_ray_intersect", "lr_ray_intersect_noalloc", "lr_noalloc_max_rays", "lr_cancel", "lr_stats_get", "lr_set_stream",
+    "lr_grid_grad_device_ptr", "lr_grid_size", "lr_set_lane_map", "lr_sensor_set", "lr_ray_intersect", "lr_ray_intersect_noalloc", "lr_noalloc_max_rays", "lr_cancel", "lr_stats_get", "lr_set_stream",
     "lr_profile_enable", "lr_profile_get", "lr_stage_name",
     "lr_kat_bsdf_eval_pdf", "lr_kat_bsdf_sample", "lr_kat_phase", "lr_kat_grid_eval", "lr_kat_emitter_sample", "lr_kat_env_eval_pdf",
     "lr_kat_tissue",
@@ -177,6 +177,7 @@ def load_library(path: str | None = None):
     lib.lr_kat_grid_eval.argtypes = [vp, C.c_uint32, vp, C.c_uint64, vp, C.c_int]; lib.lr_kat_grid_eval.restype = C.c_int
     lib.lr_kat_emitter_sample.argtypes = [vp, vp, C.c_uint64, vp]; lib.lr_kat_emitter_sample.restype = C.c_int
     lib.lr_kat_env_eval_pdf.argtypes = [vp, vp, C.c_uint64, vp]; lib.lr_kat_env_eval_pdf.restype = C.c_int
+    lib.lr_sensor_set.argtypes = [vp, C.POINTER(lr_sensor)]; lib.lr_sensor_set.restype = C.c_int
     lib.lr_kat_tissue.argtypes = [vp, C.POINTER(lr_medium), vp, C.c_uint64, vp]; lib.lr_kat_tissue.restype = C.c_int
     if path is None:
         _LIB = lib

@@ -81,14 +81,25 @@ class Context:
     def upload(self, scene: Scene):
         pod = scene.pod()
         self._chk(self.lib.lr_scene_upload(self.ctx, C.byref(pod)), "lr_scene_upload")
-        self.scene = scene
+        self.scene = scene; self._sensor_index = scene.sensor_index
         return self
 
     def set_stream(self, cuda_stream_ptr: int):
         self._chk(self.lib.lr_set_stream(self.ctx, C.c_void_p(cuda_stream_ptr)), "lr_set_stream")
 
     # -- forward ---------------------------------------------------------------
-    def render(self, seed: int = 0, spp: int | None = None, out=None):
+    def set_sensor(self, index: int):
+        """lr_sensor_set: render the uploaded scene through another of its sensors (the `sensor` argument of mi.render)."""
+        sc = self.scene
+        if index != sc.sensor_index:
+            sc.select_sensor(index)
+        if index != self._sensor_index:
+            self._chk(self.lib.lr_sensor_set(self.ctx, C.byref(sc.sensors[index])), "lr_sensor_set")
+            self._sensor_index = index
+
+    def render(self, seed: int = 0, spp: int | None = None, out=None, sensor: int | None = None):
+        if sensor is not None:
+            self.set_sensor(sensor)
         sc = self.scene; W, H = sc.film_size; spp = spp or sc.spp
         if out is None:
             out = np.empty((H, W, sc.out_channels), dtype=np.float32)

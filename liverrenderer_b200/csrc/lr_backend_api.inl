@@ -82,7 +82,9 @@ int lr_scene_upload(lr_ctx *c, const lr_scene *s) {
     sc.max_depth = s->integrator.max_depth < 0 ? 0xffffffffu : (uint32_t) s->integrator.max_depth;
     sc.rr_depth = s->integrator.rr_depth; sc.hide_emitters = s->integrator.hide_emitters;
     if (s->sensor.rfilter == LR_RFILTER_GAUSSIAN) gaussian_coeffs(s->sensor.rfilter_stddev, s->sensor.rfilter_radius, sc.gauss_coeff);
-    if (s->sensor.rfilter_radius > 2.5f) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: reconstruction filter radius > 2.5 px is outside the hot path");
+    if (s->sensor.rfilter_radius > 7.5f) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: reconstruction filter radius > 7.5 px is outside the hot path");
+    if (s->sensor.rfilter_radius > 2.5f && s->sensor.rfilter != LR_RFILTER_BOX && s->integrator.kind == LR_INTEGRATOR_PRBVOLPATH)
+        LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_scene_upload: prbvolpath gathers dL/dI through the 6-tap footprint: reconstruction filter radius > 2.5 px is not supported by the adjoint");
     LR_CUDA(c, c->scratch.alloc(256));
 
     // ---- meshes: concatenate triangles (gid order), upload per-mesh attribute arrays ----
@@ -369,6 +371,39 @@ static int copy_out(lr_ctx *c, void *dst, const void *src_dev, size_t bytes, int
 }
 
 extern "C" {
+
+// Scene::sensors()[i]: SamplingIntegrator::render(scene, sensor_index, ...) (src/render/integrator.cpp:33-44) picks one of the scene's
+// sensors per call.  Geometry, media, emitters and the acceleration structure stay as uploaded; only the camera, film window, reconstruction
+// filter and the sensor's medium change.  The film accumulator is re-created (zeroed) for the new sensor's size.
+int lr_sensor_set(lr_ctx *c, const lr_sensor *sn) {
+    if (!c || !sn) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_sensor_set: NULL argument");
+    if (!c->has_scene) LR_FAIL(c, LR_ERR_NO_SCENE, "lr_sensor_set: no scene uploaded");
+    if (sn->film_width == 0 || sn->film_height == 0) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_sensor_set: empty film");
+    if (sn->rfilter_radius > 7.5f) LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_sensor_set: reconstruction filter radius > 7.5 px is outside the hot path");
+    if (sn->rfilter_radius > 2.5f && sn->rfilter != LR_RFILTER_BOX && c->sc.integ.kind == LR_INTEGRATOR_PRBVOLPATH)
+        LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_sensor_set: prbvolpath gathers dL/dI through the 6-tap footprint: reconstruction filter radius > 2.5 px is not supported by the adjoint");
+    if (sn->medium >= (int) c->h_media.size()) LR_FAIL(c, LR_ERR_INVALID_ARG, "lr_sensor_set: sensor medium %d out of range", sn->medium);
+    if (sn->medium >= 0 && (c->h_media[sn->medium].m.kind >= LR_MEDIUM_LIVER) != (c->sc.integ.kind == LR_INTEGRATOR_BIOVOLPATH))
+        LR_FAIL(c, LR_ERR_UNSUPPORTED, "lr_sensor_set: the sensor's medium does not go with the scene's integrator");
+    LR_CUDA(c, cudaSetDevice(c->device));
+    LR_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (sn->medium >= 0 && c->h_media[sn->medium].sealed) {          // a medium that contains the sensor is not sealed (seal_media)
+        c->h_media[sn->medium].sealed = 0;
+        LR_CUDA(c, cudaMemcpyAsync(c->d_media->p, c->h_media.data(), c->h_media.size() * sizeof(DMedium), cudaMemcpyHostToDevice, c->stream));
+    }
+    DScene &sc = c->sc; sc.sensor = *sn;
+    mat_copy(sc.cam_to_world, sn->to_world); mat_copy(sc.sample_to_camera, sn->sample_to_camera);
+    if (sn->rfilter == LR_RFILTER_GAUSSIAN) gaussian_coeffs(sn->rfilter_stddev, sn->rfilter_radius, sc.gauss_coeff);
+    const int ch = sn->has_alpha ? 5 : 4;
+    if (c->W != sn->film_width || c->H != sn->film_height || c->film_channels != ch) {
+        c->W = sn->film_width; c->H = sn->film_height; c->film_channels = ch;
+        LR_CUDA(c, c->film.alloc((size_t) c->W * c->H * c->film_channels * 4));
+        LR_CUDA(c, c->weight_img.alloc((size_t) c->W * c->H * 4));
+    }
+    LR_CUDA(c, cudaMemsetAsync(c->film.p, 0, c->film.bytes, c->stream));
+    LR_CUDA(c, cudaStreamSynchronize(c->stream));
+    return LR_OK;
+}
 
 int lr_film_clear(lr_ctx *c) {
     if (!c || !c->has_scene) return LR_ERR_NO_SCENE;

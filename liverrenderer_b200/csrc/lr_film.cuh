@@ -52,9 +52,41 @@ LR_DEV bool film_footprint(const DScene &sc, V2 pos, bool coalesce, Footprint &f
     return true;
 }
 
+// Filters wider than the 6-tap footprint (radius > 2.5 px, e.g. a gaussian with stddev 1): the same two windows of ImageBlock::put with the
+// separable weights evaluated inside the loops instead of being kept in registers -- the narrow filters of the configured scenes keep their code.
+template <int C>
+LR_DEV void film_put_wide(const DScene &sc, float *film, V2 pos, const float *values, bool coalesce) {
+    const int W = (int) sc.sensor.film_width, H = (int) sc.sensor.film_height; const float radius = sc.sensor.rfilter_radius;
+    int x0, y0, nx, ny; float rx0, ry0;
+    if (coalesce) {                                                // imageblock.cpp:431-455
+        const int n = (int) ceilf(radius - .5f); nx = ny = 2 * n + 1;
+        x0 = (int) floorf(pos.x) - n; y0 = (int) floorf(pos.y) - n;
+        rx0 = __fsub_rn(__fadd_rn((float) x0, .5f), pos.x); ry0 = __fsub_rn(__fadd_rn((float) y0, .5f), pos.y);
+    } else {                                                       // :262-275
+        const float pfx = pos.x - .5f, pfy = pos.y - .5f;
+        x0 = max((int) ceilf(pfx - radius), 0); y0 = max((int) ceilf(pfy - radius), 0);
+        const int x1 = min((int) floorf(pfx + radius), W - 1), y1 = min((int) floorf(pfy + radius), H - 1);
+        if (x0 > x1 || y0 > y1) return;
+        nx = x1 - x0 + 1; ny = y1 - y0 + 1; rx0 = (float) x0 - pfx; ry0 = (float) y0 - pfy;
+    }
+    float ry = ry0;
+    for (int j = 0; j < ny; ++j, ry += 1.f) {
+        const int y = y0 + j; if (y < 0 || y >= H) continue;
+        const float wy = rfilter_eval(sc, ry); float rx = rx0;
+        for (int i = 0; i < nx; ++i, rx += 1.f) {
+            const int x = x0 + i; if (x < 0 || x >= W) continue;
+            const float w = __fmul_rn(wy, rfilter_eval(sc, rx));
+            float *dst = film + ((size_t) y * W + x) * C;
+#pragma unroll
+            for (int k = 0; k < C; ++k) atomicAdd(dst + k, __fmul_rn(values[k], w));
+        }
+    }
+}
+
 // ImageBlock::accum -> fire-and-forget fp32 reductions into L2 (RED.E.ADD.F32)
 template <int C>
 LR_DEV void film_put(const DScene &sc, float *film, V2 pos, const float *values, bool coalesce) {
+    if (sc.sensor.rfilter != LR_RFILTER_BOX && sc.sensor.rfilter_radius > 2.5f) { film_put_wide<C>(sc, film, pos, values, coalesce); return; }
     Footprint fp; if (!film_footprint(sc, pos, coalesce, fp)) return;
     const int W = (int) sc.sensor.film_width, H = (int) sc.sensor.film_height;
     for (int j = 0; j < fp.ny; ++j) {

@@ -127,7 +127,7 @@ class Scene:
             elif t in ("constant", "envmap"):
                 self._add_env(v)
             elif t == "perspective":
-                self._sensor_dict = v
+                self._sensor_dicts = getattr(self, "_sensor_dicts", []) + [v]
             elif t in ("path", "volpath", "prbvolpath", "biovolpath", "volpathmis"):
                 self._integrator_dict = v
             elif t in ("biovolpath06", "direct", "aov", "moment", "ptracer", "stokes", "depth",
@@ -141,11 +141,25 @@ class Scene:
                                           "perspective, path/volpath/volpathmis/prbvolpath/biovolpath, rectangle/cube/sphere/obj/mesh, constant/envmap, "
                                           "diffuse/roughdielectric/principled/null/dielectric/bumpmap, homogeneous/heterogeneous, "
                                           "liver/glissonCapsule/parenchyma")
-        if not hasattr(self, "_sensor_dict"):
+        if not hasattr(self, "_sensor_dicts"):
             raise ValueError("scene has no 'perspective' sensor")
-        self._build_sensor(self._sensor_dict)
+        # Scene::sensors(): every sensor of the scene, in order; render(scene, sensor=i) picks one (src/render/integrator.cpp:33-44)
+        self.sensors, self._sensor_spp = [], []
+        for v in self._sensor_dicts:
+            kind0, seed0 = getattr(self, "sampler_kind", None), getattr(self, "base_seed", None)
+            self._build_sensor(v)
+            if kind0 is not None and (kind0 != self.sampler_kind or seed0 != self.base_seed):
+                raise NotImplementedError("the sensors of one scene must share the sampler plugin and its seed on this path")
+            self.sensors.append(self.sensor); self._sensor_spp.append(self.spp)
+        self.select_sensor(0)
         self._build_integrator(getattr(self, "_integrator_dict", {"type": "path"}))
         self._ctx = None
+
+    def select_sensor(self, index: int):
+        """Make sensor `index` the one film_size / spp / pod() describe (the backend is told by Context.render(sensor=...))."""
+        if not 0 <= index < len(self.sensors):
+            raise RuntimeError(f"Scene::render(): sensor index {index} is out of bounds!")
+        self.sensor_index = index; self.sensor = self.sensors[index]; self.spp = self._sensor_spp[index]
 
     # ---- BSDFs ------------------------------------------------------------
     def _resolve_bsdf(self, v):

@@ -62,7 +62,7 @@ struct Film {
    ImageBlock::put (src/render/imageblock.cpp:174-560), JIT semantics:
    box fast path (:206-235); coalesced window when spp >= 4 (:431-455);
    else the clipped radius window (:262-275). `count` <= 5 on this path. */
-struct Footprint { int x0, y0, nx, ny; float wx[8], wy[8]; };
+struct Footprint { int x0, y0, nx, ny; float wx[16], wy[16]; };    /* radius <= 7.5 px */
 inline bool film_footprint(const Scene &sc, V2 pos, bool coalesce, Footprint &fp) {
     const lr_sensor &s = sc.sensor; int W = (int) s.film_width, H = (int) s.film_height;
     if (s.rfilter == LR_RFILTER_BOX) {

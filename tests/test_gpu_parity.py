@@ -445,3 +445,26 @@ def test_cancel_from_another_thread():
     assert "err" in res and "status -6" in res["err"] and "cancel" in res["err"].lower(), res
     assert res["t"] - tc < 0.5 * full + 0.05, (res["t"] - tc, full)                  # stopped early, not after finishing the frame
     ctx.film_clear(); ctx.render_lanes(3, 1, 0, 0); assert ctx.stats()["samples"] == 1080 * 1080
+
+
+def test_second_sensor_and_wide_gaussian_filter():
+    """`render(scene, sensor=1)` (integrator.cpp:33-44) through lr_sensor_set, and a reconstruction filter wider than the 6-tap footprint
+    (gaussian, stddev 1 => radius 4 px, 9 x 9 taps): the film of each sensor equals the oracle's film of a scene holding only that sensor."""
+    d = scenes.cornell_box_path(res=24, spp=16)
+    d["sensor2"] = dict(d["sensor"]); d["sensor2"]["fov"] = 25.0
+    d["sensor2"]["film"] = {"type": "hdrfilm", "width": 32, "height": 20, "rfilter": {"type": "gaussian", "stddev": 1.0}, "pixel_format": "rgba"}
+    sc = mi.load_dict(d); ctx = mi.Context(0).upload(sc)
+    img0 = ctx.render(seed=1, spp=16, sensor=0); img1 = ctx.render(seed=1, spp=16, sensor=1); img0b = ctx.render(seed=1, spp=16, sensor=0)
+    assert img0.shape == (24, 24, 3) and img1.shape == (20, 32, 4) and np.allclose(img0, img0b, rtol=1e-5, atol=1e-7)    # fp32 atomics in another order
+    for idx, img in ((0, img0), (1, img1)):
+        one = dict(d); one["sensor"] = d["sensor" if idx == 0 else "sensor2"]; one.pop("sensor2")
+        o = orc.OracleScene(mi.load_dict(one)); o.render(1, 16); ref = o.film_develop()
+        assert ref.shape == img.shape
+        close = np.isclose(img, ref, rtol=2e-3, atol=1e-5).all(-1)
+        assert close.mean() > 0.97, (idx, close.mean())
+    with pytest.raises(RuntimeError, match="out of bounds"):
+        ctx.render(seed=1, spp=16, sensor=2)
+    # spp < 4: the clipped (non-coalesced) window of ImageBlock::put, wide filter
+    a = ctx.render(seed=2, spp=1, sensor=1); one = dict(d); one["sensor"] = d["sensor2"]; one.pop("sensor2")
+    o = orc.OracleScene(mi.load_dict(one)); o.render(2, 1); ref = o.film_develop()
+    assert np.isclose(a, ref, rtol=2e-3, atol=1e-5).all(-1).mean() > 0.97

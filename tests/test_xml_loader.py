@@ -153,3 +153,20 @@ def test_unknown_top_level_plugin_raises():
     for extra in ({"type": "point", "intensity": 1.0}, {"type": "ply", "filename": "x.ply"}, {"type": "plastic"}):
         with pytest.raises(NotImplementedError, match=extra["type"]):
             mi.load_dict(dict(base, thing=extra))
+
+
+def test_scene_with_two_sensors_and_wide_filter():
+    """Scene::sensors(): every `perspective` of the scene is kept, in order; render(scene, sensor=i) picks one."""
+    from liverrenderer_b200 import scenes
+    d = scenes.cornell_box_path(res=16, spp=4)
+    d["sensor2"] = dict(d["sensor"]); d["sensor2"]["film"] = {"type": "hdrfilm", "width": 24, "height": 12, "rfilter": {"type": "gaussian", "stddev": 1.0}}
+    d["sensor2"]["fov"] = 25.0
+    sc = mi.load_dict(d)
+    assert len(sc.sensors) == 2 and sc.film_size == (16, 16) and sc.sensor_index == 0
+    sc.select_sensor(1)
+    assert sc.film_size == (24, 12) and abs(sc.sensor.rfilter_radius - 4.0) < 1e-6
+    with pytest.raises(RuntimeError, match="out of bounds"):
+        sc.select_sensor(2)
+    d["sensor2"]["sampler"] = {"type": "ldsampler", "sample_count": 4}
+    with pytest.raises(NotImplementedError, match="share the sampler"):
+        mi.load_dict(d)

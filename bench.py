@@ -422,15 +422,15 @@ def run_b200(args):
                 except Exception as ex:                                   # the oracle is the checker, never a dependency of the measured arm
                     e["cpu_baseline"] = {"unavailable": str(ex)[:120]}
                 return e
-            # SURVEY.md 8(f) rank 4 (first half): volpathmis on the C3 frame.  One lane per thread, global-majorant tracking in the reference's
-            # draw order; the comparable volpath figure is extras.reference_order_tracking (wavefront).  16 spp: the kernel is ~30x slower.
+            # SURVEY.md 8(f) rank 4 (first half): volpathmis on the C3 frame, wavefront, global-majorant tracking in the reference's draw order
+            # (it has no production-tracking variant); the comparable volpath figure is extras.reference_order_tracking.
             def mis(spectral):
-                dd = _sc.liver_single_mesh(res=args.res, spp=16, grid_res=256, tracking="reference")
+                dd = _sc.liver_single_mesh(res=args.res, spp=64, grid_res=256, tracking="reference")
                 dd["integrator"] = {"type": "volpathmis", "max_depth": 12, "rr_depth": 5, "use_spectral_mis": spectral}
                 c2 = mi.Context(local).upload(mi.load_dict(dd)); c2.set_stream(stream.cuda_stream)
-                ms, st2 = timed_render(torch, c2, stream, barrier, 7, 16, 1); c2.close()
-                return {"value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "spp": 16, "collisions_per_sample": st2["collisions"] / max(st2["samples"], 1),
-                        "collisions_per_s": st2["collisions"] / (ms * 1e-3), "kernel": "k_render<volpathmis> (one lane per thread: a warp waits for its longest path)",
+                ms, st2 = timed_render(torch, c2, stream, barrier, 7, 64, 1); c2.close()
+                return {"value": st2["samples"] / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "spp": 64, "collisions_per_sample": st2["collisions"] / max(st2["samples"], 1),
+                        "collisions_per_s": st2["collisions"] / (ms * 1e-3), "kernel": "wavefront volpathmis (lr_wavefront_mis.cuh: k_mis_track / shade_a / nee / shade_b over queues, TRACE stage; 128 B of p / f state per path)", "launches": st2.get("launches"),
                         "note": f"C3 frame under volpathmis, use_spectral_mis = {str(spectral).lower()} (volpathmis.cpp:79)"}
             extras["volpathmis_c3"] = mis(True)
             extras["volpathmis_c3_plain_mis"] = mis(False)

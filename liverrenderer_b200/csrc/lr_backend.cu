@@ -30,7 +30,7 @@ struct DevBuf {
 // iterations write their live counts to
 struct WVRing { uint32_t live; uint32_t pad; unsigned long long lane_next; };
 struct WVPool {
-    DevBuf planes, queues, counters, trace_ovf; uint32_t cap = 0;
+    DevBuf planes, queues, counters, trace_ovf, mis; uint32_t cap = 0;      // mis: 128 B per slot of p / f state, volpathmis scenes only
     WVRing *ring_host = nullptr, *ring_dev = nullptr; std::vector<cudaEvent_t> ring_ev;
     ~WVPool() { if (ring_host) cudaFreeHost(ring_host); for (auto e : ring_ev) cudaEventDestroy(e); }
 };

@@ -357,6 +357,16 @@ static int render_lanes_impl(lr_ctx *c, uint32_t seed, uint32_t spp, uint64_t be
         if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false, 3>(c, a) : wavefront_render_t<4, false, 3>(c, a);
         return c->film_channels == 5 ? wavefront_render_t<5, true, 3>(c, a) : wavefront_render_t<4, true, 3>(c, a);
     }
+    if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATHMIS && !getenv("LR_MIS_PER_LANE")) {    // LR_MIS_PER_LANE=1: k_render<volpathmis>, the parity probe
+        if (int r = wv_prepare(c, (end - begin))) return r;
+        const bool s5 = c->film_channels == 5;
+        if (c->sc.integ.spectral_mis) {
+            if (lanes_out) return s5 ? wavefront_render_t<5, false, 4>(c, a) : wavefront_render_t<4, false, 4>(c, a);
+            return s5 ? wavefront_render_t<5, true, 4>(c, a) : wavefront_render_t<4, true, 4>(c, a);
+        }
+        if (lanes_out) return s5 ? wavefront_render_t<5, false, 5>(c, a) : wavefront_render_t<4, false, 5>(c, a);
+        return s5 ? wavefront_render_t<5, true, 5>(c, a) : wavefront_render_t<4, true, 5>(c, a);
+    }
     if (c->use_wavefront && c->sc.integ.kind == LR_INTEGRATOR_VOLPATH) {
         if (int r = wv_prepare(c, (end - begin))) return r;
         if (lanes_out) return c->film_channels == 5 ? wavefront_render_t<5, false>(c, a) : wavefront_render_t<4, false>(c, a);

@@ -272,4 +272,5 @@ __global__ void __launch_bounds__(128) k_backward(const __grid_constant__ DScene
 #include "lr_wavefront.cuh"
 #include "lr_wavefront_prb.cuh"
 #include "lr_wavefront_bio.cuh"
+#include "lr_wavefront_mis.cuh"
 #endif

@@ -73,6 +73,7 @@ struct WVArgs {
     uint64_t lane_begin, lane_end; unsigned long long *lane_next;      // lane cursor shared by all batches of one render call
     uint32_t seed, spp_per_pass, n_passes;
     unsigned long long *stats; LaneMap map;
+    float4 *mis;                                                       // volpathmis: eight 16-byte records per slot (lr_wavefront_mis.cuh), else nullptr
 };
 
 LR_DEV Sampler wv_rng(const WVPlanes &p, uint32_t s) { const ulonglong2 r = p.rng(s); Sampler m; m.state = r.x; m.inc = r.y; return m; }
@@ -212,6 +213,11 @@ LR_DEV void wv_start_paths(const DScene &sc, const WVArgs &a, bool have, uint64_
         p.lsp(slot) = make_float4(0.f, 0.f, 0.f, 1.f);
         p.lane(slot) = make_float4(__uint_as_float((uint32_t) lane), __uint_as_float((uint32_t) (lane >> 32)), fp.x, fp.y);
         if (sc.integ.kind == LR_INTEGRATOR_BIOVOLPATH) p.adj(slot) = make_float4(LR_INF, 0.f, 0.f, 0.f);   // { previous si.t, tissue depth } (lr_wavefront_bio.cuh)
+        if (sc.integ.kind == LR_INTEGRATOR_VOLPATHMIS) {                                                     // p_over_f = p_over_f_nee = 1 (lr_wavefront_mis.cuh)
+            float4 *m = a.mis + (size_t) slot * 8u;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) m[k] = make_float4(1.f, 1.f, 1.f, 0.f);
+        }
     }
     wv_route(sc, a, slot, keep, f, h);
 }

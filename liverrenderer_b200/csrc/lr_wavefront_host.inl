@@ -22,6 +22,7 @@ static int wv_alloc(lr_ctx *c, WVPool *&wp, uint64_t want) {
         LR_CUDA(c, w.queues.alloc((size_t) w.cap * 4 * WV_N_QUEUES));
         LR_CUDA(c, w.counters.alloc(sizeof(WVQueues)));
     }
+    if (c->sc.integ.kind == LR_INTEGRATOR_VOLPATHMIS && w.mis.bytes < (size_t) w.cap * 128) LR_CUDA(c, w.mis.alloc((size_t) w.cap * 128));
     {   // stack entries beyond the shared-memory part of the trace kernels' stacks (one column per resident thread)
         const size_t need = (size_t) c->n_sm * LR_TRACE_THREADS * std::max<uint32_t>(c->sc.bvh4_stack > c->trace_sd ? c->sc.bvh4_stack - c->trace_sd : 0u, 1u) * sizeof(int);
         if (w.trace_ovf.bytes < need) LR_CUDA(c, w.trace_ovf.alloc(need));
@@ -58,7 +59,7 @@ static void wv_bind(WVArgs &a, WVPool &w) {
     char *pb = (char *) w.planes.p; const size_t u = (size_t) w.cap * 16;           // 16-byte units per slot: h0 2, h1 2, h2 2, hit 1, lane 1, n0 2, n1 2
     a.p.h0 = (float4 *) pb; a.p.h1 = (float4 *) (pb + 2 * u); a.p.h2 = (float4 *) (pb + 4 * u); a.p.hit_ = (float4 *) (pb + 6 * u); a.p.lane_ = (float4 *) (pb + 7 * u);
     a.p.n0 = (float4 *) (pb + 8 * u); a.p.n1 = (float4 *) (pb + 10 * u); a.p.adj_ = (float4 *) (pb + 12 * u);
-    a.q = w.counters.as<WVQueues>(); a.cap = w.cap;
+    a.q = w.counters.as<WVQueues>(); a.cap = w.cap; a.mis = w.mis.as<float4>();
     uint32_t *qb = w.queues.as<uint32_t>(); const size_t qs = w.cap;
     a.q_trace = qb; a.q_track = qb + qs; a.q_scatter = qb + 2 * qs; a.q_escape = qb + 3 * qs; a.q_shadow = qb + 4 * qs; a.q_nee = qb + 5 * qs; a.q_regen = qb + 6 * qs;
     for (int b = 0; b < WF_N_SURF; ++b) a.q_surf[b] = qb + (7 + b) * qs;
@@ -77,10 +78,10 @@ struct WvRun {
 // depend on the batching.  The host never waits for an iteration it has just enqueued: the live count of iteration i is written
 // to mapped pinned memory by the iteration itself and checked WF_LAG iterations later.
 // MODE 0: volpath (lr_wavefront.cuh); 1: prbvolpath primal, 2: prbvolpath adjoint replay (lr_wavefront_prb.cuh); 3: biovolpath
-// (lr_wavefront_bio.cuh: no medium SHADE stages) -- the same stage sequence, queues, pools and TRACE kernels; the stage kernels differ.
+// (lr_wavefront_bio.cuh: no medium SHADE stages); 4 / 5: volpathmis with / without spectral MIS (lr_wavefront_mis.cuh) -- the same stage sequence, queues, pools and TRACE kernels; the stage kernels differ.
 template <int C, bool TO_FILM, int MODE = 0>
 static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs pa = WFPrbArgs{}) {
-    constexpr bool ADJ = MODE == 2;
+    constexpr bool ADJ = MODE == 2, MIS = MODE == 4 || MODE == 5, SMIS = MODE == 4;
     const uint64_t cap = c->wv[0]->cap, n_lanes = ra.lane_end - ra.lane_begin;
     const bool prof = c->profile_on;
     WvRun runs[4]; int n_runs = 0;
@@ -100,9 +101,10 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
     if (n_runs > 1) { LR_CUDA(c, cudaEventRecord(c->fork_ev, c->stream)); for (int k = 1; k < n_runs; ++k) LR_CUDA(c, cudaStreamWaitEvent(runs[k].s, c->fork_ev, 0)); }
     const uint32_t surf_mask = c->surf_bucket_mask;                    // surface buckets present in this scene
     const int grid = c->n_sm * c->wf_grid_mult, grid128 = c->n_sm * c->wf_grid_mult128, grid_tr = c->n_sm;      // trace: one block of LR_TRACE_THREADS per SM
+    const int grid_mis = c->n_sm * LR_MIS_OCC, grid128_mis = c->n_sm * 2 * LR_MIS_OCC;       // the volpathmis stage kernels are compiled for 128 registers
     const bool stk16 = c->bvh4_small; const size_t smem_tr = c->trace_smem;
     const bool multipass = ra.n_passes > 1;
-    const int shadow_mode = (MODE != 3 && c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf && !getenv("LR_SHADOW_CLOSEST")) ? 1 : 2;   // LR_SHADOW_CLOSEST: A/B of the any-hit query
+    const int shadow_mode = (MODE < 3 && c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf && !getenv("LR_SHADOW_CLOSEST")) ? 1 : 2;   // LR_SHADOW_CLOSEST: A/B of the any-hit query
     uint64_t launches = 0; bool lanes_done = false; const bool dbg_sync = getenv("LR_WF_SYNC") != nullptr;
     // per-stage CUDA events (profile mode: one batch in flight, so the intervals do not overlap)
     std::vector<cudaEvent_t> &kev = c->prof_ev; size_t kev_used = 0; std::vector<int> kev_kind;
@@ -135,7 +137,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
         // GEN hands out lanes while n_alloc + slack <= cap; slack = 32 slots per resident warp of the GEN grid bounds the overshoot
         r.gen_grid = (int) std::max<uint64_t>(1, std::min<uint64_t>((uint64_t) grid, a.cap / 512)); a.slack = (uint32_t) r.gen_grid * 256u;
         k_wv_init<<<1, 1, 0, r.s>>>(a.q); ++launches;
-        launch(r, ST_GEN, [&] { if constexpr (MODE == 0 || MODE == 3) k_wv_gen<C, TO_FILM><<<r.gen_grid, 256, 0, r.s>>>(c->sc, a);
+        launch(r, ST_GEN, [&] { if constexpr (MODE == 0 || MODE >= 3) k_wv_gen<C, TO_FILM><<<r.gen_grid, 256, 0, r.s>>>(c->sc, a);
                                 else k_wvp_gen<C, TO_FILM, ADJ><<<r.gen_grid, 256, 0, r.s>>>(c->sc, a, pa); });
         r.iter = 0; r.busy = true;
         return readback(r);
@@ -149,31 +151,38 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
             if (w.ring_host[slot].live == 0 || *c->cancel_host) { r.busy = false; return 1; }
         }
         launch(r, ST_TRACK, [&] { if constexpr (MODE == 3) k_bio_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a);
+                                  else if constexpr (MIS) k_mis_track<C, TO_FILM, SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                   else if constexpr (MODE != 0) { if (c->all_media_dda && !getenv("LR_PRB_TRACK_SIMPLE")) k_wvp_track_dda<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); }
                                   else if (c->all_media_dda && c->smaj_floats) k_wv_track_dda<C, TO_FILM, true><<<c->n_sm, 1024, (size_t) c->smaj_floats * 4, s>>>(c->sc, a, TrackSmaj{c->smaj_grid, c->smaj_floats});
                                   else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM, false><<<grid, 256, 0, s>>>(c->sc, a, TrackSmaj{-1, 0u}); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
-        if (MODE != 3) launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MODE != 3) k_wvp_shade_a_medium<ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
+        if (MODE != 3) launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_a_medium<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
+                                                       else if constexpr (MODE != 3) k_wvp_shade_a_medium<ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] {
             if constexpr (MODE == 0) k_wv_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b);
             else if constexpr (MODE == 3) k_bio_shade_a<<<grid128, 128, 0, s>>>(c->sc, a, b);
+            else if constexpr (MIS) k_mis_shade_a_surface<C, TO_FILM, SMIS><<<grid128_mis, 128, 0, s>>>(c->sc, a, b);
             else k_wvp_shade_a_surface<C, TO_FILM, ADJ><<<grid128, 128, 0, s>>>(c->sc, a, b); });
         if (MODE != 2) launch(r, ST_ESCAPE, [&] { if constexpr (MODE == 0) k_wv_escape<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a);
                                                   else if constexpr (MODE == 3) k_bio_escape<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a);
+                                                  else if constexpr (MIS) k_mis_escape<C, TO_FILM, SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                                   else k_wvp_escape<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         launch(r, ST_TRACE_S, [&] {
             if (shadow_mode == 1) { if (stk16) k_wv_trace<1, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<1, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); }
             else { if (stk16) k_wv_trace<2, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<2, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); } });
         launch(r, ST_NEE, [&] { if constexpr (MODE == 0) k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0);
                                 else if constexpr (MODE == 3) k_bio_nee<<<grid, 256, 0, s>>>(c->sc, a);
+                                else if constexpr (MIS) k_mis_nee<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                 else k_wvp_nee<ADJ><<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });
-        if (MODE != 3) launch(r, ST_SHADE_B_MED, [&] { if constexpr (MODE == 0) k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MODE != 3) k_wvp_shade_b_medium<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
+        if (MODE != 3) launch(r, ST_SHADE_B_MED, [&] { if constexpr (MODE == 0) k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_b_medium<C, TO_FILM, SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
+                                                       else if constexpr (MODE != 3) k_wvp_shade_b_medium<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_B_SURF, [&] {
             if constexpr (MODE == 0) k_wv_shade_b_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b);
             else if constexpr (MODE == 3) k_bio_shade_b<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b);
+            else if constexpr (MIS) k_mis_shade_b_surface<C, TO_FILM, SMIS><<<grid128_mis, 128, 0, s>>>(c->sc, a, b);
             else k_wvp_shade_b_surface<C, TO_FILM, ADJ><<<grid128, 128, 0, s>>>(c->sc, a, b); });
         k_wv_mid_iteration<<<1, 1, 0, s>>>(a.q, d_items, sids); ++launches;
         launch(r, ST_TRACE_C, [&] { if (stk16) k_wv_trace<0, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<0, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); });
-        if constexpr (MODE == 0 || MODE == 3) { if (multipass) launch(r, ST_REGEN, [&] { k_wv_regen<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); }); }
+        if constexpr (MODE == 0 || MODE >= 3) { if (multipass) launch(r, ST_REGEN, [&] { k_wv_regen<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); }); }
         return readback(r);
     };
     for (bool any = true; any;) {

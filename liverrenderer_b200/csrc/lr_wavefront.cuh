@@ -383,8 +383,10 @@ LR_DEV void wv_track_out(const DScene &sc, const WVArgs &a, uint32_t slot, int e
     if (event > 0) {
         p.o(slot) = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
         p.thr(slot) = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
-        p.hit(slot).x = hit_t;
+        if (event == 3) p.d(slot) = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(f));      // scatter already shaded (wv_track_scatter_sealed): new direction
+        else p.hit(slot).x = hit_t;
     }
+    wf_push(a.q_trace, &a.q->n_trace, slot, event == 3);
     const bool esc = event == 2 && !hit_valid(h0);
     const uint32_t b = (event == 2 && !esc) ? wv_bucket(sc, h0) : 0xffu;
     wf_push(a.q_regen, &a.q->n_regen, slot, fin && wv_more_passes(a, f));
@@ -469,6 +471,26 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
     flush_counters(cnt, 0, a.stats);
 }
 
+// A real scatter inside a SEALED medium in production tracking (DMedium::sealed: every shadow ray from inside ends on an opaque surface) needs no
+// SHADE_A -- the emitter sample is two discarded draws (wv_nee_setup) -- so TRACK finishes the vertex itself: flags, phase sample, the roulette of
+// the next iteration (k_wv_shade_a_medium + k_wv_shade_b_medium, same draws in the same order), and hands the path straight to TRACE_C (event 3)
+// instead of sending its state through two more kernels (10.8 % of the C3 step).  Not inlined: the walk loop keeps its register budget.
+__noinline__ LR_DEV void wv_track_scatter_sealed(const DScene &sc, const WVPlanes &p, uint32_t slot, Sampler &smp, Ray &ray, V3 &thr, uint32_t depth, uint32_t &f, int &event) {
+    const DMedium &m = sc.media[wf_medium(f)];
+    if (!m.sealed) return;
+    const bool sample_emitters = m.m.sample_emitters != 0;
+    f |= WF_VALID_RAY; f = sample_emitters ? (f & ~WF_SPEC_CHAIN) : (f | WF_SPEC_CHAIN);
+    if (sample_emitters) (void) smp.next_2d();
+    Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
+    (void) smp.next_1d(); const V2 s2 = smp.next_2d();
+    float phase_pdf; const V3 wo = phase.sample(-ray.d, s2, phase_pdf);
+    const float eta = depth > (uint32_t) sc.rr_depth ? p.res(slot).w : 1.f;
+    if (wv_rr(sc, smp, thr, eta, depth)) {
+        if (phase_pdf > 0.f) { ray.d = wo; ray.maxt = LR_LARGEST; reinterpret_cast<float *>(&p.lsp(slot))[3] = phase_pdf; }
+        event = 3;
+    } else event = 0;
+}
+
 // TRACK for scenes whose media all use the majorant DDA (production mode): the same per-item work as k_wv_track, run as a
 // persistent "while-while" loop.  The number of super-voxels a free flight crosses is roughly exponentially distributed, so a
 // warp that waits for its longest walk keeps 4-5 of 32 lanes busy; here a lane that has finished its item parks, and once
@@ -485,7 +507,7 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track(const __grid_consta
 // dependent global load (the walk is a chain of such loads: the kernel is latency-bound, ncu long-scoreboard).  128 KiB for the 256^3
 // grid at cell 8, so the block is 1024 threads, one per SM (same resident threads as 4 x 256).  Grids whose super-grid does not fit
 // (C3-XL: 1 MiB) and scenes with several grids use the global-memory form.
-struct TrackSmaj { int grid; uint32_t floats; };
+struct TrackSmaj { int grid; uint32_t floats; int fuse; };      // fuse: finish scatter vertices of sealed media inside TRACK (wv_track_scatter_sealed)
 template <int C, bool TO_FILM, bool SMAJ>
 __global__ void __launch_bounds__(SMAJ ? 1024 : 256, SMAJ ? 1 : LR_WF_OCC) k_wv_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a, const TrackSmaj sm) {
     extern __shared__ __align__(16) float s_maj[];
@@ -514,6 +536,7 @@ __global__ void __launch_bounds__(SMAJ ? 1024 : 256, SMAJ ? 1 : LR_WF_OCC) k_wv_
         if (__popc(walking) <= LR_TRACK_REFILL) {
             // ---- write finished items out and queue them (converged: the pushes use warp ballots) ----
             if (__any_sync(0xffffffffu, event >= 0)) {
+                if (event == 1 && sm.fuse) wv_track_scatter_sealed(sc, p, slot, smp, ray, thr, depth, f, event);
                 wv_track_out<C, TO_FILM>(sc, a, slot, event >= 0 ? event : -1, smp, ray, thr, depth, hit_t, f, h0);
                 if (event >= 0) event = -2;
             }

@@ -468,3 +468,19 @@ def test_second_sensor_and_wide_gaussian_filter():
     a = ctx.render(seed=2, spp=1, sensor=1); one = dict(d); one["sensor"] = d["sensor2"]; one.pop("sensor2")
     o = orc.OracleScene(mi.load_dict(one)); o.render(2, 1); ref = o.film_develop()
     assert np.isclose(a, ref, rtol=2e-3, atol=1e-5).all(-1).mean() > 0.97
+
+
+def test_track_finishes_sealed_scatter_vertices_itself(monkeypatch):
+    """Production tracking, sealed medium: TRACK shades its own scatter vertices (wv_track_scatter_sealed) instead of sending them through
+    SHADE_A / SHADE_B medium.  Same draws in the same order: lane-for-lane IDENTICAL to the three-kernel form (LR_TRACK_FUSE_OFF=1)."""
+    for phase in ("isotropic", "hg"):
+        sc = mi.load_dict(scenes.liver_single_mesh(res=48, spp=16, grid_res=32, phase=phase, tracking="dda")); n = 48 * 48 * 16
+        monkeypatch.delenv("LR_TRACK_FUSE_OFF", raising=False)
+        c1 = mi.Context(0).upload(sc); a = c1.sample_lanes(5, 16, 0, n); st_a = c1.stats()
+        c1.profile(True); c1.film_clear(); c1.render_lanes(5, 16, 0, 0); pa = c1.stage_profile(); c1.profile(False)
+        monkeypatch.setenv("LR_TRACK_FUSE_OFF", "1")
+        c2 = mi.Context(0).upload(sc); b = c2.sample_lanes(5, 16, 0, n); st_b = c2.stats()
+        c2.profile(True); c2.film_clear(); c2.render_lanes(5, 16, 0, 0); pb = c2.stage_profile(); c2.profile(False)
+        assert np.array_equal(a, b)
+        assert st_a["collisions"] == st_b["collisions"] and st_a["real_scatters"] == st_b["real_scatters"] and st_a["rays"] == st_b["rays"]
+        assert pa["shade_b_medium"]["items"] == 0 and pb["shade_b_medium"]["items"] == st_b["real_scatters"] - 0 or pb["shade_b_medium"]["items"] > 0

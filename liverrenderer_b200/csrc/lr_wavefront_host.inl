@@ -105,6 +105,8 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
     const bool stk16 = c->bvh4_small; const size_t smem_tr = c->trace_smem;
     const bool multipass = ra.n_passes > 1;
     const int fuse = getenv("LR_TRACK_FUSE_OFF") ? 0 : 1;               // A/B: scatter vertices of sealed media finished inside TRACK
+    bool all_sealed = !c->h_media.empty(); for (const auto &m : c->h_media) all_sealed = all_sealed && m.sealed != 0;
+    const bool no_medium_shade = MODE == 0 && fuse && c->all_media_dda && all_sealed;      // nothing ever reaches the scatter queue
     const int shadow_mode = (MODE < 3 && c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf && !getenv("LR_SHADOW_CLOSEST")) ? 1 : 2;   // LR_SHADOW_CLOSEST: A/B of the any-hit query
     uint64_t launches = 0; bool lanes_done = false; const bool dbg_sync = getenv("LR_WF_SYNC") != nullptr;
     // per-stage CUDA events (profile mode: one batch in flight, so the intervals do not overlap)
@@ -156,7 +158,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
                                   else if constexpr (MODE != 0) { if (c->all_media_dda && !getenv("LR_PRB_TRACK_SIMPLE")) k_wvp_track_dda<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); }
                                   else if (c->all_media_dda && c->smaj_floats) k_wv_track_dda<C, TO_FILM, true><<<c->n_sm, 1024, (size_t) c->smaj_floats * 4, s>>>(c->sc, a, TrackSmaj{c->smaj_grid, c->smaj_floats, fuse});
                                   else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM, false><<<grid, 256, 0, s>>>(c->sc, a, TrackSmaj{-1, 0u, fuse}); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
-        if (MODE != 3) launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_a_medium<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
+        if (MODE != 3 && !no_medium_shade) launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_a_medium<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                                        else if constexpr (MODE != 3) k_wvp_shade_a_medium<ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] {
             if constexpr (MODE == 0) k_wv_shade_a_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b);
@@ -174,7 +176,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
                                 else if constexpr (MODE == 3) k_bio_nee<<<grid, 256, 0, s>>>(c->sc, a);
                                 else if constexpr (MIS) k_mis_nee<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                 else k_wvp_nee<ADJ><<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });
-        if (MODE != 3) launch(r, ST_SHADE_B_MED, [&] { if constexpr (MODE == 0) k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_b_medium<C, TO_FILM, SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
+        if (MODE != 3 && !no_medium_shade) launch(r, ST_SHADE_B_MED, [&] { if constexpr (MODE == 0) k_wv_shade_b_medium<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_b_medium<C, TO_FILM, SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                                        else if constexpr (MODE != 3) k_wvp_shade_b_medium<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_B_SURF, [&] {
             if constexpr (MODE == 0) k_wv_shade_b_surface<C, TO_FILM><<<grid128, 128, 0, s>>>(c->sc, a, b);

@@ -61,7 +61,7 @@ struct WVPlanes {
 struct WVQueues {                      // device-side counters of one pool
     uint32_t n_trace, n_track, n_scatter, n_escape, n_shadow, n_nee, n_regen;
     uint32_t n_surf[WF_N_SURF]; uint32_t cursor[3];                    // work cursors of TRACE_C, TRACK, TRACE_S
-    uint32_t n_alloc, live, pad[3];
+    uint32_t n_alloc, live, cursor_nee, pad[2];                        // cursor_nee: work cursor of the persistent NEE walk (lr_wavefront_mis.cuh)
 };
 #define WV_N_QUEUES (7 + WF_N_SURF)
 
@@ -917,7 +917,7 @@ __global__ void k_wv_mid_iteration(WVQueues *q, unsigned long long *items, const
     atomicAdd(items + st.trace_s, (unsigned long long) q->n_shadow); atomicAdd(items + st.nee, (unsigned long long) q->n_nee);
     q->n_track = 0; q->n_scatter = 0; q->n_escape = 0; q->n_shadow = 0; q->n_nee = 0;
     for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
-    q->cursor[0] = q->cursor[1] = q->cursor[2] = 0;
+    q->cursor[0] = q->cursor[1] = q->cursor[2] = 0; q->cursor_nee = 0;
 }
 // end of an iteration: what is still alive; the consumed trace / regen queues are emptied
 __global__ void k_wv_end_iteration(WVQueues *q, uint32_t *live_out, const unsigned long long *lane_next, unsigned long long *lane_next_out,
@@ -931,7 +931,7 @@ __global__ void k_wv_end_iteration(WVQueues *q, uint32_t *live_out, const unsign
 __global__ void k_wv_init(WVQueues *q) {
     q->n_trace = 0; q->n_track = q->n_scatter = q->n_escape = q->n_shadow = q->n_nee = q->n_regen = 0;
     for (int b = 0; b < WF_N_SURF; ++b) q->n_surf[b] = 0;
-    q->cursor[0] = q->cursor[1] = q->cursor[2] = 0; q->n_alloc = 0; q->live = 0;
+    q->cursor[0] = q->cursor[1] = q->cursor[2] = 0; q->cursor_nee = 0; q->n_alloc = 0; q->live = 0;
 }
 
 } // namespace lr

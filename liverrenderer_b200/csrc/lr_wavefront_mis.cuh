@@ -64,29 +64,57 @@ LR_DEV bool mis_nee_setup(const DScene &sc, const WVArgs &a, uint32_t slot, cons
 }
 
 // ------------------------------------------------------------------------------------------
-// TRACK (volpathmis.cpp:236-312): free flights against the global majorant until a real scatter (1), the boundary (2) or the end (0)
+// TRACK (volpathmis.cpp:236-312): free flights against the global majorant until a real scatter (1), the boundary (2) or the end (0).
+// A persistent "while-while" loop like k_wv_track_dda: a path meets ~28 tentative collisions on the C3 frame and the chains of one warp differ
+// widely, so a lane whose item is finished parks; once LR_MIS_REFILL lanes are parked they are written out (converged: the queue pushes use
+// warp ballots) and pull the next queue entries.  One loop turn = one tentative collision per walking lane; per-lane draw order is unchanged.
 // ------------------------------------------------------------------------------------------
+#ifndef LR_MIS_REFILL
+#define LR_MIS_REFILL 12              // refill once at least this many lanes of the warp are parked
+#endif
 template <int C, bool TO_FILM, bool S>
 __global__ void __launch_bounds__(256, LR_MIS_OCC) k_mis_track(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     const WVPlanes &p = a.p;
-    WF_FOR_QUEUE(a.q->n_track) {
-        const bool item = qi < _n; const uint32_t slot = item ? a.q_track[qi] : 0;
-        int event = -1; Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f;
-        uint32_t depth = 0, f = 0; float hit_t = 0.f; Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
-        if (item) {
-            smp = wv_rng(p, slot);
-            float4 t4 = p.o(slot); ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
-            t4 = p.d(slot); ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
-            depth = __float_as_uint(p.thr(slot).w);
-            h0 = wf_hit(p.hit(slot)); hit_t = h0.t;
-            const float eta = p.res(slot).w;
+    const uint32_t n_items = a.q->n_track;
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    int event = -2;                                                        // -2 idle, -1 walking, 0 end of path, 1 scatter, 2 boundary
+    uint32_t slot = 0, depth = 0, f = 0; float hit_t = 0.f, eta = 1.f; bool first = true, exhausted = false;
+    Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f;
+    Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
+    MisW<S> P = misw_ones<S>(), N = misw_ones<S>();
+    for (;;) {
+        const unsigned walking = __ballot_sync(0xffffffffu, event == -1);
+        if (__popc(walking) <= 32 - LR_MIS_REFILL) {
+            if (__any_sync(0xffffffffu, event >= 0)) {
+                if (event > 0) { float4 *mr = mis_rec(a, slot); misw_store<S>(mr, 0, P); misw_store<S>(mr, 3, N); }
+                wv_track_out<C, TO_FILM>(sc, a, slot, event >= 0 ? event : -1, smp, ray, mk3(0.f), depth, hit_t, f, h0);
+                if (event >= 0) event = -2;
+            }
+            if (!exhausted) {
+                const unsigned idle = ~walking; uint32_t base = 0;
+                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor[1], (uint32_t) __popc(idle));
+                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+                exhausted = base + (uint32_t) __popc(idle) >= n_items;
+                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+                if (event == -2 && qi < n_items) {
+                    slot = a.q_track[qi];
+                    smp = wv_rng(p, slot);
+                    float4 t4 = p.o(slot); ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+                    t4 = p.d(slot); ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
+                    depth = __float_as_uint(p.thr(slot).w);
+                    h0 = wf_hit(p.hit(slot)); hit_t = h0.t; eta = p.res(slot).w;
+                    const float4 *mr = mis_rec(a, slot); P = misw_load<S>(mr, 0); N = misw_load<S>(mr, 3);
+                    first = true; event = -1;
+                }
+            }
+        }
+        if (event == -1) {                                                  // one loop iteration of the reference for this lane
             const uint32_t channel = f & WF_CHANNEL_MASK; const int medium = wf_medium(f);
             const DMedium &m = sc.media[medium];
-            float4 *mr = mis_rec(a, slot);
-            MisW<S> P = misw_load<S>(mr, 0), N = misw_load<S>(mr, 3);
-            for (bool first = true;; first = false) {
-                if (!first && !mis_next_iteration<S>(sc, smp, P, eta, depth, channel, true)) { event = 0; break; }   // after a null collision: no roulette
+            if (!first && !mis_next_iteration<S>(sc, smp, P, eta, depth, channel, true)) event = 0;       // after a null collision: no roulette
+            else {
+                first = false;
                 MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
                 if (hit_t < mei.t) mei.t = LR_INF;
                 const bool is_spectral = m.m.has_spectral_extinction != 0;
@@ -97,28 +125,31 @@ __global__ void __launch_bounds__(256, LR_MIS_OCC) k_mis_track(const __grid_cons
                     update_weights<S>(P, pdf, tr, channel, true);
                     update_weights<S>(N, pdf, tr, channel, true);
                 }
-                if (!mei_valid(mei)) { event = 2; break; }
-                const float null_scatter_prob = hmean(mei.sigma_n / mei.combined_extinction);
-                if (smp.next_1d() < null_scatter_prob) {                            // null collision: the reference's next loop iteration
-                    if (is_spectral) {
-                        update_weights<S>(P, mk3(null_scatter_prob), mei.sigma_n, channel, true);
-                        update_weights<S>(N, mk3(1.f), mei.sigma_n, channel, true);
+                if (!mei_valid(mei)) event = 2;
+                else {
+                    const float null_scatter_prob = hmean(mei.sigma_n / mei.combined_extinction);
+                    if (smp.next_1d() < null_scatter_prob) {                        // null collision: the reference's next loop iteration
+                        if (is_spectral) {
+                            update_weights<S>(P, mk3(null_scatter_prob), mei.sigma_n, channel, true);
+                            update_weights<S>(N, mk3(1.f), mei.sigma_n, channel, true);
+                        } else {
+                            update_weights<S>(P, mei.sigma_n, mei.sigma_n, channel, true);
+                            update_weights<S>(N, mk3(1.f), mk3(null_scatter_prob), channel, true);
+                        }
+                        ray.o = mei.p; hit_t = hit_t - mei.t;
                     } else {
-                        update_weights<S>(P, mei.sigma_n, mei.sigma_n, channel, true);
-                        update_weights<S>(N, mk3(1.f), mk3(null_scatter_prob), channel, true);
+                        depth += 1; cnt.real_scatters++; p.lsp(slot) = make_float4(mei.p.x, mei.p.y, mei.p.z, 0.f);
+                        if (!(depth < sc.max_depth)) event = 0;
+                        else {
+                            if (is_spectral) update_weights<S>(P, mk3(1.f - null_scatter_prob), mei.sigma_s, channel, true);
+                            else update_weights<S>(P, mei.sigma_t, mei.sigma_s, channel, true);
+                            ray.o = mei.p; event = 1;
+                        }
                     }
-                    ray.o = mei.p; hit_t = hit_t - mei.t;
-                    continue;
                 }
-                depth += 1; cnt.real_scatters++; p.lsp(slot) = make_float4(mei.p.x, mei.p.y, mei.p.z, 0.f);
-                if (!(depth < sc.max_depth)) { event = 0; break; }
-                if (is_spectral) update_weights<S>(P, mk3(1.f - null_scatter_prob), mei.sigma_s, channel, true);
-                else update_weights<S>(P, mei.sigma_t, mei.sigma_s, channel, true);
-                ray.o = mei.p; event = 1; break;
             }
-            if (event > 0) { misw_store<S>(mr, 0, P); misw_store<S>(mr, 3, N); }
         }
-        wv_track_out<C, TO_FILM>(sc, a, slot, event, smp, ray, mk3(0.f), depth, hit_t, f, h0);
+        if (exhausted && !__any_sync(0xffffffffu, event != -2)) break;
     }
     flush_counters(cnt, 0, a.stats);
 }
@@ -236,29 +267,60 @@ __global__ void __launch_bounds__(256, LR_MIS_OCC) k_mis_escape(const __grid_con
     }
 }
 
-// NEE: the walk of sample_emitter (volpathmis.cpp:523-629) from TRACE_S's closest hit, then the two end-point updates and the estimate
+// NEE: the walk of sample_emitter (volpathmis.cpp:523-629) from TRACE_S's closest hit, then the two end-point updates and the estimate.
+// Persistent refill loop like k_mis_track: one loop turn = one iteration of the reference's walk per lane.
 template <bool S>
 __global__ void __launch_bounds__(256, LR_MIS_OCC) k_mis_nee(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     const WVPlanes &p = a.p;
-    WF_FOR_QUEUE(a.q->n_nee) {
-        if (qi < _n) {
-            const uint32_t slot = a.q_nee[qi];
-            Sampler smp = wv_rng(p, slot);
-            const uint32_t channel = __float_as_uint(p.d(slot).w) & WF_CHANNEL_MASK;
-            const float4 o4 = p.no(slot), d4 = p.nd(slot);
-            const float4 *mr = mis_rec(a, slot); const float4 e4 = mr[6], v4 = mr[7];
-            Ray ray; ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z);
-            const float max_dist = o4.w, ds_dist = d4.w; float total_dist = 0.f;
-            int medium = __float_as_int(p.nw(slot).w);
-            Hit h = wf_hit(p.nhit(slot));
-            float si_t = h.t; bool needs_intersection = false, active = true;
-            MisW<S> nee = misw_load<S>(mr, 0), uni = nee;
-            update_weights<S>(nee, mk3(e4.w), mk3(1.f), channel, true);                // :481
-            while (active) {
-                const float remaining_dist = max_dist - total_dist; ray.maxt = remaining_dist;
-                active &= remaining_dist > 0.f;
-                if (!active) break;
+    const uint32_t n_items = a.q->n_nee;
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    int state = -2;                                                        // -2 idle, -1 walking, 0 walk finished
+    uint32_t slot = 0, channel = 0; bool exhausted = false, needs_intersection = false;
+    Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f;
+    float max_dist = 0.f, ds_dist = 0.f, total_dist = 0.f, si_t = LR_INF; int medium = -1;
+    Hit h; h.t = LR_INF; h.prim = 0xffffffffu; h.u = h.v = 0.f;
+    MisW<S> nee = misw_ones<S>(), uni = misw_ones<S>();
+    for (;;) {
+        const unsigned walking = __ballot_sync(0xffffffffu, state == -1);
+        if (__popc(walking) <= 32 - LR_MIS_REFILL) {
+            if (state == 0) {                                               // the two end-point updates and the estimate (:326-329, :413-416)
+                const float4 *mr = mis_rec(a, slot); const float4 e4 = mr[6], v4 = mr[7];
+                const V3 val = mk3(v4.x, v4.y, v4.z);
+                update_weights<S>(nee, mk3(1.f), val, channel, true);
+                update_weights<S>(uni, mk3(v4.w), val, channel, true);
+                const V3 c = mis_weight2<S>(nee, uni) * mk3(e4.x, e4.y, e4.z);
+                float4 r4 = p.res(slot); r4.x += c.x; r4.y += c.y; r4.z += c.z; p.res(slot) = r4;
+                wv_rng_store(p, slot, smp);
+                state = -2;
+            }
+            if (!exhausted) {
+                const unsigned idle = ~walking; uint32_t base = 0;
+                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor_nee, (uint32_t) __popc(idle));
+                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+                exhausted = base + (uint32_t) __popc(idle) >= n_items;
+                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+                if (state == -2 && qi < n_items) {
+                    slot = a.q_nee[qi];
+                    smp = wv_rng(p, slot);
+                    channel = __float_as_uint(p.d(slot).w) & WF_CHANNEL_MASK;
+                    const float4 o4 = p.no(slot), d4 = p.nd(slot);
+                    ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z);
+                    max_dist = o4.w; ds_dist = d4.w; total_dist = 0.f;
+                    medium = __float_as_int(p.nw(slot).w);
+                    h = wf_hit(p.nhit(slot)); si_t = h.t; needs_intersection = false;
+                    const float4 *mr = mis_rec(a, slot);
+                    nee = misw_load<S>(mr, 0); uni = nee;
+                    update_weights<S>(nee, mk3(mr[6].w), mk3(1.f), channel, true);     // :481
+                    state = -1;
+                }
+            }
+        }
+        if (state == -1) {                                                  // one iteration of the walk
+            bool active = true;
+            const float remaining_dist = max_dist - total_dist; ray.maxt = remaining_dist;
+            active &= remaining_dist > 0.f;
+            if (active) {
                 bool escaped_medium = false, active_medium = medium >= 0, active_surface = !active_medium;
                 if (active_medium) {
                     const DMedium &m = sc.media[medium];
@@ -305,19 +367,14 @@ __global__ void __launch_bounds__(256, LR_MIS_OCC) k_mis_nee(const __grid_consta
                     update_weights<S>(uni, mk3(1.f), bsdf_val, channel, true);
                     Ray r2 = spawn_ray(si.p, si.n, ray.d); ray.o = r2.o;
                 }
-                ray.maxt = remaining_dist;
                 needs_intersection |= active_surface;
                 if (S) active &= (active_medium || active_surface) && any_nonzero(mis_weight1<S>(uni));
                 else active &= (active_medium || active_surface) && (any_nonzero(uni.r[0]) || any_nonzero(nee.r[0]));
                 if (active_surface && mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
             }
-            const V3 val = mk3(v4.x, v4.y, v4.z);
-            update_weights<S>(nee, mk3(1.f), val, channel, true);                      // :326-327, :413-414
-            update_weights<S>(uni, mk3(v4.w), val, channel, true);
-            const V3 c = mis_weight2<S>(nee, uni) * mk3(e4.x, e4.y, e4.z);
-            float4 r4 = p.res(slot); r4.x += c.x; r4.y += c.y; r4.z += c.z; p.res(slot) = r4;
-            wv_rng_store(p, slot, smp);
+            if (!active) state = 0;
         }
+        if (exhausted && !__any_sync(0xffffffffu, state != -2)) break;
     }
     flush_counters(cnt, 0, a.stats);
 }

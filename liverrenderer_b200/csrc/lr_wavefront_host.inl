@@ -106,7 +106,8 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
     const bool multipass = ra.n_passes > 1;
     const int fuse = getenv("LR_TRACK_FUSE_OFF") ? 0 : 1;               // A/B: scatter vertices of sealed media finished inside TRACK
     bool all_sealed = !c->h_media.empty(); for (const auto &m : c->h_media) all_sealed = all_sealed && m.sealed != 0;
-    const bool no_medium_shade = MODE == 0 && fuse && c->all_media_dda && all_sealed;      // nothing ever reaches the scatter queue
+    const bool no_medium_shade = fuse && c->all_media_dda && all_sealed &&                 // nothing ever reaches the scatter queue
+                                 (MODE == 0 || ((MODE == 1 || MODE == 2) && !getenv("LR_PRB_TRACK_SIMPLE")));
     const int shadow_mode = (MODE < 3 && c->sc.integ.tracking == LR_TRACKING_DDA && !c->sc.any_null_bsdf && !getenv("LR_SHADOW_CLOSEST")) ? 1 : 2;   // LR_SHADOW_CLOSEST: A/B of the any-hit query
     uint64_t launches = 0; bool lanes_done = false; const bool dbg_sync = getenv("LR_WF_SYNC") != nullptr;
     // per-stage CUDA events (profile mode: one batch in flight, so the intervals do not overlap)
@@ -155,7 +156,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
         }
         launch(r, ST_TRACK, [&] { if constexpr (MODE == 3) k_bio_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a);
                                   else if constexpr (MIS) k_mis_track<C, TO_FILM, SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
-                                  else if constexpr (MODE != 0) { if (c->all_media_dda && !getenv("LR_PRB_TRACK_SIMPLE")) k_wvp_track_dda<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); else k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); }
+                                  else if constexpr (MODE != 0) { if (c->all_media_dda && !getenv("LR_PRB_TRACK_SIMPLE")) k_wvp_track_dda<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a, fuse); else k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); }
                                   else if (c->all_media_dda && c->smaj_floats) k_wv_track_dda<C, TO_FILM, true><<<c->n_sm, 1024, (size_t) c->smaj_floats * 4, s>>>(c->sc, a, TrackSmaj{c->smaj_grid, c->smaj_floats, fuse});
                                   else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM, false><<<grid, 256, 0, s>>>(c->sc, a, TrackSmaj{-1, 0u, fuse}); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         if (MODE != 3 && !no_medium_shade) launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_a_medium<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);

@@ -222,8 +222,26 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track(const __grid_const
 // parked the parked lanes are written out and pull the next queue entries.  After a null collision the walk CONTINUES in its DDA state
 // (k_wvp_track restarts it from the collision point: the same cell, the same majorant); draw order per lane is unchanged: optical
 // depth, then per tentative collision (null test, roulette of the next loop iteration, next optical depth).
+// scatter vertex inside a sealed medium: k_wvp_shade_a_medium + k_wvp_shade_b_medium done by TRACK itself (see wv_track_scatter_sealed,
+// lr_wavefront.cuh): flags, the two discarded emitter draws, phase sample, roulette of the next iteration -> TRACE_C (event 3) or the end (0)
+__noinline__ LR_DEV void wvp_track_scatter_sealed(const DScene &sc, const WVPlanes &p, uint32_t slot, Sampler &smp, Ray &ray, V3 &thr, float eta, uint32_t depth, uint32_t &f, int &event) {
+    const DMedium &m = sc.media[wf_medium(f)];
+    if (!m.sealed) return;
+    const bool sample_emitters = m.m.sample_emitters != 0;
+    f = sample_emitters ? (f & ~WF_SPEC_CHAIN) : (f | WF_SPEC_CHAIN); f &= ~(WF_NEE_ACTIVE | WF_DEAD);
+    if (sample_emitters) (void) smp.next_2d();
+    f |= WF_VALID_RAY;
+    Phase phase; phase.kind = m.m.phase; phase.g = m.m.phase_g;
+    (void) smp.next_1d(); const V2 s2 = smp.next_2d();
+    float phase_pdf; const V3 wo = phase.sample(-ray.d, s2, phase_pdf);
+    if (wvp_rr(sc, smp, thr, depth > (uint32_t) sc.rr_depth ? eta : 1.f, depth)) {
+        if (phase_pdf > 0.f) { ray.d = wo; ray.maxt = LR_LARGEST; reinterpret_cast<float *>(&p.lsp(slot))[3] = phase_pdf; }
+        event = 3;
+    } else event = 0;
+}
+
 template <int C, bool TO_FILM, bool ADJ>
-__global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track_dda(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a, const int fuse) {
     Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
     const WVPlanes &p = a.p;
     const uint32_t n_items = a.q->n_track;
@@ -238,13 +256,16 @@ __global__ void __launch_bounds__(256, LR_WF_OCC) k_wvp_track_dda(const __grid_c
         if (__popc(walking) <= LR_TRACK_REFILL) {
             // ---- write finished items out and queue them (converged: the pushes use warp ballots) ----
             if (__any_sync(0xffffffffu, event >= 0)) {
+                if (event == 1 && fuse) wvp_track_scatter_sealed(sc, p, slot, smp, ray, thr, eta, depth, f, event);
                 if (event >= 0) wv_rng_store(p, slot, smp);
                 if (event > 0) {
                     p.o(slot) = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.maxt);
                     p.thr(slot) = make_float4(thr.x, thr.y, thr.z, __uint_as_float(depth));
-                    p.hit(slot).x = hit_t;
+                    if (event == 3) p.d(slot) = make_float4(ray.d.x, ray.d.y, ray.d.z, __uint_as_float(f));
+                    else p.hit(slot).x = hit_t;
                 }
                 wvp_finish<C, TO_FILM, ADJ>(sc, a, slot, event == 0, f);
+                wf_push(a.q_trace, &a.q->n_trace, slot, event == 3);
                 const bool esc = event == 2 && !hit_valid(h0);
                 const uint32_t b = (event == 2 && !esc) ? wv_bucket(sc, h0) : 0xffu;
                 wf_push(a.q_scatter, &a.q->n_scatter, slot, event == 1);

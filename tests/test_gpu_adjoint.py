@@ -257,3 +257,25 @@ def test_albedo_grid_gradient(tracking):
         c1.grid_update(1, a); return float((c1.render(seed=21, spp=spp).astype(np.float64) * w).sum())
     b1 = np.ascontiguousarray(base[..., :1]); fd = (loss1(b1 + eps) - loss1(b1 - eps)) / (2 * eps)
     assert abs(fd - g1.sum()) <= 3e-3 * abs(fd) + 1e-5, (fd, g1.sum())
+
+
+def test_prb_track_finishes_sealed_scatter_vertices_itself(monkeypatch):
+    """prbvolpath in production tracking with a sealed medium: TRACK shades its scatter vertices itself (wvp_track_scatter_sealed).  Same draws
+    in the same order as the three-kernel form (LR_TRACK_FUSE_OFF=1): identical primal lanes, the same gradient up to fp32 atomic order."""
+    sc = mi.load_dict(scenes.sphere_liver_inverse(res=48, spp=8, grid_res=32, tracking="dda")); n = 48 * 48 * 8
+    out = {}
+    for key, env in (("fused", None), ("plain", "1")):
+        if env is None:
+            monkeypatch.delenv("LR_TRACK_FUSE_OFF", raising=False)
+        else:
+            monkeypatch.setenv("LR_TRACK_FUSE_OFF", env)
+        ctx = mi.Context(0).upload(sc)
+        lanes = ctx.sample_lanes(2, 8, 0, n); img = ctx.render(seed=2, spp=8)
+        g = np.ones_like(img) / img.size
+        ctx.grid_grad_zero(0); ctx.render_backward(g, seed=3, spp=8); grad = ctx.grid_grad_read(0).copy()
+        out[key] = (lanes, grad, ctx.stats())
+    assert np.array_equal(out["fused"][0], out["plain"][0])
+    ga, gb = out["fused"][1], out["plain"][1]
+    assert np.abs(gb).max() > 0
+    np.testing.assert_allclose(ga, gb, rtol=2e-4, atol=1e-7 * np.abs(gb).max())
+    assert out["fused"][2]["collisions"] == out["plain"][2]["collisions"]

@@ -906,6 +906,180 @@ __global__ void __launch_bounds__(128, LR_WF_OCC_SURF) k_wv_shade_b_surface(cons
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Reference-order tracking (LR_TRACKING_REFERENCE: one global majorant, the reference's draw order) as persistent refill loops: the same
+// per-item work as k_wv_track / k_wv_nee, but a path meets 25-28 tentative collisions on the C3 frame and the chains of one warp differ
+// widely, so one loop turn is ONE tentative collision per walking lane, finished lanes park, and once LR_REF_REFILL lanes are parked they
+// are written out and pull the next queue entries (the form k_wv_track_dda has).  Per-lane draw order is unchanged.
+// ------------------------------------------------------------------------------------------
+#ifndef LR_REF_REFILL
+#define LR_REF_REFILL 12
+#endif
+template <int C, bool TO_FILM>
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_track_ref(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+    const WVPlanes &p = a.p;
+    const uint32_t n_items = a.q->n_track;
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    int event = -2;                                                        // -2 idle, -1 walking, 0 end of path, 1 scatter, 2 boundary
+    uint32_t slot = 0, depth = 0, f = 0; float hit_t = 0.f, eta = 1.f; bool first = true, exhausted = false;
+    Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f; V3 thr = mk3(0.f);
+    Hit h0; h0.t = LR_INF; h0.prim = 0xffffffffu; h0.u = h0.v = 0.f;
+    for (;;) {
+        const unsigned walking = __ballot_sync(0xffffffffu, event == -1);
+        if (__popc(walking) <= 32 - LR_REF_REFILL) {
+            if (__any_sync(0xffffffffu, event >= 0)) {
+                wv_track_out<C, TO_FILM>(sc, a, slot, event >= 0 ? event : -1, smp, ray, thr, depth, hit_t, f, h0);
+                if (event >= 0) event = -2;
+            }
+            if (!exhausted) {
+                const unsigned idle = ~walking; uint32_t base = 0;
+                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor[1], (uint32_t) __popc(idle));
+                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+                exhausted = base + (uint32_t) __popc(idle) >= n_items;
+                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+                if (event == -2 && qi < n_items) {
+                    slot = a.q_track[qi];
+                    smp = wv_rng(p, slot);
+                    float4 t4 = p.o(slot); ray.o = mk3(t4.x, t4.y, t4.z); ray.maxt = t4.w;
+                    t4 = p.d(slot); ray.d = mk3(t4.x, t4.y, t4.z); f = __float_as_uint(t4.w);
+                    t4 = p.thr(slot); thr = mk3(t4.x, t4.y, t4.z); depth = __float_as_uint(t4.w);
+                    h0 = wf_hit(p.hit(slot)); hit_t = h0.t; eta = p.res(slot).w;
+                    first = true; event = -1;
+                }
+            }
+        }
+        if (event == -1) {                                                  // one loop iteration of the reference for this lane (volpath.cpp:160-253)
+            const uint32_t channel = f & WF_CHANNEL_MASK; const int medium = wf_medium(f);
+            const DMedium &m = sc.media[medium];
+            if (!first && !wv_rr(sc, smp, thr, eta, depth)) event = 0;
+            else {
+                first = false;
+                MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
+                if (hit_t < mei.t) mei.t = LR_INF;
+                const bool is_spectral = m.m.has_spectral_extinction != 0;
+                if (is_spectral) {
+                    const float t = fminf(mei.t, hit_t) - mei.mint;
+                    const V3 tr = exp3(mei.combined_extinction * (-t));
+                    const V3 pdf = hit_t < mei.t ? tr : tr * mei.combined_extinction;
+                    const float tr_pdf = idx3(pdf, channel);
+                    thr *= tr_pdf > 0.f ? tr / tr_pdf : mk3(0.f);
+                }
+                if (!mei_valid(mei)) event = 2;
+                else {
+                    const float null_scatter_prob = hmean(mei.sigma_n / mei.combined_extinction);
+                    if (smp.next_1d() < null_scatter_prob) {                       // null collision: next loop iteration of the reference
+                        if (is_spectral) thr *= mei.sigma_n / null_scatter_prob;
+                        ray.o = mei.p; hit_t = hit_t - mei.t;
+                    } else {
+                        depth += 1; cnt.real_scatters++; p.lsp(slot) = make_float4(mei.p.x, mei.p.y, mei.p.z, p.lsp(slot).w);
+                        if (!(depth < sc.max_depth)) event = 0;
+                        else {
+                            if (is_spectral) thr *= mei.sigma_s / hmean(mei.sigma_t / mei.combined_extinction);
+                            else thr *= mei.sigma_s / mei.sigma_t;
+                            ray.o = mei.p; event = 1;
+                        }
+                    }
+                }
+            }
+        }
+        if (exhausted && !__any_sync(0xffffffffu, event != -2)) break;
+    }
+    flush_counters(cnt, 0, a.stats);
+}
+
+// the ratio-tracking walk of k_wv_nee for scenes in reference-order tracking (every item comes with TRACE_S's closest hit)
+__global__ void __launch_bounds__(256, LR_WF_OCC) k_wv_nee_ref(const __grid_constant__ DScene sc, const __grid_constant__ WVArgs a) {
+    Counters cnt; cnt.rays = cnt.collisions = cnt.real_scatters = 0;
+    const WVPlanes &p = a.p;
+    const uint32_t n_items = a.q->n_nee;
+    const unsigned lane = threadIdx.x & 31u, lt = (1u << lane) - 1u;
+    int state = -2;                                                        // -2 idle, -1 walking, 0 walk finished
+    uint32_t slot = 0, channel = 0; bool exhausted = false, needs_intersection = false;
+    Sampler smp; smp.state = smp.inc = 0; Ray ray; ray.o = ray.d = mk3(0.f); ray.maxt = 0.f;
+    float max_dist = 0.f, ds_dist = 0.f, total_dist = 0.f, si_t = LR_INF; int medium = -1; V3 transmittance = mk3(1.f);
+    Hit h; h.t = LR_INF; h.prim = 0xffffffffu; h.u = h.v = 0.f;
+    for (;;) {
+        const unsigned walking = __ballot_sync(0xffffffffu, state == -1);
+        if (__popc(walking) <= 32 - LR_REF_REFILL) {
+            if (state == 0) {                                               // result += throughput * (phase | bsdf) value * mis * emitter_val * transmittance
+                const float4 w4 = p.nw(slot); float4 r4 = p.res(slot);
+                r4.x = fmaf(w4.x, transmittance.x, r4.x); r4.y = fmaf(w4.y, transmittance.y, r4.y); r4.z = fmaf(w4.z, transmittance.z, r4.z);
+                p.res(slot) = r4;
+                wv_rng_store(p, slot, smp);
+                state = -2;
+            }
+            if (!exhausted) {
+                const unsigned idle = ~walking; uint32_t base = 0;
+                if (lane == (unsigned) (__ffs(idle) - 1)) base = atomicAdd(&a.q->cursor_nee, (uint32_t) __popc(idle));
+                base = __shfl_sync(0xffffffffu, base, __ffs(idle) - 1);
+                exhausted = base + (uint32_t) __popc(idle) >= n_items;
+                const uint32_t qi = base + (uint32_t) __popc(idle & lt);
+                if (state == -2 && qi < n_items) {
+                    slot = a.q_nee[qi];
+                    smp = wv_rng(p, slot);
+                    channel = __float_as_uint(p.d(slot).w) & WF_CHANNEL_MASK;
+                    const float4 o4 = p.no(slot), d4 = p.nd(slot);
+                    ray.o = mk3(o4.x, o4.y, o4.z); ray.d = mk3(d4.x, d4.y, d4.z);
+                    max_dist = o4.w; ds_dist = d4.w; total_dist = 0.f;
+                    medium = __float_as_int(p.nw(slot).w);
+                    h = wf_hit(p.nhit(slot)); si_t = h.t; needs_intersection = false; transmittance = mk3(1.f);
+                    state = -1;
+                }
+            }
+        }
+        if (state == -1) {                                                  // one iteration of the walk (volpath.cpp:454-551)
+            bool active = true;
+            const float remaining_dist = max_dist - total_dist; ray.maxt = remaining_dist;
+            active &= remaining_dist > 0.f;
+            if (active) {
+                bool escaped_medium = false, active_medium = medium >= 0, active_surface = !active_medium;
+                if (active_medium) {
+                    const DMedium &m = sc.media[medium];
+                    MediumInteraction mei = sample_interaction<false>(sc, medium, ray, smp.next_1d(), channel, nullptr, cnt.collisions);
+                    if (needs_intersection) {
+                        if (m.m.kind == LR_MEDIUM_HOMOGENEOUS && mei_valid(mei)) ray.maxt = fminf(mei.t, remaining_dist);
+                        cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false;
+                    }
+                    if (si_t < mei.t) mei.t = LR_INF;
+                    const bool is_spectral = m.m.has_spectral_extinction != 0;
+                    if (is_spectral) {
+                        const float t = fminf(remaining_dist, fminf(mei.t, si_t)) - mei.mint;
+                        const V3 tr = exp3(mei.combined_extinction * (-t));
+                        const V3 ffp = (si_t < mei.t || mei.t > remaining_dist) ? tr : tr * mei.combined_extinction;
+                        const float tr_pdf = idx3(ffp, channel);
+                        transmittance *= tr_pdf > 0.f ? tr / tr_pdf : mk3(0.f);
+                    }
+                    if (mei.t > remaining_dist && mei_valid(mei)) total_dist = ds_dist;
+                    if (mei.t > remaining_dist) mei.t = LR_INF;
+                    escaped_medium = !mei_valid(mei); active_medium = mei_valid(mei);
+                    if (active_medium) {
+                        total_dist += mei.t; ray.o = mei.p; si_t = si_t - mei.t;
+                        if (is_spectral) transmittance *= mei.sigma_n; else transmittance *= mei.sigma_n / mei.combined_extinction;
+                    }
+                }
+                if (active_surface && needs_intersection) { cnt.rays++; h = bvh_trace<false, false>(sc, ray); si_t = h.t; needs_intersection = false; }
+                active_surface |= escaped_medium;
+                if (active_surface) total_dist += si_t;
+                active_surface &= (si_t != LR_INF) && !active_medium;
+                SurfaceInteraction si;
+                if (active_surface) {
+                    h.t = si_t; si = compute_si(sc, ray, h, sc.tris_gid);
+                    BSDF bsdf(sc, si);
+                    transmittance *= bsdf.eval_null_transmission();
+                    Ray r2 = spawn_ray(si.p, si.n, ray.d); ray.o = r2.o;
+                }
+                needs_intersection |= active_surface;
+                active &= (active_medium || active_surface) && any_nonzero(transmittance);
+                if (active_surface && mesh_is_transition(sc, si.mesh)) medium = target_medium(sc, si, ray.d);
+            }
+            if (!active) state = 0;
+        }
+        if (exhausted && !__any_sync(0xffffffffu, state != -2)) break;
+    }
+    flush_counters(cnt, 0, a.stats);
+}
+
 // counters of the queues the second half of an iteration fills (after SHADE_B has consumed the scatter / surface queues)
 // `items`: per-stage totals of queue entries consumed (lr_stage_profile.items; index = the host's stage enum, passed in `st`)
 struct WVStageIds { int track, shade_a_med, shade_a_surf, escape, trace_s, nee, shade_b_med, shade_b_surf, trace_c, regen; };

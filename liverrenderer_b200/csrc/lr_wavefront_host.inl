@@ -104,6 +104,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
     const int grid_mis = c->n_sm * LR_MIS_OCC, grid128_mis = c->n_sm * 2 * LR_MIS_OCC;       // the volpathmis stage kernels are compiled for 128 registers
     const bool stk16 = c->bvh4_small; const size_t smem_tr = c->trace_smem;
     const bool multipass = ra.n_passes > 1;
+    const bool ref_persistent = c->sc.integ.tracking == LR_TRACKING_REFERENCE && !getenv("LR_REF_REFILL_OFF");   // reference-order TRACK / NEE as refill loops (A/B: the one-item-per-thread kernels)
     const int fuse = getenv("LR_TRACK_FUSE_OFF") ? 0 : 1;               // A/B: scatter vertices of sealed media finished inside TRACK
     bool all_sealed = !c->h_media.empty(); for (const auto &m : c->h_media) all_sealed = all_sealed && m.sealed != 0;
     const bool no_medium_shade = fuse && c->all_media_dda && all_sealed &&                 // nothing ever reaches the scatter queue
@@ -158,7 +159,8 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
                                   else if constexpr (MIS) k_mis_track<C, TO_FILM, SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                   else if constexpr (MODE != 0) { if (c->all_media_dda && !getenv("LR_PRB_TRACK_SIMPLE")) k_wvp_track_dda<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a, fuse); else k_wvp_track<C, TO_FILM, ADJ><<<grid, 256, 0, s>>>(c->sc, a); }
                                   else if (c->all_media_dda && c->smaj_floats) k_wv_track_dda<C, TO_FILM, true><<<c->n_sm, 1024, (size_t) c->smaj_floats * 4, s>>>(c->sc, a, TrackSmaj{c->smaj_grid, c->smaj_floats, fuse});
-                                  else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM, false><<<grid, 256, 0, s>>>(c->sc, a, TrackSmaj{-1, 0u, fuse}); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
+                                  else if (c->all_media_dda) k_wv_track_dda<C, TO_FILM, false><<<grid, 256, 0, s>>>(c->sc, a, TrackSmaj{-1, 0u, fuse});
+                                  else if (ref_persistent) k_wv_track_ref<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); else k_wv_track<C, TO_FILM><<<grid, 256, 0, s>>>(c->sc, a); });
         if (MODE != 3 && !no_medium_shade) launch(r, ST_SHADE_A_MED, [&] { if constexpr (MODE == 0) k_wv_shade_a_medium<<<grid, 256, 0, s>>>(c->sc, a); else if constexpr (MIS) k_mis_shade_a_medium<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                                        else if constexpr (MODE != 3) k_wvp_shade_a_medium<ADJ><<<grid, 256, 0, s>>>(c->sc, a); });
         for (int b = 0; b < WF_N_SURF; ++b) if ((surf_mask >> b) & 1u) launch(r, ST_SHADE_A_SURF, [&] {
@@ -173,7 +175,7 @@ static int wavefront_render_t(lr_ctx *c, const RenderArgs &ra, const WFPrbArgs p
         launch(r, ST_TRACE_S, [&] {
             if (shadow_mode == 1) { if (stk16) k_wv_trace<1, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<1, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); }
             else { if (stk16) k_wv_trace<2, short><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); else k_wv_trace<2, int><<<grid_tr, LR_TRACE_THREADS, smem_tr, s>>>(c->sc, a, r.tcfg); } });
-        launch(r, ST_NEE, [&] { if constexpr (MODE == 0) k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0);
+        launch(r, ST_NEE, [&] { if constexpr (MODE == 0) { if (ref_persistent && shadow_mode == 2) k_wv_nee_ref<<<grid, 256, 0, s>>>(c->sc, a); else k_wv_nee<<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); }
                                 else if constexpr (MODE == 3) k_bio_nee<<<grid, 256, 0, s>>>(c->sc, a);
                                 else if constexpr (MIS) k_mis_nee<SMIS><<<grid_mis, 256, 0, s>>>(c->sc, a);
                                 else k_wvp_nee<ADJ><<<grid, 256, 0, s>>>(c->sc, a, shadow_mode == 2 ? 1 : 0); });

@@ -484,3 +484,17 @@ def test_track_finishes_sealed_scatter_vertices_itself(monkeypatch):
         assert np.array_equal(a, b)
         assert st_a["collisions"] == st_b["collisions"] and st_a["real_scatters"] == st_b["real_scatters"] and st_a["rays"] == st_b["rays"]
         assert pa["shade_b_medium"]["items"] == 0 and pb["shade_b_medium"]["items"] == st_b["real_scatters"] - 0 or pb["shade_b_medium"]["items"] > 0
+
+
+def test_reference_order_refill_loops_equal_one_item_per_thread_kernels(monkeypatch):
+    """k_wv_track_ref / k_wv_nee_ref (persistent refill loops) against k_wv_track / k_wv_nee (LR_REF_REFILL_OFF=1): identical lanes."""
+    d = scenes.liver_multi_mesh(res=40, spp=8)
+    d["capsule"]["sigma_t"]["grid"] = scenes.sigmat_field(16); d["parenchyma"]["sigma_t"]["grid"] = scenes.sigmat_field(32)
+    for dd in (scenes.liver_single_mesh(res=40, spp=8, grid_res=32, phase="hg"), d, G.scene("test_homo_null_envmap", spp=8)):
+        sc = mi.load_dict(dd); W, H = sc.film_size; n = W * H * 8
+        monkeypatch.delenv("LR_REF_REFILL_OFF", raising=False)
+        c1 = mi.Context(0).upload(sc); a = c1.sample_lanes(7, 8, 0, n); st_a = c1.stats()
+        monkeypatch.setenv("LR_REF_REFILL_OFF", "1")
+        c2 = mi.Context(0).upload(sc); b = c2.sample_lanes(7, 8, 0, n); st_b = c2.stats()
+        assert np.array_equal(a, b)
+        assert st_a["collisions"] == st_b["collisions"] and st_a["rays"] == st_b["rays"]

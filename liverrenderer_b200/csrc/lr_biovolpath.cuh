@@ -2,7 +2,7 @@
 // Media: src/media/liver.cpp:133-574, glissonCapsule.cpp:134-414, parenchyma.cpp:134-393 (element types:
 // organic_material.h:30-35).  Integrator: src/integrators/biovolpath.cpp:95-551.
 // Semantics are those of the reference's JIT variants (cuda_rgb / llvm_ad_rgb), including the statements that run without
-// a per-lane mask -- see the notes at bio_sample_interaction and at the top of sample_biovolpath.  Every tissue medium is
+// a per-lane mask -- see the notes at bio_sample_interaction and above BioPath.  Every tissue medium is
 // `m_is_homogeneous` with sigma_n = 0: a free path is not an exponential in sigma_t but the minimum of one exponential per
 // tissue element, drawn from an inner PCG32 seeded with the bit pattern of the integrator's sample.
 #pragma once
@@ -77,7 +77,7 @@ LR_DEV float bio_compute_distance(const lr_medium &m, uint32_t channel, float sa
 
 // sample_interaction with the tissue depth (liver.cpp:483-547, glissonCapsule.cpp:307-383, parenchyma.cpp:305-362).
 // `maxt` is what the integrator passes as Ray3f(ray, si.t).maxt.  `active_in` is the Mask argument: false only in the
-// iteration in which a lane dies (see sample_biovolpath).  JIT semantics of the `if (any_or<true>(..)) .. else if ..`
+// iteration in which a lane dies (note (2) above BioPath).  JIT semantics of the `if (any_or<true>(..)) .. else if ..`
 // chains in glissonCapsule.cpp / parenchyma.cpp: only the first branch executes (under its own mask).
 LR_DEV BioInteraction bio_sample_interaction(const lr_medium &m, const Ray &ray, float maxt, float sample, uint32_t channel, float depth,
                                              bool active_in, uint32_t &n_collisions) {
@@ -193,10 +193,10 @@ LR_DEV void bio_apply_transmittance(const BioInteraction &mei, int medium, V3 &r
 //  (2) in the iteration in which a lane dies at the top (Russian roulette / max_depth), lanes inside a medium still get a
 //      fresh interaction -- from the sampler's NEXT value, which a masked next_1d returns without consuming it, and with
 //      active = false -- and :304 zeroes `result` per channel where that interaction's transmittance is 0.
-// The loop is written as a resumable path: init() + one step() per iteration of the reference's loop (the unit a wavefront port
-// would cut at).  Handing a finished lane a new path between steps was tried and bought nothing (0.98x / 0.88x on the two liver
-// scenes): the idle lanes of k_render<biovolpath> -- 8 of 32 threads active per instruction, profiles/r2_kernel_metrics_bio_per_lane.txt --
-// sit inside a step (BVH walks and shadow walks of different lengths), not behind a long path.
+// The loop is written as a resumable path: init() + one step() per iteration of the reference's loop -- the unit the production wavefront
+// (lr_wavefront_bio.cuh) cuts at; this per-lane form is the parity probe.  Handing a finished lane a new path between steps was tried
+// first and bought nothing (0.98x / 0.88x on the two liver scenes): the idle lanes of k_render<biovolpath> -- 8 of 32 threads active per
+// instruction, profiles/r2_kernel_metrics_bio_per_lane.txt -- sit inside a step (BVH walks and shadow walks of different lengths).
 struct BioPath {
     Sampler smp; Ray ray; V3 throughput, result, last_scatter_p;
     float eta, last_scatter_direction_pdf, tissue_depth, si_t;            // si_t: the previous intersection's distance (what :222 passes as maxt)

@@ -139,9 +139,9 @@ LR_DEV V3 sample_emitter_mis(const DScene &sc, const DTri *tris_gid, V3 ref_p, V
 }
 
 // VolpathMisIntegratorImpl::sample (volpathmis.cpp:120-463) as a resumable path: init() + one step() per iteration of the reference's
-// loop.  Refilling finished lanes between steps does not help (1.04x on the C3 frame): 2.4 of 32 threads are active per instruction
-// (profiles/r2_kernel_metrics_mis.txt) because a step contains the emitter-sampling walk -- tens of global-majorant collisions for one
-// lane while its neighbours wait.  The fix is the wavefront cut at collision granularity that volpath already has (lr_wavefront.cuh).
+// loop.  This per-lane form is the parity probe; production is the wavefront (lr_wavefront_mis.cuh).  ncu on k_render<volpathmis>: 2.4 of 32
+// threads active per instruction (profiles/r2_kernel_metrics_mis.txt) -- a step contains the emitter-sampling walk, tens of global-majorant
+// collisions for one lane while its neighbours wait -- and refilling finished lanes between steps does not help (1.04x).
 template <bool SPECTRAL>
 struct MisPath {
     Sampler smp; Ray ray; SurfaceInteraction si; V3 result, last_scatter_p; float eta;
